@@ -1,0 +1,194 @@
+// C ABI of the host-side harness (mesh generation, decomposition, initial conditions).
+// Declared in include/mpas_b200.h.  Handles are opaque pointers; errors return non-zero /
+// NULL and leave a message retrievable through mpas_b200_last_error().
+#include <cstring>
+#include <memory>
+#include <string>
+
+#include "decomp.h"
+#include "init_atm.h"
+#include "mesh.h"
+#include "pool.h"
+
+using namespace mpas;
+
+namespace mpas {
+std::string g_last_error;
+}
+
+struct HostCase {
+    Mesh global;                 // global mesh (SFC order if requested), unit sphere scaled to radius a
+    MeshPermutation perm;        // SFC permutation (new -> generator order)
+    bool has_perm = false;
+    InitConfig cfg;
+    std::vector<int> part;       // partition (0-based block id per global cell)
+    int nBlocks = 0;
+    std::vector<std::unique_ptr<Block>> blocks;
+};
+
+#define API_TRY try {
+#define API_CATCH(ret)                      \
+    }                                       \
+    catch (const std::exception& e) {       \
+        mpas::g_last_error = e.what();      \
+        return ret;                         \
+    }
+
+extern "C" {
+
+const char* mpas_b200_last_error() { return mpas::g_last_error.c_str(); }
+
+// Create a global icosahedral mesh (unit sphere -> radius a), optionally SFC-reordered.
+void* mpas_host_case_create(int level, int lloyd_iters, int sfc) {
+    API_TRY
+    auto* hc = new HostCase();
+    Mesh gen;
+    make_icosahedral_mesh(level, gen, lloyd_iters);
+    if (sfc) {
+        sfc_reorder(gen, hc->global, hc->perm);
+        hc->has_perm = true;
+    } else {
+        hc->global = gen;
+    }
+    scale_mesh_to_sphere(hc->global, Constants::a);
+    return hc;
+    API_CATCH(nullptr)
+}
+
+void mpas_host_case_destroy(void* h) { delete (HostCase*)h; }
+
+int mpas_host_case_dims(void* h, int* nCells, int* nEdges, int* nVertices, int* maxEdges, int* maxEdges2) {
+    auto* hc = (HostCase*)h;
+    *nCells = hc->global.nCells; *nEdges = hc->global.nEdges; *nVertices = hc->global.nVertices;
+    *maxEdges = hc->global.maxEdges; *maxEdges2 = hc->global.maxEdges2;
+    return 0;
+}
+
+// SFC permutation: kind 0 cells, 1 edges, 2 vertices; out[new] = old (0-based)
+int mpas_host_case_permutation(void* h, int kind, int* out) {
+    auto* hc = (HostCase*)h;
+    if (!hc->has_perm) { mpas::g_last_error = "case has no SFC permutation"; return 1; }
+    const std::vector<int>& v = kind == 0 ? hc->perm.cellNewToOld : kind == 1 ? hc->perm.edgeNewToOld : hc->perm.vertexNewToOld;
+    std::memcpy(out, v.data(), v.size() * sizeof(int));
+    return 0;
+}
+
+// Partition into nBlocks: method 0 = METIS k-way (libmetis), 1 = contiguous SFC chunks,
+// 2 = read "<prefix><nBlocks>" partition file (reference format).  Writes graph.info and the
+// partition file when prefix is non-empty.
+int mpas_host_case_partition(void* h, int nBlocks, int method, const char* prefix) {
+    API_TRY
+    auto* hc = (HostCase*)h;
+    std::string pre = prefix ? prefix : "";
+    hc->nBlocks = nBlocks;
+    if (nBlocks == 1) {
+        hc->part.assign(hc->global.nCells, 0);
+    } else if (method == 2) {
+        if (!read_partition(pre + std::to_string(nBlocks), hc->global.nCells, hc->part))
+            throw std::runtime_error("partition file missing or wrong number of lines");
+    } else {
+        partition_cells(hc->global, nBlocks, method, hc->part);
+    }
+    if (!pre.empty() && method != 2) {
+        write_graph_info(hc->global, pre.substr(0, pre.size() - 6));  // "graph.info.part." -> "graph.info"
+        write_partition(hc->part, pre + std::to_string(nBlocks));
+    }
+    return 0;
+    API_CATCH(1)
+}
+
+int mpas_host_case_get_partition(void* h, int* out) {
+    auto* hc = (HostCase*)h;
+    std::memcpy(out, hc->part.data(), hc->part.size() * sizeof(int));
+    return 0;
+}
+
+// Build block `iBlock` (owned + 2 cell halo layers / 3 edge+vertex layers, reference ordering and
+// exchange lists) and initialise its pool with the JW case.  Other blocks need not exist in this
+// process (one process per GPU builds only its own block).
+int mpas_host_case_build_block(void* h, int iBlock, int nVertLevels, int init_case, int num_scalars, int full_fields, int keep_zb) {
+    API_TRY
+    auto* hc = (HostCase*)h;
+    if (hc->nBlocks == 0) { hc->nBlocks = 1; hc->part.assign(hc->global.nCells, 0); }
+    if ((int)hc->blocks.size() < hc->nBlocks) hc->blocks.resize(hc->nBlocks);
+    hc->cfg.nVertLevels = nVertLevels;
+    hc->cfg.init_case = init_case;
+    hc->cfg.num_scalars = num_scalars;
+    hc->cfg.keep_zb = keep_zb != 0;
+    auto blk = std::make_unique<Block>();
+    build_block(hc->global, hc->part, hc->nBlocks, iBlock, 2, *blk);
+    Pool& p = blk->pool;
+    mesh_to_pool(blk->mesh, p);
+    init_advection_and_deformation(blk->mesh, p);
+    init_case_jw(blk->mesh, hc->cfg, p);
+    core_init_derived(blk->mesh, hc->cfg, p);
+    allocate_dycore_fields(blk->mesh, hc->cfg, p, full_fields != 0);
+    p.cfg["config_coef_3rd_order"] = hc->cfg.coef_3rd_order;
+    hc->blocks[iBlock] = std::move(blk);
+    return 0;
+    API_CATCH(1)
+}
+
+void* mpas_host_case_block(void* h, int iBlock) {
+    auto* hc = (HostCase*)h;
+    if (iBlock < 0 || iBlock >= (int)hc->blocks.size() || !hc->blocks[iBlock]) return nullptr;
+    return hc->blocks[iBlock].get();
+}
+
+// ---- pool access -----------------------------------------------------------------------
+int mpas_host_block_nfields(void* b) { return (int)((Block*)b)->pool.f.size(); }
+
+int mpas_host_block_field_info(void* b, int idx, char* name, int name_cap, int* kind, int* loc, int* ndims, long long* dims) {
+    Pool& p = ((Block*)b)->pool;
+    auto it = p.f.begin();
+    std::advance(it, idx);
+    std::strncpy(name, it->first.c_str(), name_cap - 1);
+    name[name_cap - 1] = 0;
+    *kind = it->second.kind; *loc = it->second.loc; *ndims = (int)it->second.dims.size();
+    for (size_t k = 0; k < it->second.dims.size(); ++k) dims[k] = it->second.dims[k];
+    return 0;
+}
+
+void* mpas_host_block_field_ptr(void* b, const char* name) {
+    Pool& p = ((Block*)b)->pool;
+    auto it = p.f.find(name);
+    if (it == p.f.end()) { mpas::g_last_error = std::string("no field ") + name; return nullptr; }
+    return it->second.kind == FK_REAL ? (void*)it->second.r.data() : (void*)it->second.i.data();
+}
+
+int mpas_host_block_ncfg(void* b) { return (int)((Block*)b)->pool.cfg.size(); }
+int mpas_host_block_cfg_info(void* b, int idx, char* name, int name_cap, double* value) {
+    Pool& p = ((Block*)b)->pool;
+    auto it = p.cfg.begin();
+    std::advance(it, idx);
+    std::strncpy(name, it->first.c_str(), name_cap - 1);
+    name[name_cap - 1] = 0;
+    *value = it->second;
+    return 0;
+}
+
+// ---- exchange lists (reference form, src/framework/mpas_dmpar.F:1483-2038) -----------------
+// kind: 0 cells, 1 edges, 2 vertices; which: 0 send, 1 recv.  Returns the number of
+// (neighbour, layer) lists; each list is queried by index.
+int mpas_host_block_nexch(void* b, int kind, int which) {
+    Block* blk = (Block*)b;
+    const ExchangeSet& s = kind == 0 ? blk->cellExch : kind == 1 ? blk->edgeExch : blk->vertexExch;
+    return (int)(which == 0 ? s.send.size() : s.recv.size());
+}
+int mpas_host_block_exch_info(void* b, int kind, int which, int idx, int* endPoint, int* haloLayer, int* nlist) {
+    Block* blk = (Block*)b;
+    const ExchangeSet& s = kind == 0 ? blk->cellExch : kind == 1 ? blk->edgeExch : blk->vertexExch;
+    const ExchangeList& l = which == 0 ? s.send[idx] : s.recv[idx];
+    *endPoint = l.endPointID; *haloLayer = l.haloLayer; *nlist = (int)l.srcList.size();
+    return 0;
+}
+int mpas_host_block_exch_lists(void* b, int kind, int which, int idx, int* srcList, int* destList) {
+    Block* blk = (Block*)b;
+    const ExchangeSet& s = kind == 0 ? blk->cellExch : kind == 1 ? blk->edgeExch : blk->vertexExch;
+    const ExchangeList& l = which == 0 ? s.send[idx] : s.recv[idx];
+    std::memcpy(srcList, l.srcList.data(), l.srcList.size() * sizeof(int));
+    std::memcpy(destList, l.destList.data(), l.destList.size() * sizeof(int));
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,571 @@
+// In-harness mesh generation: icosahedral Voronoi meshes (recursive bisection) and the
+// MPAS connectivity arrays the dycore reads.  The reference does not contain a mesh
+// generator (meshes come from external MPAS-Tools files); array names,
+// shapes and conventions follow src/core_atmosphere/Registry.xml:1127-1330 and the
+// usage in src/core_atmosphere/dynamics/mpas_atm_time_integration.F:4812-4819 (Coriolis
+// weights), :5606-5620 (vertex circulation sign), :5702-5711 (kites), and
+// src/core_init_atmosphere/mpas_atm_advection.F:744-937 (vertex i precedes edge i,
+// counter-clockwise ordering around a cell).
+#include "mesh.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <stdexcept>
+#include <unordered_map>
+
+namespace mpas {
+
+void Mesh::alloc(int nc, int ne, int nv) {
+    nCells = nc;
+    nEdges = ne;
+    nVertices = nv;
+    auto R = [](std::vector<double>& v, size_t n) { v.assign(n, 0.0); };
+    auto I = [](std::vector<int>& v, size_t n) { v.assign(n, 0); };
+    size_t c1 = nc + 1, e1 = ne + 1, v1 = nv + 1;
+    I(indexToCellID, c1); I(indexToEdgeID, e1); I(indexToVertexID, v1);
+    R(xCell, c1); R(yCell, c1); R(zCell, c1); R(latCell, c1); R(lonCell, c1);
+    R(xEdge, e1); R(yEdge, e1); R(zEdge, e1); R(latEdge, e1); R(lonEdge, e1);
+    R(xVertex, v1); R(yVertex, v1); R(zVertex, v1); R(latVertex, v1); R(lonVertex, v1);
+    R(dcEdge, e1); R(dvEdge, e1); R(angleEdge, e1); R(areaCell, c1); R(areaTriangle, v1);
+    meshDensity.assign(c1, 1.0);
+    R(kiteAreasOnVertex, 3 * v1);
+    R(weightsOnEdge, (size_t)maxEdges2 * e1);
+    I(nEdgesOnCell, c1);
+    I(cellsOnCell, (size_t)maxEdges * c1); I(edgesOnCell, (size_t)maxEdges * c1);
+    I(verticesOnCell, (size_t)maxEdges * c1);
+    I(cellsOnEdge, 2 * e1); I(verticesOnEdge, 2 * e1);
+    I(nEdgesOnEdge, e1); I(edgesOnEdge, (size_t)maxEdges2 * e1);
+    I(cellsOnVertex, 3 * v1); I(edgesOnVertex, 3 * v1);
+}
+
+namespace {
+
+struct V3 {
+    double x, y, z;
+};
+inline V3 operator+(V3 a, V3 b) { return {a.x + b.x, a.y + b.y, a.z + b.z}; }
+inline V3 operator-(V3 a, V3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline V3 operator*(double s, V3 a) { return {s * a.x, s * a.y, s * a.z}; }
+inline double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+inline V3 cross(V3 a, V3 b) { return {a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x}; }
+inline double norm(V3 a) { return std::sqrt(dot(a, a)); }
+inline V3 unit(V3 a) {
+    double n = norm(a);
+    return {a.x / n, a.y / n, a.z / n};
+}
+inline double arc(V3 a, V3 b) {  // great-circle distance on the unit sphere
+    return 2.0 * std::asin(std::min(1.0, 0.5 * norm(a - b)));
+}
+// area of spherical triangle on unit sphere (robust formula via tan(E/2))
+inline double tri_area(V3 a, V3 b, V3 c) {
+    double num = std::fabs(dot(a, cross(b, c)));
+    double den = 1.0 + dot(a, b) + dot(b, c) + dot(c, a);
+    return 2.0 * std::atan2(num, den);
+}
+
+struct Tri {
+    int v[3];
+};
+
+}  // namespace
+
+// Build all connectivity from cell positions + CCW triangles (Delaunay dual).
+static void build_from_triangulation(const std::vector<V3>& pts, const std::vector<Tri>& tris, Mesh& m) {
+    const int nc = (int)pts.size();
+    const int nv = (int)tris.size();
+    // ---- edges: unique cell pairs
+    struct Half {
+        int a, b, tri;
+    };
+    std::vector<Half> halves;
+    halves.reserve((size_t)3 * nv);
+    for (int t = 0; t < nv; ++t)
+        for (int s = 0; s < 3; ++s) {
+            int a = tris[t].v[s], b = tris[t].v[(s + 1) % 3];
+            halves.push_back({a, b, t});
+        }
+    // key on (min,max); directed a->b has the triangle on its LEFT (CCW triangle)
+    std::vector<int> order(halves.size());
+    for (size_t i = 0; i < order.size(); ++i) order[i] = (int)i;
+    auto key = [&](int i) {
+        const Half& h = halves[i];
+        uint64_t lo = std::min(h.a, h.b), hi = std::max(h.a, h.b);
+        return (lo << 32) | hi;
+    };
+    std::sort(order.begin(), order.end(), [&](int i, int j) {
+        uint64_t ki = key(i), kj = key(j);
+        if (ki != kj) return ki < kj;
+        return i < j;
+    });
+    if (order.size() % 2) throw std::runtime_error("mesh: open triangulation");
+    const int ne = (int)(order.size() / 2);
+    m.maxEdges = 6;
+    m.maxEdges2 = 12;
+    m.alloc(nc, ne, nv);
+    m.nCellsSolve = nc;
+    m.nEdgesSolve = ne;
+    m.nVerticesSolve = nv;
+    for (int i = 0; i < nc; ++i) {
+        m.xCell[i] = pts[i].x; m.yCell[i] = pts[i].y; m.zCell[i] = pts[i].z;
+        m.indexToCellID[i] = i + 1;
+    }
+    for (int t = 0; t < nv; ++t) {
+        V3 a = pts[tris[t].v[0]], b = pts[tris[t].v[1]], c = pts[tris[t].v[2]];
+        V3 cc = unit(cross(b - a, c - a));  // circumcentre direction (outward for CCW)
+        m.xVertex[t] = cc.x; m.yVertex[t] = cc.y; m.zVertex[t] = cc.z;
+        m.indexToVertexID[t] = t + 1;
+        for (int s = 0; s < 3; ++s) m.cellsOnVertex[3 * t + s] = tris[t].v[s] + 1;
+    }
+    // per-cell incident edges (neighbour, edge)
+    std::vector<int> nInc(nc, 0);
+    std::vector<int> incNbr((size_t)nc * 6, -1), incEdge((size_t)nc * 6, -1);
+    std::vector<int> evCount(nv, 0);
+    for (int e = 0; e < ne; ++e) {
+        const Half& h0 = halves[order[2 * e]];
+        const Half& h1 = halves[order[2 * e + 1]];
+        if (key(order[2 * e]) != key(order[2 * e + 1])) throw std::runtime_error("mesh: unmatched edge");
+        int c1 = std::min(h0.a, h0.b), c2 = std::max(h0.a, h0.b);
+        // triangle on the left of c1->c2 is the half whose a==c1
+        int tl = (h0.a == c1) ? h0.tri : h1.tri;
+        int tr = (h0.a == c1) ? h1.tri : h0.tri;
+        m.cellsOnEdge[2 * e] = c1 + 1;
+        m.cellsOnEdge[2 * e + 1] = c2 + 1;
+        m.verticesOnEdge[2 * e] = tr + 1;      // vertex 1: right of the normal
+        m.verticesOnEdge[2 * e + 1] = tl + 1;  // vertex 2: left  (tangent = k x n points 1->2)
+        m.indexToEdgeID[e] = e + 1;
+        for (int c : {c1, c2}) {
+            if (nInc[c] >= 6) throw std::runtime_error("mesh: cell with more than 6 edges");
+            incNbr[(size_t)c * 6 + nInc[c]] = (c == c1) ? c2 : c1;
+            incEdge[(size_t)c * 6 + nInc[c]] = e;
+            nInc[c]++;
+        }
+        for (int t : {tr, tl}) {
+            if (evCount[t] >= 3) throw std::runtime_error("mesh: vertex degree > 3");
+            m.edgesOnVertex[3 * t + evCount[t]++] = e + 1;
+        }
+    }
+    // per-cell incident triangles as (q, r, tri) meaning CCW triangle (p,q,r)
+    std::vector<int> nT(nc, 0);
+    std::vector<int> tq((size_t)nc * 6), trr((size_t)nc * 6), tt((size_t)nc * 6);
+    for (int t = 0; t < nv; ++t)
+        for (int s = 0; s < 3; ++s) {
+            int p = tris[t].v[s], q = tris[t].v[(s + 1) % 3], r = tris[t].v[(s + 2) % 3];
+            if (nT[p] >= 6) throw std::runtime_error("mesh: cell with more than 6 triangles");
+            size_t k = (size_t)p * 6 + nT[p]++;
+            tq[k] = q; trr[k] = r; tt[k] = t;
+        }
+    for (int p = 0; p < nc; ++p) {
+        int n = nT[p];
+        if (n != nInc[p] || n < 5) throw std::runtime_error("mesh: inconsistent cell degree");
+        m.nEdgesOnCell[p] = n;
+        // start with the triangle whose q is the smallest neighbour (deterministic)
+        int start = 0;
+        for (int k = 1; k < n; ++k)
+            if (tq[(size_t)p * 6 + k] < tq[(size_t)p * 6 + start]) start = k;
+        int cur = start;
+        // slot i: cellsOnCell = r of current triangle, verticesOnCell = current triangle
+        // (vertex i lies between neighbour i-1 (=q) and neighbour i (=r): it PRECEDES edge i)
+        for (int i = 0; i < n; ++i) {
+            size_t k = (size_t)p * 6 + cur;
+            int r = trr[k];
+            m.cellsOnCell[(size_t)p * m.maxEdges + i] = r + 1;
+            m.verticesOnCell[(size_t)p * m.maxEdges + i] = tt[k] + 1;
+            int e = -1;
+            for (int j = 0; j < n; ++j)
+                if (incNbr[(size_t)p * 6 + j] == r) e = incEdge[(size_t)p * 6 + j];
+            if (e < 0) throw std::runtime_error("mesh: edge lookup failed");
+            m.edgesOnCell[(size_t)p * m.maxEdges + i] = e + 1;
+            // next triangle CCW: the one whose q == r
+            int nxt = -1;
+            for (int j = 0; j < n; ++j)
+                if (tq[(size_t)p * 6 + j] == r) nxt = j;
+            if (nxt < 0) throw std::runtime_error("mesh: triangle fan broken");
+            cur = nxt;
+        }
+    }
+    // garbage element connectivity -> garbage (as the reference's reindexing does)
+    m.nEdgesOnCell[nc] = 0;
+    m.cellsOnEdge[2 * ne] = nc + 1;
+    m.cellsOnEdge[2 * ne + 1] = nc + 1;
+    m.verticesOnEdge[2 * ne] = nv + 1;
+    m.verticesOnEdge[2 * ne + 1] = nv + 1;
+    for (int s = 0; s < 3; ++s) {
+        m.cellsOnVertex[3 * nv + s] = nc + 1;
+        m.edgesOnVertex[3 * nv + s] = ne + 1;
+    }
+    m.nCellsHalo = {nc};
+    m.nEdgesHalo = {ne};
+    m.nVerticesHalo = {nv};
+}
+
+// ---------------------------------------------------------------------------------------
+// Metrics: lat/lon, dcEdge, dvEdge, angleEdge, kite areas, areaCell, areaTriangle and the
+// TRiSK tangential-reconstruction weights (Thuburn et al. 2009; Ringler et al. 2010):
+//   weightsOnEdge(j,e) = n(e,i) * n(e',i) * (1/2 - sum_{v from e to e' CCW} R(i,v)) * dv(e')/dc(e)
+// with R(i,v) = kiteArea(i,v)/areaCell(i), n(e,i) = +1 when cell i is cellsOnEdge(1,e).
+// Sign convention verified by tests/test_mesh.py (solid-body rotation: v = u . (k x n)).
+// ---------------------------------------------------------------------------------------
+static inline void latlon(double x, double y, double z, double& lat, double& lon) {
+    double r = std::sqrt(x * x + y * y + z * z);
+    lat = std::asin(std::max(-1.0, std::min(1.0, z / r)));
+    lon = std::atan2(y, x);
+    if (lon < 0.0) lon += 2.0 * M_PI;
+}
+
+void compute_mesh_metrics(Mesh& m) {
+    if (!m.on_a_sphere) return;  // planar meshes are generated with analytic metrics
+    const int nc = m.nCells, ne = m.nEdges, nv = m.nVertices, mE = m.maxEdges, mE2 = m.maxEdges2;
+    auto C = [&](int i) { return V3{m.xCell[i], m.yCell[i], m.zCell[i]}; };
+    auto Vv = [&](int i) { return V3{m.xVertex[i], m.yVertex[i], m.zVertex[i]}; };
+    auto E = [&](int i) { return V3{m.xEdge[i], m.yEdge[i], m.zEdge[i]}; };
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < nc; ++i) latlon(m.xCell[i], m.yCell[i], m.zCell[i], m.latCell[i], m.lonCell[i]);
+#pragma omp parallel for schedule(static)
+    for (int i = 0; i < nv; ++i) latlon(m.xVertex[i], m.yVertex[i], m.zVertex[i], m.latVertex[i], m.lonVertex[i]);
+#pragma omp parallel for schedule(static)
+    for (int e = 0; e < ne; ++e) {
+        int c1 = m.cellsOnEdge[2 * e] - 1, c2 = m.cellsOnEdge[2 * e + 1] - 1;
+        int v1 = m.verticesOnEdge[2 * e] - 1, v2 = m.verticesOnEdge[2 * e + 1] - 1;
+        if (c1 >= nc || c2 >= nc || v1 >= nv || v2 >= nv) continue;  // incomplete halo edge
+        V3 xe = unit(C(c1) + C(c2));
+        m.xEdge[e] = xe.x; m.yEdge[e] = xe.y; m.zEdge[e] = xe.z;
+        latlon(xe.x, xe.y, xe.z, m.latEdge[e], m.lonEdge[e]);
+        m.dcEdge[e] = arc(C(c1), C(c2));
+        m.dvEdge[e] = arc(Vv(v1), Vv(v2));
+        // normal direction at the edge point: c1 -> c2 projected on the tangent plane
+        V3 d = C(c2) - C(c1);
+        V3 n = unit(d - dot(d, xe) * xe);
+        double lat = m.latEdge[e], lon = m.lonEdge[e];
+        V3 east{-std::sin(lon), std::cos(lon), 0.0};
+        V3 north{-std::sin(lat) * std::cos(lon), -std::sin(lat) * std::sin(lon), std::cos(lat)};
+        m.angleEdge[e] = std::atan2(dot(n, north), dot(n, east));
+    }
+    // kites: for vertex v and its cell j: quad (cell, edge point a, vertex, edge point b) where a,b are
+    // the two edges of v that touch cell j.
+#pragma omp parallel for schedule(static)
+    for (int v = 0; v < nv; ++v) {
+        double tot = 0.0;
+        for (int j = 0; j < 3; ++j) {
+            int c = m.cellsOnVertex[3 * v + j] - 1;
+            double a = 0.0;
+            if (c < nc) {
+                for (int k = 0; k < 3; ++k) {
+                    int e = m.edgesOnVertex[3 * v + k] - 1;
+                    if (e >= ne) continue;
+                    if (m.cellsOnEdge[2 * e] - 1 == c || m.cellsOnEdge[2 * e + 1] - 1 == c)
+                        a += tri_area(C(c), E(e), Vv(v));
+                }
+            }
+            m.kiteAreasOnVertex[3 * v + j] = a;
+            tot += a;
+        }
+        m.areaTriangle[v] = tot;
+    }
+#pragma omp parallel for schedule(static)
+    for (int c = 0; c < nc; ++c) {
+        double a = 0.0;
+        for (int i = 0; i < m.nEdgesOnCell[c]; ++i) {
+            int v = m.verticesOnCell[(size_t)c * mE + i] - 1;
+            if (v >= nv) continue;
+            for (int j = 0; j < 3; ++j)
+                if (m.cellsOnVertex[3 * v + j] - 1 == c) a += m.kiteAreasOnVertex[3 * v + j];
+        }
+        m.areaCell[c] = a;
+    }
+    // TRiSK weights
+#pragma omp parallel for schedule(static)
+    for (int e = 0; e < ne; ++e) {
+        int k = 0;
+        for (int j = 0; j < mE2; ++j) {
+            m.edgesOnEdge[(size_t)e * mE2 + j] = ne + 1;
+            m.weightsOnEdge[(size_t)e * mE2 + j] = 0.0;
+        }
+        bool complete = true;
+        for (int side = 0; side < 2; ++side) {
+            int c = m.cellsOnEdge[2 * e + side] - 1;
+            if (c >= nc) { complete = false; continue; }
+            int n = m.nEdgesOnCell[c];
+            int pos = -1;
+            for (int i = 0; i < n; ++i)
+                if (m.edgesOnCell[(size_t)c * mE + i] - 1 == e) pos = i;
+            if (pos < 0) { complete = false; continue; }
+            double ne_i = (side == 0) ? 1.0 : -1.0;
+            double sumR = 0.0;
+            for (int l = 1; l < n; ++l) {
+                int slot = (pos + l) % n;
+                int v = m.verticesOnCell[(size_t)c * mE + slot] - 1;  // vertex preceding edge 'slot'
+                double kite = 0.0;
+                if (v < nv)
+                    for (int j = 0; j < 3; ++j)
+                        if (m.cellsOnVertex[3 * v + j] - 1 == c) kite = m.kiteAreasOnVertex[3 * v + j];
+                sumR += kite / m.areaCell[c];
+                int eo = m.edgesOnCell[(size_t)c * mE + slot] - 1;
+                double nep_i = (eo < ne && m.cellsOnEdge[2 * eo] - 1 == c) ? 1.0 : -1.0;
+                if (k < mE2) {
+                    m.edgesOnEdge[(size_t)e * mE2 + k] = eo + 1;
+                    double dvp = (eo < ne) ? m.dvEdge[eo] : 0.0;
+                    m.weightsOnEdge[(size_t)e * mE2 + k] = ne_i * nep_i * (0.5 - sumR) * dvp / m.dcEdge[e];
+                }
+                ++k;
+            }
+        }
+        (void)complete;
+        m.nEdgesOnEdge[e] = std::min(k, mE2);
+    }
+    m.nEdgesOnEdge[ne] = 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// Icosahedral grid by recursive bisection
+// ---------------------------------------------------------------------------------------
+void make_icosahedral_mesh(int level, Mesh& m, int lloyd_iters) {
+    const double t = (1.0 + std::sqrt(5.0)) / 2.0;
+    std::vector<V3> pts = {{-1, t, 0}, {1, t, 0}, {-1, -t, 0}, {1, -t, 0}, {0, -1, t}, {0, 1, t},
+                           {0, -1, -t}, {0, 1, -t}, {t, 0, -1}, {t, 0, 1}, {-t, 0, -1}, {-t, 0, 1}};
+    for (auto& p : pts) p = unit(p);
+    static const int F[20][3] = {{0, 11, 5}, {0, 5, 1}, {0, 1, 7}, {0, 7, 10}, {0, 10, 11}, {1, 5, 9}, {5, 11, 4},
+                                 {11, 10, 2}, {10, 7, 6}, {7, 1, 8}, {3, 9, 4}, {3, 4, 2}, {3, 2, 6}, {3, 6, 8},
+                                 {3, 8, 9}, {4, 9, 5}, {2, 4, 11}, {6, 2, 10}, {8, 6, 7}, {9, 8, 1}};
+    std::vector<Tri> tris(20);
+    for (int f = 0; f < 20; ++f) {
+        tris[f] = {{F[f][0], F[f][1], F[f][2]}};
+        V3 a = pts[F[f][0]], b = pts[F[f][1]], c = pts[F[f][2]];
+        if (dot(cross(b - a, c - a), a) < 0) std::swap(tris[f].v[1], tris[f].v[2]);
+    }
+    for (int l = 0; l < level; ++l) {
+        std::unordered_map<uint64_t, int> mid;
+        mid.reserve(tris.size() * 2);
+        std::vector<Tri> nt;
+        nt.reserve(tris.size() * 4);
+        auto midpoint = [&](int a, int b) {
+            uint64_t lo = std::min(a, b), hi = std::max(a, b);
+            uint64_t k = (lo << 32) | hi;
+            auto it = mid.find(k);
+            if (it != mid.end()) return it->second;
+            int id = (int)pts.size();
+            pts.push_back(unit(pts[a] + pts[b]));
+            mid.emplace(k, id);
+            return id;
+        };
+        for (const Tri& T : tris) {
+            int a = T.v[0], b = T.v[1], c = T.v[2];
+            int ab = midpoint(a, b), bc = midpoint(b, c), ca = midpoint(c, a);
+            nt.push_back({{a, ab, ca}});
+            nt.push_back({{b, bc, ab}});
+            nt.push_back({{c, ca, bc}});
+            nt.push_back({{ab, bc, ca}});
+        }
+        tris.swap(nt);
+    }
+    m.on_a_sphere = true;
+    m.sphere_radius = 1.0;
+    build_from_triangulation(pts, tris, m);
+    compute_mesh_metrics(m);
+    // optional fixed-topology Lloyd relaxation toward a centroidal Voronoi tessellation
+    for (int it = 0; it < lloyd_iters; ++it) {
+        const int nc = m.nCells, mE = m.maxEdges;
+        std::vector<V3> np(nc);
+#pragma omp parallel for schedule(static)
+        for (int c = 0; c < nc; ++c) {
+            V3 ctr{m.xCell[c], m.yCell[c], m.zCell[c]};
+            V3 acc{0, 0, 0};
+            int n = m.nEdgesOnCell[c];
+            for (int i = 0; i < n; ++i) {
+                int v0 = m.verticesOnCell[(size_t)c * mE + i] - 1;
+                int v1 = m.verticesOnCell[(size_t)c * mE + (i + 1) % n] - 1;
+                V3 a{m.xVertex[v0], m.yVertex[v0], m.zVertex[v0]}, b{m.xVertex[v1], m.yVertex[v1], m.zVertex[v1]};
+                double w = tri_area(ctr, a, b);
+                acc = acc + w * unit(ctr + a + b);
+            }
+            np[c] = unit(acc);
+        }
+        for (int c = 0; c < nc; ++c) { m.xCell[c] = np[c].x; m.yCell[c] = np[c].y; m.zCell[c] = np[c].z; }
+#pragma omp parallel for schedule(static)
+        for (int v = 0; v < m.nVertices; ++v) {
+            V3 a = np[m.cellsOnVertex[3 * v] - 1], b = np[m.cellsOnVertex[3 * v + 1] - 1], c = np[m.cellsOnVertex[3 * v + 2] - 1];
+            V3 cc = unit(cross(b - a, c - a));
+            m.xVertex[v] = cc.x; m.yVertex[v] = cc.y; m.zVertex[v] = cc.z;
+        }
+    }
+    if (lloyd_iters > 0) compute_mesh_metrics(m);
+    // unused connectivity slots point at the garbage element
+    for (int c = 0; c <= m.nCells; ++c)
+        for (int i = (c < m.nCells ? m.nEdgesOnCell[c] : 0); i < m.maxEdges; ++i) {
+            m.cellsOnCell[(size_t)c * m.maxEdges + i] = m.nCells + 1;
+            m.edgesOnCell[(size_t)c * m.maxEdges + i] = m.nEdges + 1;
+            m.verticesOnCell[(size_t)c * m.maxEdges + i] = m.nVertices + 1;
+        }
+}
+
+// ---------------------------------------------------------------------------------------
+// Space-filling-curve renumbering.  Cells are sorted by a 3-D Hilbert key of their unit-
+// sphere position; edges and vertices are numbered in first-encounter order over the new
+// cell order (the same rule the reference uses for block-local edge numbering,
+// src/framework/mpas_block_decomp.F:369-421), so neighbouring columns sit close in memory.
+// ---------------------------------------------------------------------------------------
+static uint64_t hilbert3(uint32_t x, uint32_t y, uint32_t z, int bits) {
+    // Skilling's transpose-based Hilbert index
+    uint32_t X[3] = {x, y, z};
+    uint32_t M = 1u << (bits - 1), P, Q, t;
+    for (Q = M; Q > 1; Q >>= 1) {
+        P = Q - 1;
+        for (int i = 0; i < 3; ++i) {
+            if (X[i] & Q) X[0] ^= P;
+            else { t = (X[0] ^ X[i]) & P; X[0] ^= t; X[i] ^= t; }
+        }
+    }
+    for (int i = 1; i < 3; ++i) X[i] ^= X[i - 1];
+    t = 0;
+    for (Q = M; Q > 1; Q >>= 1)
+        if (X[2] & Q) t ^= Q - 1;
+    for (int i = 0; i < 3; ++i) X[i] ^= t;
+    uint64_t h = 0;
+    for (int b = bits - 1; b >= 0; --b)
+        for (int i = 0; i < 3; ++i) h = (h << 1) | ((X[i] >> b) & 1u);
+    return h;
+}
+
+void apply_permutation(const Mesh& in, const MeshPermutation& p, Mesh& out) {
+    const int nc = in.nCells, ne = in.nEdges, nv = in.nVertices, mE = in.maxEdges, mE2 = in.maxEdges2;
+    out = Mesh();
+    out.maxEdges = mE; out.maxEdges2 = mE2; out.vertexDegree = in.vertexDegree;
+    out.on_a_sphere = in.on_a_sphere; out.sphere_radius = in.sphere_radius;
+    out.alloc(nc, ne, nv);
+    out.nCellsSolve = in.nCellsSolve; out.nEdgesSolve = in.nEdgesSolve; out.nVerticesSolve = in.nVerticesSolve;
+    out.nCellsHalo = in.nCellsHalo; out.nEdgesHalo = in.nEdgesHalo; out.nVerticesHalo = in.nVerticesHalo;
+    auto mc = [&](int old1) { return old1 > nc ? nc + 1 : p.cellOldToNew[old1 - 1] + 1; };
+    auto me = [&](int old1) { return old1 > ne ? ne + 1 : p.edgeOldToNew[old1 - 1] + 1; };
+    auto mv = [&](int old1) { return old1 > nv ? nv + 1 : p.vertexOldToNew[old1 - 1] + 1; };
+#pragma omp parallel for schedule(static)
+    for (int c = 0; c < nc; ++c) {
+        int o = p.cellNewToOld[c];
+        out.indexToCellID[c] = c + 1;
+        out.xCell[c] = in.xCell[o]; out.yCell[c] = in.yCell[o]; out.zCell[c] = in.zCell[o];
+        out.latCell[c] = in.latCell[o]; out.lonCell[c] = in.lonCell[o];
+        out.areaCell[c] = in.areaCell[o]; out.meshDensity[c] = in.meshDensity[o];
+        out.nEdgesOnCell[c] = in.nEdgesOnCell[o];
+        for (int i = 0; i < mE; ++i) {
+            out.cellsOnCell[(size_t)c * mE + i] = mc(in.cellsOnCell[(size_t)o * mE + i]);
+            out.edgesOnCell[(size_t)c * mE + i] = me(in.edgesOnCell[(size_t)o * mE + i]);
+            out.verticesOnCell[(size_t)c * mE + i] = mv(in.verticesOnCell[(size_t)o * mE + i]);
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int e = 0; e < ne; ++e) {
+        int o = p.edgeNewToOld[e];
+        out.indexToEdgeID[e] = e + 1;
+        out.xEdge[e] = in.xEdge[o]; out.yEdge[e] = in.yEdge[o]; out.zEdge[e] = in.zEdge[o];
+        out.latEdge[e] = in.latEdge[o]; out.lonEdge[e] = in.lonEdge[o];
+        out.dcEdge[e] = in.dcEdge[o]; out.dvEdge[e] = in.dvEdge[o]; out.angleEdge[e] = in.angleEdge[o];
+        for (int s = 0; s < 2; ++s) {
+            out.cellsOnEdge[2 * e + s] = mc(in.cellsOnEdge[2 * o + s]);
+            out.verticesOnEdge[2 * e + s] = mv(in.verticesOnEdge[2 * o + s]);
+        }
+        out.nEdgesOnEdge[e] = in.nEdgesOnEdge[o];
+        for (int j = 0; j < mE2; ++j) {
+            out.edgesOnEdge[(size_t)e * mE2 + j] = me(in.edgesOnEdge[(size_t)o * mE2 + j]);
+            out.weightsOnEdge[(size_t)e * mE2 + j] = in.weightsOnEdge[(size_t)o * mE2 + j];
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int v = 0; v < nv; ++v) {
+        int o = p.vertexNewToOld[v];
+        out.indexToVertexID[v] = v + 1;
+        out.xVertex[v] = in.xVertex[o]; out.yVertex[v] = in.yVertex[o]; out.zVertex[v] = in.zVertex[o];
+        out.latVertex[v] = in.latVertex[o]; out.lonVertex[v] = in.lonVertex[o];
+        out.areaTriangle[v] = in.areaTriangle[o];
+        for (int s = 0; s < 3; ++s) {
+            out.cellsOnVertex[3 * v + s] = mc(in.cellsOnVertex[3 * o + s]);
+            out.edgesOnVertex[3 * v + s] = me(in.edgesOnVertex[3 * o + s]);
+            out.kiteAreasOnVertex[3 * v + s] = in.kiteAreasOnVertex[3 * o + s];
+        }
+    }
+    // garbage elements
+    out.cellsOnEdge[2 * ne] = out.cellsOnEdge[2 * ne + 1] = nc + 1;
+    out.verticesOnEdge[2 * ne] = out.verticesOnEdge[2 * ne + 1] = nv + 1;
+    for (int s = 0; s < 3; ++s) { out.cellsOnVertex[3 * nv + s] = nc + 1; out.edgesOnVertex[3 * nv + s] = ne + 1; }
+    for (int i = 0; i < mE; ++i) {
+        out.cellsOnCell[(size_t)nc * mE + i] = nc + 1; out.edgesOnCell[(size_t)nc * mE + i] = ne + 1;
+        out.verticesOnCell[(size_t)nc * mE + i] = nv + 1;
+    }
+    for (int j = 0; j < mE2; ++j) out.edgesOnEdge[(size_t)ne * mE2 + j] = ne + 1;
+}
+
+void invert_permutation(const MeshPermutation& p, MeshPermutation& inv) {
+    inv.cellNewToOld = p.cellOldToNew; inv.cellOldToNew = p.cellNewToOld;
+    inv.edgeNewToOld = p.edgeOldToNew; inv.edgeOldToNew = p.edgeNewToOld;
+    inv.vertexNewToOld = p.vertexOldToNew; inv.vertexOldToNew = p.vertexNewToOld;
+}
+
+void sfc_reorder(const Mesh& in, Mesh& out, MeshPermutation& p) {
+    const int nc = in.nCells, ne = in.nEdges, nv = in.nVertices, mE = in.maxEdges;
+    const int bits = 20;
+    std::vector<std::pair<uint64_t, int>> keys(nc);
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (int c = 0; c < nc; ++c) {
+        double q[3] = {in.xCell[c], in.yCell[c], in.zCell[c]};
+        for (int d = 0; d < 3; ++d) { lo[d] = std::min(lo[d], q[d]); hi[d] = std::max(hi[d], q[d]); }
+    }
+    for (int d = 0; d < 3; ++d) if (hi[d] <= lo[d]) hi[d] = lo[d] + 1.0;
+#pragma omp parallel for schedule(static)
+    for (int c = 0; c < nc; ++c) {
+        double q[3] = {in.xCell[c], in.yCell[c], in.zCell[c]};
+        uint32_t u[3];
+        for (int d = 0; d < 3; ++d) {
+            double s = (q[d] - lo[d]) / (hi[d] - lo[d]);
+            double f = s * (double)((1u << bits) - 1);
+            u[d] = (uint32_t)std::max(0.0, std::min((double)((1u << bits) - 1), f));
+        }
+        keys[c] = {hilbert3(u[0], u[1], u[2], bits), c};
+    }
+    std::sort(keys.begin(), keys.end());
+    p.cellNewToOld.resize(nc); p.cellOldToNew.resize(nc);
+    for (int c = 0; c < nc; ++c) { p.cellNewToOld[c] = keys[c].second; p.cellOldToNew[keys[c].second] = c; }
+    p.edgeOldToNew.assign(ne, -1); p.edgeNewToOld.clear(); p.edgeNewToOld.reserve(ne);
+    p.vertexOldToNew.assign(nv, -1); p.vertexNewToOld.clear(); p.vertexNewToOld.reserve(nv);
+    for (int c = 0; c < nc; ++c) {
+        int o = p.cellNewToOld[c];
+        for (int i = 0; i < in.nEdgesOnCell[o]; ++i) {
+            int e = in.edgesOnCell[(size_t)o * mE + i] - 1;
+            if (e < ne && p.edgeOldToNew[e] < 0) { p.edgeOldToNew[e] = (int)p.edgeNewToOld.size(); p.edgeNewToOld.push_back(e); }
+            int v = in.verticesOnCell[(size_t)o * mE + i] - 1;
+            if (v < nv && p.vertexOldToNew[v] < 0) { p.vertexOldToNew[v] = (int)p.vertexNewToOld.size(); p.vertexNewToOld.push_back(v); }
+        }
+    }
+    if ((int)p.edgeNewToOld.size() != ne || (int)p.vertexNewToOld.size() != nv)
+        throw std::runtime_error("sfc_reorder: unreachable edges/vertices");
+    apply_permutation(in, p, out);
+}
+
+void write_graph_info(const Mesh& m, const std::string& path) {
+    FILE* f = std::fopen(path.c_str(), "w");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    std::fprintf(f, "%d %d\n", m.nCells, m.nEdges);
+    for (int c = 0; c < m.nCells; ++c) {
+        for (int i = 0; i < m.nEdgesOnCell[c]; ++i) {
+            int n = m.cellsOnCell[(size_t)c * m.maxEdges + i];
+            if (n >= 1 && n <= m.nCells) std::fprintf(f, "%d ", n);
+        }
+        std::fprintf(f, "\n");
+    }
+    std::fclose(f);
+}
+void write_partition(const std::vector<int>& part, const std::string& path) {
+    FILE* f = std::fopen(path.c_str(), "w");
+    if (!f) throw std::runtime_error("cannot write " + path);
+    for (int b : part) std::fprintf(f, "%d\n", b);
+    std::fclose(f);
+}
+bool read_partition(const std::string& path, int nCells, std::vector<int>& part) {
+    FILE* f = std::fopen(path.c_str(), "r");
+    if (!f) return false;
+    part.clear();
+    int b;
+    while (std::fscanf(f, "%d", &b) == 1) part.push_back(b);
+    std::fclose(f);
+    // the reference aborts on fewer/more lines than cells (mpas_block_decomp.F:131-144)
+    return (int)part.size() == nCells;
+}
+
+}  // namespace mpas
