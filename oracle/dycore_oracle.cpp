@@ -1,0 +1,1210 @@
+// CPU ORACLE -- TEST INFRASTRUCTURE ONLY.
+// Plain C++ restatement of the MPAS-Atmosphere SRK3 dycore loops of the reference file
+// TI = /root/reference/src/core_atmosphere/dynamics/mpas_atm_time_integration.F, loop for loop,
+// same operation order (compile with -O2 -ffp-contract=off, no re-association), 1-based index
+// semantics kept through the IX macros.  Only tests/, __graft_entry__.smoke() and the
+// cpu_baseline / --impl reference legs of bench.py may load this library; the product
+// (libmpas_b200.so) never links or calls it.
+//
+// PARITY STATUS: "parity unpinned" by the reference's own tests -- the reference ships no
+// atmosphere test, golden vector or fixture and cannot be compiled here (no
+// Fortran/MPI/netCDF).  The oracle is pinned instead by analytic invariants
+// (tests/test_oracle_invariants.py) and by the committed golden fixtures it generated
+// (tests/golden/, script tests/golden/make_golden.py).
+#include <algorithm>
+#include <cmath>
+#include <cstddef>
+#include <cstring>
+#include <vector>
+
+#include "../include/mpas_b200_args.h"
+
+typedef mpas_real real;
+
+#define IX2(k, i, ld) ((size_t)((i)-1) * (size_t)(ld) + (size_t)((k)-1))
+#define IX3(a, b, i, la, lb) (((size_t)((i)-1) * (size_t)(lb) + (size_t)((b)-1)) * (size_t)(la) + (size_t)((a)-1))
+
+namespace {
+// src/framework/mpas_constants.F:25-36
+const real gravity = 9.80616, rgas = 287.0, cp = 7. * rgas / 2., cv = cp - rgas, prandtl = 1.0, rvord = 461.6 / 287.0;
+const int nRelaxZone = 5, nSpecZone = 2;  // mpas_atm_boundaries.F:19-20
+const bool config_apply_lbcs = false;
+inline real fsign(real a, real b) { return std::signbit(b) ? -std::fabs(a) : std::fabs(a); }  // Fortran sign(a,b)
+inline real flux4(real q_im2, real q_im1, real q_i, real q_ip1, real ua) {  // TI:4655
+    return ua * (7. * (q_i + q_im1) - (q_ip1 + q_im2)) / 12.0;
+}
+inline real flux3(real q_im2, real q_im1, real q_i, real q_ip1, real ua, real coef3) {  // TI:4658
+    return flux4(q_im2, q_im1, q_i, q_ip1, ua) + coef3 * std::fabs(ua) * ((q_ip1 - q_im2) - 3. * (q_i - q_im1)) / 12.0;
+}
+}  // namespace
+
+extern "C" {
+
+// ------------------------------------------------------------------ TI:1799-1859
+int oracle_rk_integration_setup(MPAS_RKSETUP_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, ns = num_scalars;
+    for (int e = edgeStart; e <= edgeEnd; ++e)
+        for (int k = 1; k <= L; ++k) { ru_save[IX2(k, e, L)] = ru[IX2(k, e, L)]; u_2[IX2(k, e, L)] = u_1[IX2(k, e, L)]; }
+    for (int c = cellStart; c <= cellEnd; ++c) {
+        for (int k = 1; k <= L1; ++k) { rw_save[IX2(k, c, L1)] = rw[IX2(k, c, L1)]; w_2[IX2(k, c, L1)] = w_1[IX2(k, c, L1)]; }
+        for (int k = 1; k <= L; ++k) {
+            rtheta_p_save[IX2(k, c, L)] = rtheta_p[IX2(k, c, L)];
+            rho_p_save[IX2(k, c, L)] = rho_p[IX2(k, c, L)];
+            theta_m_2[IX2(k, c, L)] = theta_m_1[IX2(k, c, L)];
+            rho_zz_2[IX2(k, c, L)] = rho_zz_1[IX2(k, c, L)];
+            rho_zz_old_split[IX2(k, c, L)] = rho_zz_1[IX2(k, c, L)];
+            for (int q = 1; q <= ns; ++q) scalars_2[IX3(q, k, c, ns, L)] = scalars_1[IX3(q, k, c, ns, L)];
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:1862-1933
+int oracle_compute_moist_coefficients(MPAS_MOIST_ARGS) {
+    const int L = nVertLevels, ns = num_scalars;
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        for (int k = 1; k <= L; ++k) {
+            qtot[IX2(k, iCell, L)] = 0.0;
+            for (int iq = moist_start; iq <= moist_end; ++iq) qtot[IX2(k, iCell, L)] = qtot[IX2(k, iCell, L)] + scalars[IX3(iq, k, iCell, ns, L)];
+        }
+        for (int k = 2; k <= L; ++k) {
+            real qtotal = 0.5 * (qtot[IX2(k, iCell, L)] + qtot[IX2(k - 1, iCell, L)]);
+            cqw[IX2(k, iCell, L)] = 1.0 / (1.0 + qtotal);
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+        int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+        if (cell1 <= nCellsSolve || cell2 <= nCellsSolve) {
+            for (int k = 1; k <= L; ++k) {
+                real qtotal = 0.0;
+                for (int iq = moist_start; iq <= moist_end; ++iq)
+                    qtotal = qtotal + 0.5 * (scalars[IX3(iq, k, cell1, ns, L)] + scalars[IX3(iq, k, cell2, ns, L)]);
+                cqu[IX2(k, iEdge, L)] = 1.0 / (1.0 + qtotal);
+            }
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:2012-2131
+int oracle_compute_vert_imp_coefs_work(MPAS_VERTIMP_ARGS) {
+    const int L = nVertLevels, L1 = L + 1;
+    real dtseps = .5 * dts * (1. + epssm);
+    real rcv = rgas / (cp - rgas);
+    real c2 = cp * rcv;
+    for (int k = 1; k <= L; ++k) cofrz[k - 1] = dtseps * rdzw[k - 1];
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        std::vector<real> b_tri(L + 1), c_tri(L + 1);
+        for (int k = 2; k <= L; ++k)
+            cofwr[IX2(k, iCell, L)] = .5 * dtseps * gravity * (fzm[k - 1] * zz[IX2(k, iCell, L)] + fzp[k - 1] * zz[IX2(k - 1, iCell, L)]);
+        coftz[IX2(1, iCell, L1)] = 0.0;
+        for (int k = 2; k <= L; ++k) {
+            cofwz[IX2(k, iCell, L)] = dtseps * c2 * (fzm[k - 1] * zz[IX2(k, iCell, L)] + fzp[k - 1] * zz[IX2(k - 1, iCell, L)]) * rdzu[k - 1] *
+                                      cqw[IX2(k, iCell, L)] * (fzm[k - 1] * p[IX2(k, iCell, L)] + fzp[k - 1] * p[IX2(k - 1, iCell, L)]);
+            coftz[IX2(k, iCell, L1)] = dtseps * (fzm[k - 1] * t[IX2(k, iCell, L)] + fzp[k - 1] * t[IX2(k - 1, iCell, L)]);
+        }
+        coftz[IX2(L + 1, iCell, L1)] = 0.0;
+        for (int k = 1; k <= L; ++k) {
+            real qtotal = qtot[IX2(k, iCell, L)];
+            cofwt[IX2(k, iCell, L)] = .5 * dtseps * rcv * zz[IX2(k, iCell, L)] * gravity * rb[IX2(k, iCell, L)] / (1. + qtotal) * p[IX2(k, iCell, L)] /
+                                      ((rtb[IX2(k, iCell, L)] + rt[IX2(k, iCell, L)]) * pb[IX2(k, iCell, L)]);
+        }
+        a_tri[IX2(1, iCell, L)] = 0.;
+        b_tri[1] = 1.;
+        c_tri[1] = 0.;
+        gamma_tri[IX2(1, iCell, L)] = 0.;
+        alpha_tri[IX2(1, iCell, L)] = 0.;
+        for (int k = 2; k <= L; ++k) {
+            a_tri[IX2(k, iCell, L)] = -cofwz[IX2(k, iCell, L)] * coftz[IX2(k - 1, iCell, L1)] * rdzw[k - 2] * zz[IX2(k - 1, iCell, L)] +
+                                      cofwr[IX2(k, iCell, L)] * cofrz[k - 2] - cofwt[IX2(k - 1, iCell, L)] * coftz[IX2(k - 1, iCell, L1)] * rdzw[k - 2];
+            b_tri[k] = 1. +
+                       cofwz[IX2(k, iCell, L)] * (coftz[IX2(k, iCell, L1)] * rdzw[k - 1] * zz[IX2(k, iCell, L)] +
+                                                  coftz[IX2(k, iCell, L1)] * rdzw[k - 2] * zz[IX2(k - 1, iCell, L)]) -
+                       coftz[IX2(k, iCell, L1)] * (cofwt[IX2(k, iCell, L)] * rdzw[k - 1] - cofwt[IX2(k - 1, iCell, L)] * rdzw[k - 2]) +
+                       cofwr[IX2(k, iCell, L)] * (cofrz[k - 1] - cofrz[k - 2]);
+            c_tri[k] = -cofwz[IX2(k, iCell, L)] * coftz[IX2(k + 1, iCell, L1)] * rdzw[k - 1] * zz[IX2(k, iCell, L)] - cofwr[IX2(k, iCell, L)] * cofrz[k - 1] +
+                       cofwt[IX2(k, iCell, L)] * coftz[IX2(k + 1, iCell, L1)] * rdzw[k - 1];
+        }
+        for (int k = 2; k <= L; ++k) {
+            alpha_tri[IX2(k, iCell, L)] = 1. / (b_tri[k] - a_tri[IX2(k, iCell, L)] * gamma_tri[IX2(k - 1, iCell, L)]);
+            gamma_tri[IX2(k, iCell, L)] = c_tri[k] * alpha_tri[IX2(k, iCell, L)];
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:2224-2309
+int oracle_set_smlstep_pert_variables_work(MPAS_SMLSTEP_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, mE = maxEdges;
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        if (bdyMaskCell[iCell - 1] <= nRelaxZone) {
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                for (int k = 2; k <= L; ++k) {
+                    real flux = edgesOnCell_sign[IX2(i, iCell, mE)] * (fzm[k - 1] * u_tend[IX2(k, iEdge, L)] + fzp[k - 1] * u_tend[IX2(k - 1, iEdge, L)]);
+                    w_tend[IX2(k, iCell, L1)] = w_tend[IX2(k, iCell, L1)] -
+                                                (zb_cell[IX3(k, i, iCell, L1, mE)] + fsign(1.0, u_tend[IX2(k, iEdge, L)]) * zb3_cell[IX3(k, i, iCell, L1, mE)]) * flux;
+                }
+            }
+            for (int k = 2; k <= L; ++k)
+                w_tend[IX2(k, iCell, L1)] = (fzm[k - 1] * zz[IX2(k, iCell, L)] + fzp[k - 1] * zz[IX2(k - 1, iCell, L)]) * w_tend[IX2(k, iCell, L1)];
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:2447-2723
+int oracle_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, mE = maxEdges;
+    real rcv = rgas / (cp - rgas);
+    real c2 = cp * rcv;
+    real resm = (1.0 - epssm) / (1.0 + epssm);
+    if (small_step != 1) {
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+            if (cell1 <= nCellsSolve || cell2 <= nCellsSolve) {
+                for (int k = 1; k <= L; ++k) {
+                    real pgrad = ((rtheta_pp[IX2(k, cell2, L)] - rtheta_pp[IX2(k, cell1, L)]) * invDcEdge[iEdge - 1]) / (.5 * (zz[IX2(k, cell2, L)] + zz[IX2(k, cell1, L)]));
+                    pgrad = cqu[IX2(k, iEdge, L)] * 0.5 * c2 * (exner[IX2(k, cell1, L)] + exner[IX2(k, cell2, L)]) * pgrad;
+                    pgrad = pgrad + 0.5 * zxu[IX2(k, iEdge, L)] * gravity * (rho_pp[IX2(k, cell1, L)] + rho_pp[IX2(k, cell2, L)]);
+                    ru_p[IX2(k, iEdge, L)] = ru_p[IX2(k, iEdge, L)] + dts * (tend_ru[IX2(k, iEdge, L)] - (1.0 - specZoneMaskEdge[iEdge - 1]) * pgrad);
+                }
+                for (int k = 1; k <= L; ++k) ruAvg[IX2(k, iEdge, L)] = ruAvg[IX2(k, iEdge, L)] + ru_p[IX2(k, iEdge, L)];
+            }
+        }
+    } else {
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+            if (cell1 <= nCellsSolve || cell2 <= nCellsSolve) {
+                for (int k = 1; k <= L; ++k) ru_p[IX2(k, iEdge, L)] = dts * tend_ru[IX2(k, iEdge, L)];
+                for (int k = 1; k <= L; ++k) ruAvg[IX2(k, iEdge, L)] = ru_p[IX2(k, iEdge, L)];
+            }
+        }
+    }
+    if (small_step == 1) {
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+            for (int k = 1; k <= L; ++k) rtheta_pp_old[IX2(k, iCell, L)] = 0.0;
+    } else {
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+            for (int k = 1; k <= L; ++k) rtheta_pp_old[IX2(k, iCell, L)] = rtheta_pp[IX2(k, iCell, L)];
+    }
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        std::vector<real> ts(L + 1), rs(L + 1);
+        if (small_step == 1) {
+            for (int k = 1; k <= L1; ++k) wwAvg[IX2(k, iCell, L1)] = 0.0;
+            for (int k = 1; k <= L; ++k) rho_pp[IX2(k, iCell, L)] = 0.0;
+            for (int k = 1; k <= L; ++k) rtheta_pp[IX2(k, iCell, L)] = 0.0;
+            for (int k = 1; k <= L1; ++k) rw_p[IX2(k, iCell, L1)] = 0.0;
+        }
+        if (specZoneMaskCell[iCell - 1] == 0.0) {
+            for (int k = 1; k <= L; ++k) { ts[k] = 0.0; rs[k] = 0.0; }
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                for (int k = 1; k <= L; ++k) {
+                    real flux = edgesOnCell_sign[IX2(i, iCell, mE)] * dts * dvEdge[iEdge - 1] * ru_p[IX2(k, iEdge, L)] * invAreaCell[iCell - 1];
+                    rs[k] = rs[k] - flux;
+                    ts[k] = ts[k] - flux * 0.5 * (theta_m[IX2(k, cell2, L)] + theta_m[IX2(k, cell1, L)]);
+                }
+            }
+            for (int k = 1; k <= L; ++k) {
+                rs[k] = rho_pp[IX2(k, iCell, L)] + dts * tend_rho[IX2(k, iCell, L)] + rs[k] -
+                        cofrz[k - 1] * resm * (rw_p[IX2(k + 1, iCell, L1)] - rw_p[IX2(k, iCell, L1)]);
+                ts[k] = rtheta_pp[IX2(k, iCell, L)] + dts * tend_rt[IX2(k, iCell, L)] + ts[k] -
+                        resm * rdzw[k - 1] * (coftz[IX2(k + 1, iCell, L1)] * rw_p[IX2(k + 1, iCell, L1)] - coftz[IX2(k, iCell, L1)] * rw_p[IX2(k, iCell, L1)]);
+            }
+            for (int k = 2; k <= L; ++k) wwAvg[IX2(k, iCell, L1)] = wwAvg[IX2(k, iCell, L1)] + 0.5 * (1.0 - epssm) * rw_p[IX2(k, iCell, L1)];
+            for (int k = 2; k <= L; ++k) {
+                rw_p[IX2(k, iCell, L1)] =
+                    rw_p[IX2(k, iCell, L1)] + dts * tend_rw[IX2(k, iCell, L1)] -
+                    cofwz[IX2(k, iCell, L)] * ((zz[IX2(k, iCell, L)] * ts[k] - zz[IX2(k - 1, iCell, L)] * ts[k - 1]) +
+                                               resm * (zz[IX2(k, iCell, L)] * rtheta_pp[IX2(k, iCell, L)] - zz[IX2(k - 1, iCell, L)] * rtheta_pp[IX2(k - 1, iCell, L)])) -
+                    cofwr[IX2(k, iCell, L)] * ((rs[k] + rs[k - 1]) + resm * (rho_pp[IX2(k, iCell, L)] + rho_pp[IX2(k - 1, iCell, L)])) +
+                    cofwt[IX2(k, iCell, L)] * (ts[k] + resm * rtheta_pp[IX2(k, iCell, L)]) +
+                    cofwt[IX2(k - 1, iCell, L)] * (ts[k - 1] + resm * rtheta_pp[IX2(k - 1, iCell, L)]);
+            }
+            for (int k = 2; k <= L; ++k)
+                rw_p[IX2(k, iCell, L1)] = (rw_p[IX2(k, iCell, L1)] - a_tri[IX2(k, iCell, L)] * rw_p[IX2(k - 1, iCell, L1)]) * alpha_tri[IX2(k, iCell, L)];
+            for (int k = L; k >= 1; --k)
+                rw_p[IX2(k, iCell, L1)] = rw_p[IX2(k, iCell, L1)] - gamma_tri[IX2(k, iCell, L)] * rw_p[IX2(k + 1, iCell, L1)];
+            for (int k = 2; k <= L; ++k) {
+                rw_p[IX2(k, iCell, L1)] =
+                    (rw_p[IX2(k, iCell, L1)] + (rw_save[IX2(k, iCell, L1)] - rw[IX2(k, iCell, L1)]) -
+                     dts * dss[IX2(k, iCell, L)] * (fzm[k - 1] * zz[IX2(k, iCell, L)] + fzp[k - 1] * zz[IX2(k - 1, iCell, L)]) *
+                         (fzm[k - 1] * rho_zz[IX2(k, iCell, L)] + fzp[k - 1] * rho_zz[IX2(k - 1, iCell, L)]) * w[IX2(k, iCell, L1)]) /
+                        (1.0 + dts * dss[IX2(k, iCell, L)]) -
+                    (rw_save[IX2(k, iCell, L1)] - rw[IX2(k, iCell, L1)]);
+            }
+            for (int k = 2; k <= L; ++k) wwAvg[IX2(k, iCell, L1)] = wwAvg[IX2(k, iCell, L1)] + 0.5 * (1.0 + epssm) * rw_p[IX2(k, iCell, L1)];
+            for (int k = 1; k <= L; ++k) {
+                rho_pp[IX2(k, iCell, L)] = rs[k] - cofrz[k - 1] * (rw_p[IX2(k + 1, iCell, L1)] - rw_p[IX2(k, iCell, L1)]);
+                rtheta_pp[IX2(k, iCell, L)] =
+                    ts[k] - rdzw[k - 1] * (coftz[IX2(k + 1, iCell, L1)] * rw_p[IX2(k + 1, iCell, L1)] - coftz[IX2(k, iCell, L1)] * rw_p[IX2(k, iCell, L1)]);
+            }
+        } else {
+            for (int k = 1; k <= L; ++k) {
+                rho_pp[IX2(k, iCell, L)] = rho_pp[IX2(k, iCell, L)] + dts * tend_rho[IX2(k, iCell, L)];
+                rtheta_pp[IX2(k, iCell, L)] = rtheta_pp[IX2(k, iCell, L)] + dts * tend_rt[IX2(k, iCell, L)];
+                rw_p[IX2(k, iCell, L1)] = rw_p[IX2(k, iCell, L1)] + dts * tend_rw[IX2(k, iCell, L1)];
+                wwAvg[IX2(k, iCell, L1)] = wwAvg[IX2(k, iCell, L1)] + 0.5 * (1.0 + epssm) * rw_p[IX2(k, iCell, L1)];
+            }
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:2726-2795
+int oracle_divergence_damping_3d(MPAS_DIVDAMP_ARGS) {
+    const int L = nVertLevels;
+    real rdts = 1.0 / dts;
+    real coef_divdamp = 2.0 * smdiv * config_len_disp * rdts;
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+        int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+        if (cell1 <= nCellsSolve || cell2 <= nCellsSolve) {
+            for (int k = 1; k <= L; ++k) {
+                real divCell1 = -(rtheta_pp[IX2(k, cell1, L)] - rtheta_pp_old[IX2(k, cell1, L)]);
+                real divCell2 = -(rtheta_pp[IX2(k, cell2, L)] - rtheta_pp_old[IX2(k, cell2, L)]);
+                ru_p[IX2(k, iEdge, L)] = ru_p[IX2(k, iEdge, L)] + coef_divdamp * (divCell2 - divCell1) * (1.0 - specZoneMaskEdge[iEdge - 1]) /
+                                                                      (theta_m[IX2(k, cell1, L)] + theta_m[IX2(k, cell2, L)]);
+            }
+        }
+    }
+    return 0;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// ------------------------------------------------------------------ TI:2909-3099
+int oracle_recover_large_step_variables_work(MPAS_RECOVER_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, mE = maxEdges;
+    real rcv = rgas / (cp - rgas);
+    real p0 = 1.0e+05;
+    for (int k = 1; k <= L; ++k) rho_zz[IX2(k, nCells + 1, L)] = 1.0;
+    real invNs = 1 / (real)ns;
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        for (int k = 1; k <= L; ++k) {
+            rho_p[IX2(k, iCell, L)] = rho_p_save[IX2(k, iCell, L)] + rho_pp[IX2(k, iCell, L)];
+            rho_zz[IX2(k, iCell, L)] = rho_p[IX2(k, iCell, L)] + rho_base[IX2(k, iCell, L)];
+        }
+        w[IX2(1, iCell, L1)] = 0.0;
+        for (int k = 2; k <= L; ++k) {
+            wwAvg[IX2(k, iCell, L1)] = rw_save[IX2(k, iCell, L1)] + (wwAvg[IX2(k, iCell, L1)] * invNs);
+            rw[IX2(k, iCell, L1)] = rw_save[IX2(k, iCell, L1)] + rw_p[IX2(k, iCell, L1)];
+            w[IX2(k, iCell, L1)] = rw[IX2(k, iCell, L1)] / (fzm[k - 1] * zz[IX2(k, iCell, L)] + fzp[k - 1] * zz[IX2(k - 1, iCell, L)]);
+        }
+        w[IX2(L + 1, iCell, L1)] = 0.0;
+        if (rk_step == 3) {
+            for (int k = 1; k <= L; ++k) {
+                rtheta_p[IX2(k, iCell, L)] = rtheta_p_save[IX2(k, iCell, L)] + rtheta_pp[IX2(k, iCell, L)] -
+                                             dt * rho_zz[IX2(k, iCell, L)] * (rt_diabatic_tend ? rt_diabatic_tend[IX2(k, iCell, L)] : 0.0);
+                theta_m[IX2(k, iCell, L)] = (rtheta_p[IX2(k, iCell, L)] + rtheta_base[IX2(k, iCell, L)]) / rho_zz[IX2(k, iCell, L)];
+                exner[IX2(k, iCell, L)] = std::pow(zz[IX2(k, iCell, L)] * (rgas / p0) * (rtheta_p[IX2(k, iCell, L)] + rtheta_base[IX2(k, iCell, L)]), rcv);
+                pressure_p[IX2(k, iCell, L)] = zz[IX2(k, iCell, L)] * rgas *
+                                               (exner[IX2(k, iCell, L)] * rtheta_p[IX2(k, iCell, L)] +
+                                                rtheta_base[IX2(k, iCell, L)] * (exner[IX2(k, iCell, L)] - exner_base[IX2(k, iCell, L)]));
+            }
+        } else {
+            for (int k = 1; k <= L; ++k) {
+                rtheta_p[IX2(k, iCell, L)] = rtheta_p_save[IX2(k, iCell, L)] + rtheta_pp[IX2(k, iCell, L)];
+                theta_m[IX2(k, iCell, L)] = (rtheta_p[IX2(k, iCell, L)] + rtheta_base[IX2(k, iCell, L)]) / rho_zz[IX2(k, iCell, L)];
+            }
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+        int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+        for (int k = 1; k <= L; ++k) {
+            ruAvg[IX2(k, iEdge, L)] = ru_save[IX2(k, iEdge, L)] + (ruAvg[IX2(k, iEdge, L)] * invNs);
+            ru[IX2(k, iEdge, L)] = ru_save[IX2(k, iEdge, L)] + ru_p[IX2(k, iEdge, L)];
+            u[IX2(k, iEdge, L)] = 2. * ru[IX2(k, iEdge, L)] / (rho_zz[IX2(k, cell1, L)] + rho_zz[IX2(k, cell2, L)]);
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        if (bdyMaskCell[iCell - 1] <= nRelaxZone) {
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                real flux = (cf1 * ru[IX2(1, iEdge, L)] + cf2 * ru[IX2(2, iEdge, L)] + cf3 * ru[IX2(3, iEdge, L)]);
+                w[IX2(1, iCell, L1)] = w[IX2(1, iCell, L1)] + edgesOnCell_sign[IX2(i, iCell, mE)] *
+                                                                  (zb_cell[IX3(1, i, iCell, L1, mE)] + fsign(1.0, flux) * zb3_cell[IX3(1, i, iCell, L1, mE)]) * flux;
+                for (int k = 2; k <= L; ++k) {
+                    flux = (fzm[k - 1] * ru[IX2(k, iEdge, L)] + fzp[k - 1] * ru[IX2(k - 1, iEdge, L)]);
+                    w[IX2(k, iCell, L1)] = w[IX2(k, iCell, L1)] + edgesOnCell_sign[IX2(i, iCell, mE)] *
+                                                                      (zb_cell[IX3(k, i, iCell, L1, mE)] + fsign(1.0, flux) * zb3_cell[IX3(k, i, iCell, L1, mE)]) * flux;
+                }
+            }
+            w[IX2(1, iCell, L1)] = w[IX2(1, iCell, L1)] / (cf1 * rho_zz[IX2(1, iCell, L)] + cf2 * rho_zz[IX2(2, iCell, L)] + cf3 * rho_zz[IX2(3, iCell, L)]);
+            for (int k = 2; k <= L; ++k)
+                w[IX2(k, iCell, L1)] = w[IX2(k, iCell, L1)] / (fzm[k - 1] * rho_zz[IX2(k, iCell, L)] + fzp[k - 1] * rho_zz[IX2(k - 1, iCell, L)]);
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:5513-5822
+int oracle_compute_solve_diagnostics_work(MPAS_SOLVEDIAG_ARGS) {
+    const int L = nVertLevels, mE = maxEdges, mE2 = maxEdges2;
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+        int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+        for (int k = 1; k <= L; ++k) h_edge[IX2(k, iEdge, L)] = 0.5 * (h[IX2(k, cell1, L)] + h[IX2(k, cell2, L)]);
+        real efac = dcEdge[iEdge - 1] * dvEdge[iEdge - 1];
+        for (int k = 1; k <= L; ++k) ke_edge[IX2(k, iEdge, L)] = efac * (u[IX2(k, iEdge, L)] * u[IX2(k, iEdge, L)]);
+    }
+#pragma omp parallel for schedule(static)
+    for (int iVertex = vertexStart; iVertex <= vertexEnd; ++iVertex) {
+        for (int k = 1; k <= L; ++k) vorticity[IX2(k, iVertex, L)] = 0.0;
+        for (int i = 1; i <= vertexDegree; ++i) {
+            int iEdge = edgesOnVertex[IX2(i, iVertex, vertexDegree)];
+            real s = edgesOnVertex_sign[IX2(i, iVertex, vertexDegree)] * dcEdge[iEdge - 1];
+            for (int k = 1; k <= L; ++k) vorticity[IX2(k, iVertex, L)] = vorticity[IX2(k, iVertex, L)] + s * u[IX2(k, iEdge, L)];
+        }
+        for (int k = 1; k <= L; ++k) vorticity[IX2(k, iVertex, L)] = vorticity[IX2(k, iVertex, L)] * invAreaTriangle[iVertex - 1];
+    }
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        for (int k = 1; k <= L; ++k) divergence[IX2(k, iCell, L)] = 0.0;
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+            real s = edgesOnCell_sign[IX2(i, iCell, mE)] * dvEdge[iEdge - 1];
+            for (int k = 1; k <= L; ++k) divergence[IX2(k, iCell, L)] = divergence[IX2(k, iCell, L)] + s * u[IX2(k, iEdge, L)];
+        }
+        real r = invAreaCell[iCell - 1];
+        for (int k = 1; k <= L; ++k) divergence[IX2(k, iCell, L)] = divergence[IX2(k, iCell, L)] * r;
+    }
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        for (int k = 1; k <= L; ++k) ke[IX2(k, iCell, L)] = 0.0;
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+            for (int k = 1; k <= L; ++k) ke[IX2(k, iCell, L)] = ke[IX2(k, iCell, L)] + 0.25 * ke_edge[IX2(k, iEdge, L)];
+        }
+        for (int k = 1; k <= L; ++k) ke[IX2(k, iCell, L)] = ke[IX2(k, iCell, L)] * invAreaCell[iCell - 1];
+    }
+    // hollingsworth = .true.
+#pragma omp parallel for schedule(static)
+    for (int iVertex = vertexStart; iVertex <= vertexEnd; ++iVertex) {
+        real r = 0.25 * invAreaTriangle[iVertex - 1];
+        int e1 = edgesOnVertex[IX2(1, iVertex, vertexDegree)], e2 = edgesOnVertex[IX2(2, iVertex, vertexDegree)], e3 = edgesOnVertex[IX2(3, iVertex, vertexDegree)];
+        for (int k = 1; k <= L; ++k) ke_vertex[IX2(k, iVertex, L)] = (ke_edge[IX2(k, e1, L)] + ke_edge[IX2(k, e2, L)] + ke_edge[IX2(k, e3, L)]) * r;
+    }
+    real ke_fact = 1.0 - .375;
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        for (int k = 1; k <= L; ++k) ke[IX2(k, iCell, L)] = ke_fact * ke[IX2(k, iCell, L)];
+        real r = invAreaCell[iCell - 1];
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            int iVertex = verticesOnCell[IX2(i, iCell, mE)];
+            int j = kiteForCell[IX2(i, iCell, mE)];
+            for (int k = 1; k <= L; ++k)
+                ke[IX2(k, iCell, L)] = ke[IX2(k, iCell, L)] + (1. - ke_fact) * kiteAreasOnVertex[IX2(j, iVertex, 3)] * ke_vertex[IX2(k, iVertex, L)] * r;
+        }
+    }
+    bool reconstruct_v = true;
+    if (rk_step >= 0 && rk_step != 3) reconstruct_v = false;
+    if (reconstruct_v) {
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            for (int k = 1; k <= L; ++k) v[IX2(k, iEdge, L)] = 0.0;
+            for (int i = 1; i <= nEdgesOnEdge[iEdge - 1]; ++i) {
+                int eoe = edgesOnEdge[IX2(i, iEdge, mE2)];
+                for (int k = 1; k <= L; ++k) v[IX2(k, iEdge, L)] = v[IX2(k, iEdge, L)] + weightsOnEdge[IX2(i, iEdge, mE2)] * u[IX2(k, eoe, L)];
+            }
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int iVertex = vertexStart; iVertex <= vertexEnd; ++iVertex)
+        for (int k = 1; k <= L; ++k) pv_vertex[IX2(k, iVertex, L)] = (fVertex[iVertex - 1] + vorticity[IX2(k, iVertex, L)]);
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+        int v1 = verticesOnEdge[IX2(1, iEdge, 2)], v2 = verticesOnEdge[IX2(2, iEdge, 2)];
+        for (int k = 1; k <= L; ++k) pv_edge[IX2(k, iEdge, L)] = 0.5 * (pv_vertex[IX2(k, v1, L)] + pv_vertex[IX2(k, v2, L)]);
+    }
+    if (config_apvm_upwinding > 0.0) {
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+            for (int k = 1; k <= L; ++k) pv_cell[IX2(k, iCell, L)] = 0.0;
+            real r = invAreaCell[iCell - 1];
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iVertex = verticesOnCell[IX2(i, iCell, mE)];
+                int j = kiteForCell[IX2(i, iCell, mE)];
+                for (int k = 1; k <= L; ++k)
+                    pv_cell[IX2(k, iCell, L)] = pv_cell[IX2(k, iCell, L)] + kiteAreasOnVertex[IX2(j, iVertex, 3)] * pv_vertex[IX2(k, iVertex, L)] * r;
+            }
+        }
+        real r = config_apvm_upwinding * dt;
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            real r1 = 1.0 * invDvEdge[iEdge - 1], r2 = 1.0 * invDcEdge[iEdge - 1];
+            int v1 = verticesOnEdge[IX2(1, iEdge, 2)], v2 = verticesOnEdge[IX2(2, iEdge, 2)];
+            int c1 = cellsOnEdge[IX2(1, iEdge, 2)], c2 = cellsOnEdge[IX2(2, iEdge, 2)];
+            for (int k = 1; k <= L; ++k) {
+                real gt = (pv_vertex[IX2(k, v2, L)] - pv_vertex[IX2(k, v1, L)]) * r1;
+                real gn = (pv_cell[IX2(k, c2, L)] - pv_cell[IX2(k, c1, L)]) * r2;
+                if (gradPVt) gradPVt[IX2(k, iEdge, L)] = gt;
+                if (gradPVn) gradPVn[IX2(k, iEdge, L)] = gn;
+                pv_edge[IX2(k, iEdge, L)] = pv_edge[IX2(k, iEdge, L)] - r * (v[IX2(k, iEdge, L)] * gt + u[IX2(k, iEdge, L)] * gn);
+            }
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:5825-5990
+int oracle_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, mE = maxEdges, ns = num_scalars;
+    real rcv = rgas / (cp - rgas);
+    real p0 = 1.e5;
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+        for (int k = 1; k <= L; ++k) {
+            theta_m[IX2(k, iCell, L)] = theta[IX2(k, iCell, L)] * (1. + rvord * scalars[IX3(index_qv, k, iCell, ns, L)]);
+            rho_zz[IX2(k, iCell, L)] = rho[IX2(k, iCell, L)] / zz[IX2(k, iCell, L)];
+        }
+    for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+        int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+        for (int k = 1; k <= L; ++k) ru[IX2(k, iEdge, L)] = 0.5 * u[IX2(k, iEdge, L)] * (rho_zz[IX2(k, cell1, L)] + rho_zz[IX2(k, cell2, L)]);
+    }
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        rw[IX2(1, iCell, L1)] = 0.0;
+        rw[IX2(L + 1, iCell, L1)] = 0.0;
+        for (int k = 2; k <= L; ++k)
+            rw[IX2(k, iCell, L1)] = w[IX2(k, iCell, L1)] * (fzp[k - 1] * rho_zz[IX2(k - 1, iCell, L)] + fzm[k - 1] * rho_zz[IX2(k, iCell, L)]) *
+                                    (fzp[k - 1] * zz[IX2(k - 1, iCell, L)] + fzm[k - 1] * zz[IX2(k, iCell, L)]);
+    }
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+            for (int k = 2; k <= L; ++k) {
+                real flux = (fzm[k - 1] * ru[IX2(k, iEdge, L)] + fzp[k - 1] * ru[IX2(k - 1, iEdge, L)]);
+                rw[IX2(k, iCell, L1)] = rw[IX2(k, iCell, L1)] -
+                                        edgesOnCell_sign[IX2(i, iCell, mE)] * (zb_cell[IX3(k, i, iCell, L1, mE)] + fsign(1.0, flux) * zb3_cell[IX3(k, i, iCell, L1, mE)]) * flux *
+                                            (fzp[k - 1] * zz[IX2(k - 1, iCell, L)] + fzm[k - 1] * zz[IX2(k, iCell, L)]);
+            }
+        }
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+        for (int k = 1; k <= L; ++k) {
+            rho_p[IX2(k, iCell, L)] = rho_zz[IX2(k, iCell, L)] - rho_base[IX2(k, iCell, L)];
+            rtheta_base[IX2(k, iCell, L)] = theta_base[IX2(k, iCell, L)] * rho_base[IX2(k, iCell, L)];
+            rtheta_p[IX2(k, iCell, L)] = theta_m[IX2(k, iCell, L)] * rho_p[IX2(k, iCell, L)] + rho_base[IX2(k, iCell, L)] * (theta_m[IX2(k, iCell, L)] - theta_base[IX2(k, iCell, L)]);
+            exner[IX2(k, iCell, L)] = std::pow(zz[IX2(k, iCell, L)] * (rgas / p0) * (rtheta_p[IX2(k, iCell, L)] + rtheta_base[IX2(k, iCell, L)]), rcv);
+            exner_base[IX2(k, iCell, L)] = std::pow(zz[IX2(k, iCell, L)] * (rgas / p0) * (rtheta_base[IX2(k, iCell, L)]), rcv);
+            pressure_p[IX2(k, iCell, L)] = zz[IX2(k, iCell, L)] * rgas *
+                                           (exner[IX2(k, iCell, L)] * rtheta_p[IX2(k, iCell, L)] + rtheta_base[IX2(k, iCell, L)] * (exner[IX2(k, iCell, L)] - exner_base[IX2(k, iCell, L)]));
+            pressure_base[IX2(k, iCell, L)] = zz[IX2(k, iCell, L)] * rgas * exner_base[IX2(k, iCell, L)] * rtheta_base[IX2(k, iCell, L)];
+        }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:5993-6081
+int oracle_rk_dynamics_substep_finish(MPAS_SUBSTEPFINISH_ARGS) {
+    const int L = nVertLevels, L1 = L + 1;
+    real inv_dynamics_split = 1.0 / (real)dynamics_split;
+    if (dynamics_substep < dynamics_split) {
+        for (int e = edgeStart; e <= edgeEnd; ++e)
+            for (int k = 1; k <= L; ++k) { ru_save[IX2(k, e, L)] = ru[IX2(k, e, L)]; u_1[IX2(k, e, L)] = u_2[IX2(k, e, L)]; }
+        for (int c = cellStart; c <= cellEnd; ++c) {
+            for (int k = 1; k <= L1; ++k) { rw_save[IX2(k, c, L1)] = rw[IX2(k, c, L1)]; w_1[IX2(k, c, L1)] = w_2[IX2(k, c, L1)]; }
+            for (int k = 1; k <= L; ++k) {
+                rtheta_p_save[IX2(k, c, L)] = rtheta_p[IX2(k, c, L)];
+                rho_p_save[IX2(k, c, L)] = rho_p[IX2(k, c, L)];
+                theta_m_1[IX2(k, c, L)] = theta_m_2[IX2(k, c, L)];
+                rho_zz_1[IX2(k, c, L)] = rho_zz_2[IX2(k, c, L)];
+            }
+        }
+    }
+    if (dynamics_substep == 1) {
+        for (int e = edgeStart; e <= edgeEnd; ++e)
+            for (int k = 1; k <= L; ++k) ruAvg_split[IX2(k, e, L)] = ruAvg[IX2(k, e, L)];
+        for (int c = cellStart; c <= cellEnd; ++c)
+            for (int k = 1; k <= L1; ++k) wwAvg_split[IX2(k, c, L1)] = wwAvg[IX2(k, c, L1)];
+    } else {
+        for (int e = edgeStart; e <= edgeEnd; ++e)
+            for (int k = 1; k <= L; ++k) ruAvg_split[IX2(k, e, L)] = ruAvg[IX2(k, e, L)] + ruAvg_split[IX2(k, e, L)];
+        for (int c = cellStart; c <= cellEnd; ++c)
+            for (int k = 1; k <= L1; ++k) wwAvg_split[IX2(k, c, L1)] = wwAvg[IX2(k, c, L1)] + wwAvg_split[IX2(k, c, L1)];
+    }
+    if (dynamics_substep == dynamics_split) {
+        for (int e = edgeStart; e <= edgeEnd; ++e)
+            for (int k = 1; k <= L; ++k) ruAvg[IX2(k, e, L)] = ruAvg_split[IX2(k, e, L)] * inv_dynamics_split;
+        for (int c = cellStart; c <= cellEnd; ++c) {
+            for (int k = 1; k <= L1; ++k) wwAvg[IX2(k, c, L1)] = wwAvg_split[IX2(k, c, L1)] * inv_dynamics_split;
+            for (int k = 1; k <= L; ++k) rho_zz_1[IX2(k, c, L)] = rho_zz_old_split[IX2(k, c, L)];
+        }
+    }
+    return 0;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// ------------------------------------------------------------------ TI:4481-5416
+int oracle_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, mE = maxEdges, mE2 = maxEdges2, vD = vertexDegree;
+    (void)num_scalars; (void)moist_start; (void)moist_end; (void)nVertices; (void)nEdgesSolve; (void)r_earth;
+    real prandtl_inv = 1.0 / prandtl;
+    real invDt = 1.0 / dt;
+    real v_mom_eddy_visc2 = config_v_mom_eddy_visc2;
+    real v_theta_eddy_visc2 = config_v_theta_eddy_visc2;
+    real h_mom_eddy_visc4 = 0.0, h_theta_eddy_visc4 = 0.0;
+
+    if (rk_step == 1) {
+        if (config_horiz_mixing == 1) {  // "2d_smagorinsky", TI:4677-4698
+#pragma omp parallel for schedule(static)
+            for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+                std::vector<real> d_diag(L + 1, 0.0), d_off_diag(L + 1, 0.0);
+                for (int iEdge = 1; iEdge <= nEdgesOnCell[iCell - 1]; ++iEdge) {
+                    int e = edgesOnCell[IX2(iEdge, iCell, mE)];
+                    for (int k = 1; k <= L; ++k) {
+                        d_diag[k] = d_diag[k] + defc_a[IX2(iEdge, iCell, mE)] * u[IX2(k, e, L)] - defc_b[IX2(iEdge, iCell, mE)] * v[IX2(k, e, L)];
+                        d_off_diag[k] = d_off_diag[k] + defc_b[IX2(iEdge, iCell, mE)] * u[IX2(k, e, L)] + defc_a[IX2(iEdge, iCell, mE)] * v[IX2(k, e, L)];
+                    }
+                }
+                for (int k = 1; k <= L; ++k) {
+                    real cl = (c_s * config_len_disp);
+                    kdiff[IX2(k, iCell, L)] = std::min((cl * cl) * std::sqrt(d_diag[k] * d_diag[k] + d_off_diag[k] * d_off_diag[k]),
+                                                       (0.01 * (config_len_disp * config_len_disp)) * invDt);
+                }
+            }
+            h_mom_eddy_visc4 = config_visc4_2dsmag * (config_len_disp * config_len_disp * config_len_disp);
+            h_theta_eddy_visc4 = h_mom_eddy_visc4;
+        } else if (config_horiz_mixing == 2) {  // "2d_fixed"
+            for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+                for (int k = 1; k <= L; ++k) kdiff[IX2(k, iCell, L)] = config_h_theta_eddy_visc2;
+            h_mom_eddy_visc4 = config_h_mom_eddy_visc4;
+            h_theta_eddy_visc4 = config_h_theta_eddy_visc4;
+        }
+        if (config_mpas_cam_coef > 0.0) {
+            for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+                kdiff[IX2(L - 2, iCell, L)] = std::max(kdiff[IX2(L - 2, iCell, L)], 2.0833 * config_len_disp * config_mpas_cam_coef);
+                kdiff[IX2(L - 1, iCell, L)] = std::max(kdiff[IX2(L - 1, iCell, L)], 2.0 * 2.0833 * config_len_disp * config_mpas_cam_coef);
+                kdiff[IX2(L, iCell, L)] = std::max(kdiff[IX2(L, iCell, L)], 4.0 * 2.0833 * config_len_disp * config_mpas_cam_coef);
+            }
+        }
+    }
+
+    // horizontal mass-flux divergence, TI:4729-4748
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+        for (int k = 1; k <= L; ++k) h_divergence[IX2(k, iCell, L)] = 0.0;
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+            real edge_sign = edgesOnCell_sign[IX2(i, iCell, mE)] * dvEdge[iEdge - 1];
+            for (int k = 1; k <= L; ++k) h_divergence[IX2(k, iCell, L)] = h_divergence[IX2(k, iCell, L)] + edge_sign * ru[IX2(k, iEdge, L)];
+        }
+        real r = invAreaCell[iCell - 1];
+        for (int k = 1; k <= L; ++k) h_divergence[IX2(k, iCell, L)] = h_divergence[IX2(k, iCell, L)] * r;
+    }
+    if (rk_step == 1) {  // TI:4755-4766
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+            for (int k = 1; k <= L; ++k) {
+                tend_rho[IX2(k, iCell, L)] = -h_divergence[IX2(k, iCell, L)] - rdzw[k - 1] * (rw[IX2(k + 1, iCell, L1)] - rw[IX2(k, iCell, L1)]) +
+                                             (tend_rho_physics ? tend_rho_physics[IX2(k, iCell, L)] : 0.0);
+                dpdz[IX2(k, iCell, L)] = -gravity * (rb[IX2(k, iCell, L)] * (qtot[IX2(k, iCell, L)]) + rr_save[IX2(k, iCell, L)] * (1. + qtot[IX2(k, iCell, L)]));
+            }
+    }
+
+    // ---- u tendency, TI:4774-4840
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeSolveStart; iEdge <= edgeSolveEnd; ++iEdge) {
+        std::vector<real> wduz(L + 2), q(L + 1);
+        int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+        if (rk_step == 1) {
+            for (int k = 1; k <= L; ++k)
+                tend_u_euler[IX2(k, iEdge, L)] =
+                    -cqu[IX2(k, iEdge, L)] * ((pp[IX2(k, cell2, L)] - pp[IX2(k, cell1, L)]) * invDcEdge[iEdge - 1] / (.5 * (zz[IX2(k, cell2, L)] + zz[IX2(k, cell1, L)])) -
+                                              0.5 * zxu[IX2(k, iEdge, L)] * (dpdz[IX2(k, cell1, L)] + dpdz[IX2(k, cell2, L)]));
+        }
+        wduz[1] = 0.;
+        int k = 2;
+        wduz[k] = 0.5 * (rw[IX2(k, cell1, L1)] + rw[IX2(k, cell2, L1)]) * (fzm[k - 1] * u[IX2(k, iEdge, L)] + fzp[k - 1] * u[IX2(k - 1, iEdge, L)]);
+        for (k = 3; k <= L - 1; ++k)
+            wduz[k] = flux3(u[IX2(k - 2, iEdge, L)], u[IX2(k - 1, iEdge, L)], u[IX2(k, iEdge, L)], u[IX2(k + 1, iEdge, L)],
+                            0.5 * (rw[IX2(k, cell1, L1)] + rw[IX2(k, cell2, L1)]), 1.0);
+        k = L;
+        wduz[k] = 0.5 * (rw[IX2(k, cell1, L1)] + rw[IX2(k, cell2, L1)]) * (fzm[k - 1] * u[IX2(k, iEdge, L)] + fzp[k - 1] * u[IX2(k - 1, iEdge, L)]);
+        wduz[L + 1] = 0.;
+        for (k = 1; k <= L; ++k) tend_u[IX2(k, iEdge, L)] = -rdzw[k - 1] * (wduz[k + 1] - wduz[k]);
+        for (k = 1; k <= L; ++k) q[k] = 0.0;
+        for (int j = 1; j <= nEdgesOnEdge[iEdge - 1]; ++j) {
+            int eoe = edgesOnEdge[IX2(j, iEdge, mE2)];
+            for (k = 1; k <= L; ++k) {
+                real workpv = 0.5 * (pv_edge[IX2(k, iEdge, L)] + pv_edge[IX2(k, eoe, L)]);
+                q[k] = q[k] + weightsOnEdge[IX2(j, iEdge, mE2)] * u[IX2(k, eoe, L)] * workpv;
+            }
+        }
+        for (k = 1; k <= L; ++k)
+            tend_u[IX2(k, iEdge, L)] = tend_u[IX2(k, iEdge, L)] +
+                                       rho_edge[IX2(k, iEdge, L)] * (q[k] - (ke[IX2(k, cell2, L)] - ke[IX2(k, cell1, L)]) * invDcEdge[iEdge - 1]) -
+                                       u[IX2(k, iEdge, L)] * 0.5 * (h_divergence[IX2(k, cell1, L)] + h_divergence[IX2(k, cell2, L)]);
+    }
+
+    if (rk_step == 1) {  // horizontal mixing for u, TI:4849-5008
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+            int vertex1 = verticesOnEdge[IX2(1, iEdge, 2)], vertex2 = verticesOnEdge[IX2(2, iEdge, 2)];
+            real r_dc = invDcEdge[iEdge - 1];
+            real r_dv = std::min(invDvEdge[iEdge - 1], 4 * invDcEdge[iEdge - 1]);
+            for (int k = 1; k <= L; ++k) {
+                real u_diffusion = (divergence[IX2(k, cell2, L)] - divergence[IX2(k, cell1, L)]) * r_dc -
+                                   (vorticity[IX2(k, vertex2, L)] - vorticity[IX2(k, vertex1, L)]) * r_dv;
+                delsq_u[IX2(k, iEdge, L)] = 0.0 + u_diffusion;
+                real kdiffu = 0.5 * (kdiff[IX2(k, cell1, L)] + kdiff[IX2(k, cell2, L)]);
+                tend_u_euler[IX2(k, iEdge, L)] = tend_u_euler[IX2(k, iEdge, L)] + rho_edge[IX2(k, iEdge, L)] * kdiffu * u_diffusion * meshScalingDel2[iEdge - 1];
+            }
+        }
+        if (h_mom_eddy_visc4 > 0.0) {
+#pragma omp parallel for schedule(static)
+            for (int iVertex = vertexStart; iVertex <= vertexEnd; ++iVertex) {
+                for (int k = 1; k <= L; ++k) delsq_vorticity[IX2(k, iVertex, L)] = 0.0;
+                for (int i = 1; i <= vD; ++i) {
+                    int iEdge = edgesOnVertex[IX2(i, iVertex, vD)];
+                    real edge_sign = invAreaTriangle[iVertex - 1] * dcEdge[iEdge - 1] * edgesOnVertex_sign[IX2(i, iVertex, vD)];
+                    for (int k = 1; k <= L; ++k) delsq_vorticity[IX2(k, iVertex, L)] = delsq_vorticity[IX2(k, iVertex, L)] + edge_sign * delsq_u[IX2(k, iEdge, L)];
+                }
+            }
+#pragma omp parallel for schedule(static)
+            for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+                for (int k = 1; k <= L; ++k) delsq_divergence[IX2(k, iCell, L)] = 0.0;
+                real r = invAreaCell[iCell - 1];
+                for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                    int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                    real edge_sign = r * dvEdge[iEdge - 1] * edgesOnCell_sign[IX2(i, iCell, mE)];
+                    for (int k = 1; k <= L; ++k) delsq_divergence[IX2(k, iCell, L)] = delsq_divergence[IX2(k, iCell, L)] + edge_sign * delsq_u[IX2(k, iEdge, L)];
+                }
+            }
+#pragma omp parallel for schedule(static)
+            for (int iEdge = edgeSolveStart; iEdge <= edgeSolveEnd; ++iEdge) {
+                int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                int vertex1 = verticesOnEdge[IX2(1, iEdge, 2)], vertex2 = verticesOnEdge[IX2(2, iEdge, 2)];
+                real u_mix_scale = meshScalingDel4[iEdge - 1] * h_mom_eddy_visc4;
+                real r_dc = u_mix_scale * config_del4u_div_factor * invDcEdge[iEdge - 1];
+                real r_dv = u_mix_scale * std::min(invDvEdge[iEdge - 1], 4 * invDcEdge[iEdge - 1]);
+                for (int k = 1; k <= L; ++k) {
+                    real u_diffusion = rho_edge[IX2(k, iEdge, L)] * ((delsq_divergence[IX2(k, cell2, L)] - delsq_divergence[IX2(k, cell1, L)]) * r_dc -
+                                                                     (delsq_vorticity[IX2(k, vertex2, L)] - delsq_vorticity[IX2(k, vertex1, L)]) * r_dv);
+                    tend_u_euler[IX2(k, iEdge, L)] = tend_u_euler[IX2(k, iEdge, L)] - u_diffusion;
+                }
+            }
+        }
+        if (v_mom_eddy_visc2 > 0.0) {  // TI:4949-5006
+            for (int iEdge = edgeSolveStart; iEdge <= edgeSolveEnd; ++iEdge) {
+                int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                std::vector<real> u_mix(L + 1);
+                for (int k = 1; k <= L; ++k) {
+                    if (config_mix_full) u_mix[k] = u[IX2(k, iEdge, L)];
+                    else u_mix[k] = u[IX2(k, iEdge, L)] - u_init[k - 1] * std::cos(angleEdge[iEdge - 1]) - v_init[k - 1] * std::sin(angleEdge[iEdge - 1]);
+                }
+                for (int k = 2; k <= L - 1; ++k) {
+                    real z1 = 0.5 * (zgrid[IX2(k - 1, cell1, L1)] + zgrid[IX2(k - 1, cell2, L1)]);
+                    real z2 = 0.5 * (zgrid[IX2(k, cell1, L1)] + zgrid[IX2(k, cell2, L1)]);
+                    real z3 = 0.5 * (zgrid[IX2(k + 1, cell1, L1)] + zgrid[IX2(k + 1, cell2, L1)]);
+                    real z4 = 0.5 * (zgrid[IX2(k + 2, cell1, L1)] + zgrid[IX2(k + 2, cell2, L1)]);
+                    real zm = 0.5 * (z1 + z2), z0 = 0.5 * (z2 + z3), zp = 0.5 * (z3 + z4);
+                    tend_u_euler[IX2(k, iEdge, L)] = tend_u_euler[IX2(k, iEdge, L)] +
+                                                     rho_edge[IX2(k, iEdge, L)] * v_mom_eddy_visc2 *
+                                                         ((u_mix[k + 1] - u_mix[k]) / (zp - z0) - (u_mix[k] - u_mix[k - 1]) / (z0 - zm)) / (0.5 * (zp - zm));
+                }
+            }
+        }
+    }
+
+    if (config_rayleigh_damp_u) {  // TI:5015-5028
+        const int nl = config_number_rayleigh_damp_u_levels;
+        real rayleigh_coef_inverse = 1.0 / ((real)nl * (config_rayleigh_damp_u_timescale_days * 86400.0));
+        for (int iEdge = edgeSolveStart; iEdge <= edgeSolveEnd; ++iEdge)
+            for (int k = L - nl + 1; k <= L; ++k) {
+                real coef = (real)(k - (L - nl)) * rayleigh_coef_inverse;
+                tend_u[IX2(k, iEdge, L)] = tend_u[IX2(k, iEdge, L)] - rho_edge[IX2(k, iEdge, L)] * u[IX2(k, iEdge, L)] * coef;
+            }
+    }
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeSolveStart; iEdge <= edgeSolveEnd; ++iEdge)
+        for (int k = 1; k <= L; ++k)
+            tend_u[IX2(k, iEdge, L)] = tend_u[IX2(k, iEdge, L)] + tend_u_euler[IX2(k, iEdge, L)] + (tend_ru_physics ? tend_ru_physics[IX2(k, iEdge, L)] : 0.0);
+
+    // ---- w tendency: horizontal advection, TI:5046-5074
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        std::vector<real> ru_edge_w(L + 1), flux_arr(L + 1);
+        for (int k = 1; k <= L1; ++k) tend_w[IX2(k, iCell, L1)] = 0.0;
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+            for (int k = 2; k <= L; ++k) ru_edge_w[k] = fzm[k - 1] * ru[IX2(k, iEdge, L)] + fzp[k - 1] * ru[IX2(k - 1, iEdge, L)];
+            for (int k = 1; k <= L; ++k) flux_arr[k] = 0.0;
+            for (int j = 1; j <= nAdvCellsForEdge[iEdge - 1]; ++j) {
+                int iAdvCell = advCellsForEdge[IX2(j, iEdge, 15)];
+                for (int k = 2; k <= L; ++k) {
+                    real scalar_weight = adv_coefs[IX2(j, iEdge, 15)] + fsign(1.0, ru_edge_w[k]) * adv_coefs_3rd[IX2(j, iEdge, 15)];
+                    flux_arr[k] = flux_arr[k] + scalar_weight * w[IX2(k, iAdvCell, L1)];
+                }
+            }
+            for (int k = 2; k <= L; ++k) tend_w[IX2(k, iCell, L1)] = tend_w[IX2(k, iCell, L1)] - edgesOnCell_sign[IX2(i, iCell, mE)] * ru_edge_w[k] * flux_arr[k];
+        }
+    }
+    if (rk_step == 1) {  // TI:5097-5154
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+            for (int k = 1; k <= L; ++k) delsq_w[IX2(k, iCell, L)] = 0.0;
+            for (int k = 1; k <= L1; ++k) tend_w_euler[IX2(k, iCell, L1)] = 0.0;
+            real r_areaCell = invAreaCell[iCell - 1];
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                real edge_sign = 0.5 * r_areaCell * edgesOnCell_sign[IX2(i, iCell, mE)] * dvEdge[iEdge - 1] * invDcEdge[iEdge - 1];
+                int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                for (int k = 2; k <= L; ++k) {
+                    real w_turb_flux = edge_sign * (rho_edge[IX2(k, iEdge, L)] + rho_edge[IX2(k - 1, iEdge, L)]) * (w[IX2(k, cell2, L1)] - w[IX2(k, cell1, L1)]);
+                    delsq_w[IX2(k, iCell, L)] = delsq_w[IX2(k, iCell, L)] + w_turb_flux;
+                    w_turb_flux = w_turb_flux * meshScalingDel2[iEdge - 1] * 0.25 *
+                                  (kdiff[IX2(k, cell1, L)] + kdiff[IX2(k, cell2, L)] + kdiff[IX2(k - 1, cell1, L)] + kdiff[IX2(k - 1, cell2, L)]);
+                    tend_w_euler[IX2(k, iCell, L1)] = tend_w_euler[IX2(k, iCell, L1)] + w_turb_flux;
+                }
+            }
+        }
+        if (h_mom_eddy_visc4 > 0.0) {
+#pragma omp parallel for schedule(static)
+            for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+                real r_areaCell = h_mom_eddy_visc4 * invAreaCell[iCell - 1];
+                for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                    int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                    int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                    real edge_sign = meshScalingDel4[iEdge - 1] * r_areaCell * dvEdge[iEdge - 1] * edgesOnCell_sign[IX2(i, iCell, mE)] * invDcEdge[iEdge - 1];
+                    for (int k = 2; k <= L; ++k)
+                        tend_w_euler[IX2(k, iCell, L1)] = tend_w_euler[IX2(k, iCell, L1)] - edge_sign * (delsq_w[IX2(k, cell2, L)] - delsq_w[IX2(k, cell1, L)]);
+                }
+            }
+        }
+    }
+    // vertical advection, pgf, buoyancy for w, TI:5167-5223
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        std::vector<real> wdwz(L + 2);
+        wdwz[1] = 0.0;
+        int k = 2;
+        wdwz[k] = 0.25 * (rw[IX2(k, iCell, L1)] + rw[IX2(k - 1, iCell, L1)]) * (w[IX2(k, iCell, L1)] + w[IX2(k - 1, iCell, L1)]);
+        for (k = 3; k <= L - 1; ++k)
+            wdwz[k] = flux3(w[IX2(k - 2, iCell, L1)], w[IX2(k - 1, iCell, L1)], w[IX2(k, iCell, L1)], w[IX2(k + 1, iCell, L1)],
+                            0.5 * (rw[IX2(k, iCell, L1)] + rw[IX2(k - 1, iCell, L1)]), 1.0);
+        k = L;
+        wdwz[k] = 0.25 * (rw[IX2(k, iCell, L1)] + rw[IX2(k - 1, iCell, L1)]) * (w[IX2(k, iCell, L1)] + w[IX2(k - 1, iCell, L1)]);
+        wdwz[L + 1] = 0.0;
+        for (k = 2; k <= L; ++k) tend_w[IX2(k, iCell, L1)] = tend_w[IX2(k, iCell, L1)] * invAreaCell[iCell - 1] - rdzu[k - 1] * (wdwz[k + 1] - wdwz[k]);
+        if (rk_step == 1) {
+            for (k = 2; k <= L; ++k)
+                tend_w_euler[IX2(k, iCell, L1)] = tend_w_euler[IX2(k, iCell, L1)] -
+                                                  cqw[IX2(k, iCell, L)] * (rdzu[k - 1] * (pp[IX2(k, iCell, L)] - pp[IX2(k - 1, iCell, L)]) -
+                                                                           (fzm[k - 1] * dpdz[IX2(k, iCell, L)] + fzp[k - 1] * dpdz[IX2(k - 1, iCell, L)]));
+            if (v_mom_eddy_visc2 > 0.0)
+                for (k = 2; k <= L; ++k)
+                    tend_w_euler[IX2(k, iCell, L1)] = tend_w_euler[IX2(k, iCell, L1)] +
+                                                      v_mom_eddy_visc2 * 0.5 * (rho_zz[IX2(k, iCell, L)] + rho_zz[IX2(k - 1, iCell, L)]) *
+                                                          ((w[IX2(k + 1, iCell, L1)] - w[IX2(k, iCell, L1)]) * rdzw[k - 1] - (w[IX2(k, iCell, L1)] - w[IX2(k - 1, iCell, L1)]) * rdzw[k - 2]) *
+                                                          rdzu[k - 1];
+        }
+        for (k = 2; k <= L; ++k) tend_w[IX2(k, iCell, L1)] = tend_w[IX2(k, iCell, L1)] + tend_w_euler[IX2(k, iCell, L1)];
+    }
+
+    // ---- theta tendency: horizontal advection, TI:5231-5269
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        std::vector<real> flux_arr(L + 1);
+        for (int k = 1; k <= L; ++k) tend_theta[IX2(k, iCell, L)] = 0.0;
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+            for (int k = 1; k <= L; ++k) flux_arr[k] = 0.0;
+            for (int j = 1; j <= nAdvCellsForEdge[iEdge - 1]; ++j) {
+                int iAdvCell = advCellsForEdge[IX2(j, iEdge, 15)];
+                for (int k = 1; k <= L; ++k) {
+                    real scalar_weight = adv_coefs[IX2(j, iEdge, 15)] + fsign(1.0, ru[IX2(k, iEdge, L)]) * adv_coefs_3rd[IX2(j, iEdge, 15)];
+                    flux_arr[k] = flux_arr[k] + scalar_weight * theta_m[IX2(k, iAdvCell, L)];
+                }
+            }
+            for (int k = 1; k <= L; ++k) tend_theta[IX2(k, iCell, L)] = tend_theta[IX2(k, iCell, L)] - edgesOnCell_sign[IX2(i, iCell, mE)] * ru[IX2(k, iEdge, L)] * flux_arr[k];
+        }
+        if (rk_step > 1) {
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                for (int k = 1; k <= L; ++k) {
+                    real flux = edgesOnCell_sign[IX2(i, iCell, mE)] * dvEdge[iEdge - 1] * (ru_save[IX2(k, iEdge, L)] - ru[IX2(k, iEdge, L)]) * 0.5 *
+                                (theta_m_save[IX2(k, cell2, L)] + theta_m_save[IX2(k, cell1, L)]);
+                    tend_theta[IX2(k, iCell, L)] = tend_theta[IX2(k, iCell, L)] - flux;
+                }
+            }
+        }
+    }
+    if (rk_step == 1) {  // TI:5276-5325
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
+            for (int k = 1; k <= L; ++k) { delsq_theta[IX2(k, iCell, L)] = 0.0; tend_theta_euler[IX2(k, iCell, L)] = 0.0; }
+            real r_areaCell = invAreaCell[iCell - 1];
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                real edge_sign = r_areaCell * edgesOnCell_sign[IX2(i, iCell, mE)] * dvEdge[iEdge - 1] * invDcEdge[iEdge - 1];
+                real pr_scale = prandtl_inv * meshScalingDel2[iEdge - 1];
+                int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                for (int k = 1; k <= L; ++k) {
+                    real theta_turb_flux = edge_sign * (theta_m[IX2(k, cell2, L)] - theta_m[IX2(k, cell1, L)]) * rho_edge[IX2(k, iEdge, L)];
+                    delsq_theta[IX2(k, iCell, L)] = delsq_theta[IX2(k, iCell, L)] + theta_turb_flux;
+                    theta_turb_flux = theta_turb_flux * 0.5 * (kdiff[IX2(k, cell1, L)] + kdiff[IX2(k, cell2, L)]) * pr_scale;
+                    tend_theta_euler[IX2(k, iCell, L)] = tend_theta_euler[IX2(k, iCell, L)] + theta_turb_flux;
+                }
+            }
+        }
+        if (h_theta_eddy_visc4 > 0.0) {
+#pragma omp parallel for schedule(static)
+            for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+                real r_areaCell = h_theta_eddy_visc4 * prandtl_inv * invAreaCell[iCell - 1];
+                for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                    int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                    real edge_sign = meshScalingDel4[iEdge - 1] * r_areaCell * dvEdge[iEdge - 1] * edgesOnCell_sign[IX2(i, iCell, mE)] * invDcEdge[iEdge - 1];
+                    int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+                    for (int k = 1; k <= L; ++k)
+                        tend_theta_euler[IX2(k, iCell, L)] = tend_theta_euler[IX2(k, iCell, L)] - edge_sign * (delsq_theta[IX2(k, cell2, L)] - delsq_theta[IX2(k, cell1, L)]);
+                }
+            }
+        }
+    }
+    // vertical advection + diabatic, TI:5331-5354; vertical mixing :5360-5406; final sum :5408-5414
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        std::vector<real> wdtz(L + 2);
+        wdtz[1] = 0.0;
+        int k = 2;
+        wdtz[k] = rw[IX2(k, iCell, L1)] * (fzm[k - 1] * theta_m[IX2(k, iCell, L)] + fzp[k - 1] * theta_m[IX2(k - 1, iCell, L)]);
+        wdtz[k] = wdtz[k] + (rw_save[IX2(k, iCell, L1)] - rw[IX2(k, iCell, L1)]) * (fzm[k - 1] * theta_m_save[IX2(k, iCell, L)] + fzp[k - 1] * theta_m_save[IX2(k - 1, iCell, L)]);
+        for (k = 3; k <= L - 1; ++k) {
+            wdtz[k] = flux3(theta_m[IX2(k - 2, iCell, L)], theta_m[IX2(k - 1, iCell, L)], theta_m[IX2(k, iCell, L)], theta_m[IX2(k + 1, iCell, L)], rw[IX2(k, iCell, L1)], coef_3rd_order);
+            wdtz[k] = wdtz[k] + (rw_save[IX2(k, iCell, L1)] - rw[IX2(k, iCell, L1)]) * (fzm[k - 1] * theta_m_save[IX2(k, iCell, L)] + fzp[k - 1] * theta_m_save[IX2(k - 1, iCell, L)]);
+        }
+        k = L;
+        wdtz[k] = rw_save[IX2(k, iCell, L1)] * (fzm[k - 1] * theta_m[IX2(k, iCell, L)] + fzp[k - 1] * theta_m[IX2(k - 1, iCell, L)]);
+        wdtz[L + 1] = 0.0;
+        for (k = 1; k <= L; ++k) {
+            tend_theta[IX2(k, iCell, L)] = tend_theta[IX2(k, iCell, L)] * invAreaCell[iCell - 1] - rdzw[k - 1] * (wdtz[k + 1] - wdtz[k]);
+            if (tend_rtheta_adv) tend_rtheta_adv[IX2(k, iCell, L)] = tend_theta[IX2(k, iCell, L)];
+            if (rthdynten) rthdynten[IX2(k, iCell, L)] = tend_theta[IX2(k, iCell, L)] / rho_zz[IX2(k, iCell, L)];
+            tend_theta[IX2(k, iCell, L)] = tend_theta[IX2(k, iCell, L)] + rho_zz[IX2(k, iCell, L)] * (rt_diabatic_tend ? rt_diabatic_tend[IX2(k, iCell, L)] : 0.0);
+        }
+        if (rk_step == 1 && v_theta_eddy_visc2 > 0.0) {
+            for (k = 2; k <= L - 1; ++k) {
+                real z1 = zgrid[IX2(k - 1, iCell, L1)], z2 = zgrid[IX2(k, iCell, L1)], z3 = zgrid[IX2(k + 1, iCell, L1)], z4 = zgrid[IX2(k + 2, iCell, L1)];
+                real zm = 0.5 * (z1 + z2), z0 = 0.5 * (z2 + z3), zp = 0.5 * (z3 + z4);
+                if (config_mix_full)
+                    tend_theta_euler[IX2(k, iCell, L)] = tend_theta_euler[IX2(k, iCell, L)] +
+                                                         v_theta_eddy_visc2 * prandtl_inv * rho_zz[IX2(k, iCell, L)] *
+                                                             ((theta_m[IX2(k + 1, iCell, L)] - theta_m[IX2(k, iCell, L)]) / (zp - z0) -
+                                                              (theta_m[IX2(k, iCell, L)] - theta_m[IX2(k - 1, iCell, L)]) / (z0 - zm)) / (0.5 * (zp - zm));
+                else
+                    tend_theta_euler[IX2(k, iCell, L)] =
+                        tend_theta_euler[IX2(k, iCell, L)] +
+                        v_theta_eddy_visc2 * prandtl_inv * rho_zz[IX2(k, iCell, L)] *
+                            (((theta_m[IX2(k + 1, iCell, L)] - t_init[IX2(k + 1, iCell, L)]) - (theta_m[IX2(k, iCell, L)] - t_init[IX2(k, iCell, L)])) / (zp - z0) -
+                             ((theta_m[IX2(k, iCell, L)] - t_init[IX2(k, iCell, L)]) - (theta_m[IX2(k - 1, iCell, L)] - t_init[IX2(k - 1, iCell, L)])) / (z0 - zm)) /
+                            (0.5 * (zp - zm));
+            }
+        }
+        for (k = 1; k <= L; ++k)
+            tend_theta[IX2(k, iCell, L)] = tend_theta[IX2(k, iCell, L)] + tend_theta_euler[IX2(k, iCell, L)] + (tend_rtheta_physics ? tend_rtheta_physics[IX2(k, iCell, L)] : 0.0);
+    }
+    return 0;
+}
+
+}  // extern "C"
+
+extern "C" {
+
+// ------------------------------------------------------------------ TI:3238-3506
+int oracle_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, mE = maxEdges, ns = num_scalars;
+    (void)nCells; (void)nEdges;
+    real weight_time_new = 1.;
+    if (advance_density) {
+        if ((rk_step == 1) && config_time_integration_order == 3) weight_time_new = 1. / 3;
+        if ((rk_step == 1) && config_time_integration_order == 2) weight_time_new = 1. / 2;
+        if (rk_step == 2) weight_time_new = 1. / 2;
+        if (rk_step == 3) weight_time_new = 1.;
+    }
+    real weight_time_old = 1. - weight_time_new;
+#pragma omp parallel for schedule(static)
+    for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+        if ((!config_apply_lbcs) || (bdyMaskEdge[iEdge - 1] < nRelaxZone - 1)) {
+            int n = nAdvCellsForEdge[iEdge - 1];
+            if (n == 10) {
+                for (int k = 1; k <= L; ++k) {
+                    real sw[11];
+                    for (int j = 1; j <= 10; ++j) sw[j] = adv_coefs[IX2(j, iEdge, 15)] + fsign(1.0, uhAvg[IX2(k, iEdge, L)]) * adv_coefs_3rd[IX2(j, iEdge, 15)];
+                    for (int iScalar = 1; iScalar <= ns; ++iScalar) {
+                        real s = sw[1] * scalar_new[IX3(iScalar, k, advCellsForEdge[IX2(1, iEdge, 15)], ns, L)];
+                        for (int j = 2; j <= 10; ++j) s = s + sw[j] * scalar_new[IX3(iScalar, k, advCellsForEdge[IX2(j, iEdge, 15)], ns, L)];
+                        horiz_flux_arr[IX3(iScalar, k, iEdge, ns, L)] = s;
+                    }
+                }
+            } else {
+                for (int k = 1; k <= L; ++k)
+                    for (int iScalar = 1; iScalar <= ns; ++iScalar) horiz_flux_arr[IX3(iScalar, k, iEdge, ns, L)] = 0.0;
+                for (int j = 1; j <= n; ++j) {
+                    int iAdvCell = advCellsForEdge[IX2(j, iEdge, 15)];
+                    for (int k = 1; k <= L; ++k) {
+                        real scalar_weight = adv_coefs[IX2(j, iEdge, 15)] + fsign(1.0, uhAvg[IX2(k, iEdge, L)]) * adv_coefs_3rd[IX2(j, iEdge, 15)];
+                        for (int iScalar = 1; iScalar <= ns; ++iScalar)
+                            horiz_flux_arr[IX3(iScalar, k, iEdge, ns, L)] = horiz_flux_arr[IX3(iScalar, k, iEdge, ns, L)] + scalar_weight * scalar_new[IX3(iScalar, k, iAdvCell, ns, L)];
+                    }
+                }
+            }
+        }
+    }
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+        if (bdyMaskCell[iCell - 1] <= nRelaxZone) {
+            std::vector<real> col((size_t)ns * (L + 1), 0.0), wdtn((size_t)ns * (L + 2), 0.0);
+            auto COL = [&](int q, int k) -> real& { return col[(size_t)(k - 1) * ns + (q - 1)]; };
+            auto WD = [&](int q, int k) -> real& { return wdtn[(size_t)(k - 1) * ns + (q - 1)]; };
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                for (int k = 1; k <= L; ++k)
+                    for (int q = 1; q <= ns; ++q)
+                        COL(q, k) = COL(q, k) - edgesOnCell_sign[IX2(i, iCell, mE)] * uhAvg[IX2(k, iEdge, L)] * horiz_flux_arr[IX3(q, k, iEdge, ns, L)];
+            }
+            for (int k = 1; k <= L; ++k)
+                for (int q = 1; q <= ns; ++q) COL(q, k) = COL(q, k) * invAreaCell[iCell - 1] + scalar_tend_save[IX3(q, k, iCell, ns, L)];
+            int k = 2;
+            for (int q = 1; q <= ns; ++q)
+                WD(q, k) = wwAvg[IX2(k, iCell, L1)] * (fnm[k - 1] * scalar_new[IX3(q, k, iCell, ns, L)] + fnp[k - 1] * scalar_new[IX3(q, k - 1, iCell, ns, L)]);
+            for (k = 3; k <= L - 1; ++k)
+                for (int q = 1; q <= ns; ++q)
+                    WD(q, k) = flux3(scalar_new[IX3(q, k - 2, iCell, ns, L)], scalar_new[IX3(q, k - 1, iCell, ns, L)], scalar_new[IX3(q, k, iCell, ns, L)],
+                                     scalar_new[IX3(q, k + 1, iCell, ns, L)], wwAvg[IX2(k, iCell, L1)], coef_3rd_order);
+            k = L;
+            for (int q = 1; q <= ns; ++q)
+                WD(q, k) = wwAvg[IX2(k, iCell, L1)] * (fnm[k - 1] * scalar_new[IX3(q, k, iCell, ns, L)] + fnp[k - 1] * scalar_new[IX3(q, k - 1, iCell, ns, L)]);
+            for (k = 1; k <= L; ++k) {
+                real rho_zz_new_inv = 1.0 / (weight_time_old * rho_zz_old[IX2(k, iCell, L)] + weight_time_new * rho_zz_new[IX2(k, iCell, L)]);
+                for (int q = 1; q <= ns; ++q)
+                    scalar_new[IX3(q, k, iCell, ns, L)] =
+                        (scalar_old[IX3(q, k, iCell, ns, L)] * rho_zz_old[IX2(k, iCell, L)] + dt * (COL(q, k) - rdnw[k - 1] * (WD(q, k + 1) - WD(q, k)))) * rho_zz_new_inv;
+            }
+        }
+    }
+    return 0;
+}
+
+// ------------------------------------------------------------------ TI:3612-4214
+int oracle_advance_scalars_mono_work(MPAS_MONO_ARGS) {
+    const int L = nVertLevels, L1 = L + 1, mE = maxEdges, ns = num_scalars;
+    const int SCALE_IN = 1, SCALE_OUT = 2;
+    const real eps = 1.e-20;
+    (void)nEdges;
+#pragma omp parallel for schedule(static)
+    for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell)
+        for (int k = 1; k <= L; ++k)
+            for (int q = 1; q <= ns; ++q) {
+                scalars_old[IX3(q, k, iCell, ns, L)] = scalars_old[IX3(q, k, iCell, ns, L)] + dt * scalar_tend[IX3(q, k, iCell, ns, L)] / rho_zz_old[IX2(k, iCell, L)];
+                scalar_tend[IX3(q, k, iCell, ns, L)] = 0.0;
+            }
+    if (halo_fn) halo_fn(halo_ctx, 0, scalars_old);  // TI:3757
+    if (advance_density) {
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+            for (int k = 1; k <= L; ++k) rho_zz_int[IX2(k, iCell, L)] = 0.0;
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                for (int k = 1; k <= L; ++k)
+                    rho_zz_int[IX2(k, iCell, L)] = rho_zz_int[IX2(k, iCell, L)] - edgesOnCell_sign[IX2(i, iCell, mE)] * uhAvg[IX2(k, iEdge, L)] * dvEdge[iEdge - 1] * invAreaCell[iCell - 1];
+            }
+            for (int k = 1; k <= L; ++k)
+                rho_zz_int[IX2(k, iCell, L)] = rho_zz_old[IX2(k, iCell, L)] + dt * (rho_zz_int[IX2(k, iCell, L)] - rdnw[k - 1] * (wwAvg[IX2(k + 1, iCell, L1)] - wwAvg[IX2(k, iCell, L1)]));
+        }
+    }
+    const real* rho_lim = advance_density ? rho_zz_int : rho_zz_new;
+
+    for (int iScalar = 1; iScalar <= ns; ++iScalar) {
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+            for (int k = 1; k <= L; ++k) {
+                scalar_old[IX2(k, iCell, L)] = scalars_old[IX3(iScalar, k, iCell, ns, L)];
+                scalar_new[IX2(k, iCell, L)] = scalars_new[IX3(iScalar, k, iCell, ns, L)];
+            }
+        for (int k = 1; k <= L; ++k) { scalar_old[IX2(k, nCells + 1, L)] = 0.; scalar_new[IX2(k, nCells + 1, L)] = 0.; }
+
+        // vertical flux + bounds, TI:3843-3908
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+            wdtn[IX2(1, iCell, L1)] = 0.0;
+            wdtn[IX2(L + 1, iCell, L1)] = 0.0;
+            int k = 1;
+            s_max[IX2(k, iCell, L)] = std::max(scalar_old[IX2(1, iCell, L)], scalar_old[IX2(2, iCell, L)]);
+            s_min[IX2(k, iCell, L)] = std::min(scalar_old[IX2(1, iCell, L)], scalar_old[IX2(2, iCell, L)]);
+            k = 2;
+            wdtn[IX2(k, iCell, L1)] = wwAvg[IX2(k, iCell, L1)] * (fnm[k - 1] * scalar_new[IX2(k, iCell, L)] + fnp[k - 1] * scalar_new[IX2(k - 1, iCell, L)]);
+            s_max[IX2(k, iCell, L)] = std::max(std::max(scalar_old[IX2(k - 1, iCell, L)], scalar_old[IX2(k, iCell, L)]), scalar_old[IX2(k + 1, iCell, L)]);
+            s_min[IX2(k, iCell, L)] = std::min(std::min(scalar_old[IX2(k - 1, iCell, L)], scalar_old[IX2(k, iCell, L)]), scalar_old[IX2(k + 1, iCell, L)]);
+            for (k = 3; k <= L - 1; ++k) {
+                wdtn[IX2(k, iCell, L1)] = flux3(scalar_new[IX2(k - 2, iCell, L)], scalar_new[IX2(k - 1, iCell, L)], scalar_new[IX2(k, iCell, L)],
+                                                scalar_new[IX2(k + 1, iCell, L)], wwAvg[IX2(k, iCell, L1)], coef_3rd_order);
+                s_max[IX2(k, iCell, L)] = std::max(std::max(scalar_old[IX2(k - 1, iCell, L)], scalar_old[IX2(k, iCell, L)]), scalar_old[IX2(k + 1, iCell, L)]);
+                s_min[IX2(k, iCell, L)] = std::min(std::min(scalar_old[IX2(k - 1, iCell, L)], scalar_old[IX2(k, iCell, L)]), scalar_old[IX2(k + 1, iCell, L)]);
+            }
+            k = L;
+            wdtn[IX2(k, iCell, L1)] = wwAvg[IX2(k, iCell, L1)] * (fnm[k - 1] * scalar_new[IX2(k, iCell, L)] + fnp[k - 1] * scalar_new[IX2(k - 1, iCell, L)]);
+            s_max[IX2(k, iCell, L)] = std::max(scalar_old[IX2(k, iCell, L)], scalar_old[IX2(k - 1, iCell, L)]);
+            s_min[IX2(k, iCell, L)] = std::min(scalar_old[IX2(k, iCell, L)], scalar_old[IX2(k - 1, iCell, L)]);
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int cc = cellsOnCell[IX2(i, iCell, mE)];
+                for (k = 1; k <= L; ++k) {
+                    s_max[IX2(k, iCell, L)] = std::max(s_max[IX2(k, iCell, L)], scalar_old[IX2(k, cc, L)]);
+                    s_min[IX2(k, iCell, L)] = std::min(s_min[IX2(k, iCell, L)], scalar_old[IX2(k, cc, L)]);
+                }
+            }
+        }
+        // horizontal high-order flux, TI:3916-3961
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+            if (cell1 <= nCellsSolve || cell2 <= nCellsSolve) {
+                int n = nAdvCellsForEdge[iEdge - 1];
+                if (n == 10) {
+                    int ica[11];
+                    real swa[11][3];
+                    for (int jj = 1; jj <= 10; ++jj) {
+                        ica[jj] = advCellsForEdge[IX2(jj, iEdge, 15)];
+                        swa[jj][1] = adv_coefs[IX2(jj, iEdge, 15)] + adv_coefs_3rd[IX2(jj, iEdge, 15)];
+                        swa[jj][2] = adv_coefs[IX2(jj, iEdge, 15)] - adv_coefs_3rd[IX2(jj, iEdge, 15)];
+                    }
+                    for (int k = 1; k <= L; ++k) {
+                        int ii = (uhAvg[IX2(k, iEdge, L)] > 0) ? 1 : 2;
+                        real s = swa[1][ii] * scalar_new[IX2(k, ica[1], L)];
+                        for (int jj = 2; jj <= 10; ++jj) s = s + swa[jj][ii] * scalar_new[IX2(k, ica[jj], L)];
+                        flux_arr[IX2(k, iEdge, L)] = uhAvg[IX2(k, iEdge, L)] * s;
+                    }
+                } else {
+                    for (int k = 1; k <= L; ++k) flux_arr[IX2(k, iEdge, L)] = 0.0;
+                    for (int i = 1; i <= n; ++i) {
+                        int iCell = advCellsForEdge[IX2(i, iEdge, 15)];
+                        for (int k = 1; k <= L; ++k) {
+                            real scalar_weight = uhAvg[IX2(k, iEdge, L)] * (adv_coefs[IX2(i, iEdge, 15)] + fsign(1.0, uhAvg[IX2(k, iEdge, L)]) * adv_coefs_3rd[IX2(i, iEdge, 15)]);
+                            flux_arr[IX2(k, iEdge, L)] = flux_arr[IX2(k, iEdge, L)] + scalar_weight * scalar_new[IX2(k, iCell, L)];
+                        }
+                    }
+                }
+            } else {
+                for (int k = 1; k <= L; ++k) flux_arr[IX2(k, iEdge, L)] = 0.0;
+            }
+        }
+        // vertical upwind update, TI:3969-4000
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+            std::vector<real> flux_upwind_arr(L + 2);
+            int k = 1;
+            scalar_new[IX2(k, iCell, L)] = scalar_old[IX2(k, iCell, L)] * rho_zz_old[IX2(k, iCell, L)];
+            for (k = 2; k <= L; ++k) {
+                scalar_new[IX2(k, iCell, L)] = scalar_old[IX2(k, iCell, L)] * rho_zz_old[IX2(k, iCell, L)];
+                flux_upwind_arr[k] = dt * (std::max((real)0.0, wwAvg[IX2(k, iCell, L1)]) * scalar_old[IX2(k - 1, iCell, L)] + std::min((real)0.0, wwAvg[IX2(k, iCell, L1)]) * scalar_old[IX2(k, iCell, L)]);
+            }
+            for (k = 1; k <= L - 1; ++k) scalar_new[IX2(k, iCell, L)] = scalar_new[IX2(k, iCell, L)] - flux_upwind_arr[k + 1] * rdnw[k - 1];
+            for (k = 2; k <= L; ++k) {
+                scalar_new[IX2(k, iCell, L)] = scalar_new[IX2(k, iCell, L)] + flux_upwind_arr[k] * rdnw[k - 1];
+                wdtn[IX2(k, iCell, L1)] = dt * wdtn[IX2(k, iCell, L1)] - flux_upwind_arr[k];
+            }
+            for (k = 1; k <= L; ++k) {
+                scale_arr[IX3(k, SCALE_IN, iCell, L, 2)] = -rdnw[k - 1] * (std::min((real)0.0, wdtn[IX2(k + 1, iCell, L1)]) - std::max((real)0.0, wdtn[IX2(k, iCell, L1)]));
+                scale_arr[IX3(k, SCALE_OUT, iCell, L, 2)] = -rdnw[k - 1] * (std::max((real)0.0, wdtn[IX2(k + 1, iCell, L1)]) - std::min((real)0.0, wdtn[IX2(k, iCell, L1)]));
+            }
+        }
+        // horizontal upwind fluxes, TI:4007-4022
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+            for (int k = 1; k <= L; ++k) {
+                flux_upwind_tmp[IX2(k, iEdge, L)] = dvEdge[iEdge - 1] * dt *
+                                                    (std::max((real)0.0, uhAvg[IX2(k, iEdge, L)]) * scalar_old[IX2(k, cell1, L)] + std::min((real)0.0, uhAvg[IX2(k, iEdge, L)]) * scalar_old[IX2(k, cell2, L)]);
+                flux_tmp[IX2(k, iEdge, L)] = dt * flux_arr[IX2(k, iEdge, L)] - flux_upwind_tmp[IX2(k, iEdge, L)];
+            }
+            if ((config_apply_lbcs && (bdyMaskEdge[iEdge - 1] == nRelaxZone)) || (bdyMaskEdge[iEdge - 1] == nRelaxZone - 1)) {
+                for (int k = 1; k <= L; ++k) { flux_tmp[IX2(k, iEdge, L)] = 0.; flux_arr[IX2(k, iEdge, L)] = flux_upwind_tmp[IX2(k, iEdge, L)]; }
+            }
+        }
+        // accumulate + limiter, TI:4024-4076
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                for (int k = 1; k <= L; ++k) {
+                    scalar_new[IX2(k, iCell, L)] = scalar_new[IX2(k, iCell, L)] - edgesOnCell_sign[IX2(i, iCell, mE)] * flux_upwind_tmp[IX2(k, iEdge, L)] * invAreaCell[iCell - 1];
+                    scale_arr[IX3(k, SCALE_OUT, iCell, L, 2)] = scale_arr[IX3(k, SCALE_OUT, iCell, L, 2)] -
+                                                                std::max((real)0.0, edgesOnCell_sign[IX2(i, iCell, mE)] * flux_tmp[IX2(k, iEdge, L)]) * invAreaCell[iCell - 1];
+                    scale_arr[IX3(k, SCALE_IN, iCell, L, 2)] = scale_arr[IX3(k, SCALE_IN, iCell, L, 2)] -
+                                                               std::min((real)0.0, edgesOnCell_sign[IX2(i, iCell, mE)] * flux_tmp[IX2(k, iEdge, L)]) * invAreaCell[iCell - 1];
+                }
+            }
+            for (int k = 1; k <= L; ++k) {
+                real scale_factor = (s_max[IX2(k, iCell, L)] * rho_lim[IX2(k, iCell, L)] - scalar_new[IX2(k, iCell, L)]) / (scale_arr[IX3(k, SCALE_IN, iCell, L, 2)] + eps);
+                scale_arr[IX3(k, SCALE_IN, iCell, L, 2)] = std::min((real)1.0, std::max((real)0.0, scale_factor));
+                scale_factor = (s_min[IX2(k, iCell, L)] * rho_lim[IX2(k, iCell, L)] - scalar_new[IX2(k, iCell, L)]) / (scale_arr[IX3(k, SCALE_OUT, iCell, L, 2)] - eps);
+                scale_arr[IX3(k, SCALE_OUT, iCell, L, 2)] = std::min((real)1.0, std::max((real)0.0, scale_factor));
+            }
+        }
+        if (halo_fn) halo_fn(halo_ctx, 1, scale_arr);  // TI:4098
+        // perturbation flux + rescale, TI:4102-4138
+#pragma omp parallel for schedule(static)
+        for (int iEdge = edgeStart; iEdge <= edgeEnd; ++iEdge) {
+            int cell1 = cellsOnEdge[IX2(1, iEdge, 2)], cell2 = cellsOnEdge[IX2(2, iEdge, 2)];
+            if (cell1 <= nCellsSolve || cell2 <= nCellsSolve) {
+                for (int k = 1; k <= L; ++k) {
+                    real flux_upwind = dvEdge[iEdge - 1] * dt *
+                                       (std::max((real)0.0, uhAvg[IX2(k, iEdge, L)]) * scalar_old[IX2(k, cell1, L)] + std::min((real)0.0, uhAvg[IX2(k, iEdge, L)]) * scalar_old[IX2(k, cell2, L)]);
+                    flux_arr[IX2(k, iEdge, L)] = dt * flux_arr[IX2(k, iEdge, L)] - flux_upwind;
+                }
+                if ((config_apply_lbcs && (bdyMaskEdge[iEdge - 1] == nRelaxZone)) || (bdyMaskEdge[iEdge - 1] == nRelaxZone - 1))
+                    for (int k = 1; k <= L; ++k) flux_arr[IX2(k, iEdge, L)] = 0.;
+                for (int k = 1; k <= L; ++k) {
+                    real flux = flux_arr[IX2(k, iEdge, L)];
+                    flux = std::max((real)0.0, flux) * std::min(scale_arr[IX3(k, SCALE_OUT, cell1, L, 2)], scale_arr[IX3(k, SCALE_IN, cell2, L, 2)]) +
+                           std::min((real)0.0, flux) * std::min(scale_arr[IX3(k, SCALE_IN, cell1, L, 2)], scale_arr[IX3(k, SCALE_OUT, cell2, L, 2)]);
+                    flux_arr[IX2(k, iEdge, L)] = flux;
+                }
+            }
+        }
+        // rescale vertical flux, final update, TI:4145-4179
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellSolveStart; iCell <= cellSolveEnd; ++iCell) {
+            for (int k = 2; k <= L; ++k) {
+                real flux = wdtn[IX2(k, iCell, L1)];
+                flux = std::max((real)0.0, flux) * std::min(scale_arr[IX3(k - 1, SCALE_OUT, iCell, L, 2)], scale_arr[IX3(k, SCALE_IN, iCell, L, 2)]) +
+                       std::min((real)0.0, flux) * std::min(scale_arr[IX3(k, SCALE_OUT, iCell, L, 2)], scale_arr[IX3(k - 1, SCALE_IN, iCell, L, 2)]);
+                wdtn[IX2(k, iCell, L1)] = flux;
+            }
+            for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+                int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+                for (int k = 1; k <= L; ++k)
+                    scalar_new[IX2(k, iCell, L)] = scalar_new[IX2(k, iCell, L)] - edgesOnCell_sign[IX2(i, iCell, mE)] * flux_arr[IX2(k, iEdge, L)] * invAreaCell[iCell - 1];
+            }
+            for (int k = 1; k <= L; ++k)
+                scalar_new[IX2(k, iCell, L)] = (scalar_new[IX2(k, iCell, L)] + (-rdnw[k - 1] * (wdtn[IX2(k + 1, iCell, L1)] - wdtn[IX2(k, iCell, L1)]))) / rho_lim[IX2(k, iCell, L)];
+        }
+#pragma omp parallel for schedule(static)
+        for (int iCell = cellStart; iCell <= cellEnd; ++iCell)
+            if (bdyMaskCell[iCell - 1] <= nSpecZone)
+                for (int k = 1; k <= L; ++k) scalars_new[IX3(iScalar, k, iCell, ns, L)] = std::max((real)0.0, scalar_new[IX2(k, iCell, L)]);
+    }
+    return 0;
+}
+
+}  // extern "C"
