@@ -1,0 +1,104 @@
+/* C ABI of libmpas_b200.so -- the B200-native drop-in for the MPAS-Atmosphere SRK3 dycore step.
+ *
+ * Layer 1 (drop-in work routines): one entry point per reference *_work routine, same dummy-argument
+ * order (argument lists in mpas_b200_args.h, each citing TI = src/core_atmosphere/dynamics/
+ * mpas_atm_time_integration.F file:line).  Arrays may be DEVICE pointers, or HOST addresses inside a
+ * range registered with mpas_b200_register_field (the Fortran host keeps passing the pool arrays it
+ * always passed; the library maps them to device mirrors).  All calls are asynchronous on the
+ * library stream; they return 0 or a non-zero code with a message in mpas_b200_last_error()
+ * (the reference's error convention is mpas_log_write(..., MPAS_LOG_CRIT), TI:123-124).
+ *
+ * Layer 2 (device-resident dycore, the atm_srk3 call sequence TI:142-1796 for the harness, the
+ * tests and bench.py): mpas_b200_dycore_*.  Halo exchanges (mpas_dmpar_exch_halo_field,
+ * src/framework/mpas_dmpar.F:5386-5748) run as pack kernel -> NCCL grouped send/recv (or
+ * device copies between blocks of one process) -> unpack kernel.
+ *
+ * Layer 0 (host harness: mesh, decomposition, initial conditions): mpas_host_*.
+ */
+#ifndef MPAS_B200_H
+#define MPAS_B200_H
+#include <stddef.h>
+
+#include "mpas_b200_args.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- lifecycle / registry (no reference analogue) ---- */
+const char* mpas_b200_last_error(void);
+int mpas_b200_set_device(int device);
+int mpas_b200_device_count(void);
+int mpas_b200_register_field(const void* host, size_t bytes);
+int mpas_b200_unregister_field(const void* host);
+int mpas_b200_upload(const void* host);
+int mpas_b200_download(void* host);
+void* mpas_b200_device_ptr(const void* host);
+int mpas_b200_synchronize(void);
+long long mpas_b200_launch_count(void);
+int mpas_b200_finalize(void);
+
+/* ---- Layer 1: work routines ---- */
+int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS);              /* TI:2447 */
+int mpas_b200_divergence_damping_3d(MPAS_DIVDAMP_ARGS);                    /* TI:2726 */
+int mpas_b200_recover_large_step_variables_work(MPAS_RECOVER_ARGS);        /* TI:2909 */
+int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS);                    /* TI:4481 */
+int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS);                   /* TI:3612 */
+int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS);                  /* TI:3238 */
+int mpas_b200_compute_solve_diagnostics_work(MPAS_SOLVEDIAG_ARGS);         /* TI:5513 */
+int mpas_b200_compute_vert_imp_coefs_work(MPAS_VERTIMP_ARGS);              /* TI:2012 */
+int mpas_b200_set_smlstep_pert_variables_work(MPAS_SMLSTEP_ARGS);          /* TI:2224 */
+int mpas_b200_rk_integration_setup(MPAS_RKSETUP_ARGS);                     /* TI:1799 */
+int mpas_b200_compute_moist_coefficients(MPAS_MOIST_ARGS);                 /* TI:1862 */
+int mpas_b200_rk_dynamics_substep_finish(MPAS_SUBSTEPFINISH_ARGS);         /* TI:5993 */
+int mpas_b200_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS);             /* TI:5825 */
+
+/* ---- Layer 2: device-resident dycore ---- */
+void* mpas_b200_dycore_create(int nLocalBlocks, int rank, int nranks);
+void mpas_b200_dycore_destroy(void* h);
+/* upload every pool field, config value and exchange list of a host-harness block (mpas_host_case_block) */
+int mpas_b200_dycore_attach_block(void* h, int iLocal, void* hostBlock);
+int mpas_b200_dycore_set_cfg(void* h, int iLocal, const char* name, double value);
+double mpas_b200_dycore_get_cfg(void* h, int iLocal, const char* name);
+/* NCCL: rank 0 fills id (128 bytes) with mpas_b200_nccl_unique_id, the host broadcasts it, every rank calls comm_init */
+int mpas_b200_nccl_unique_id(void* id128);
+int mpas_b200_dycore_comm_init(void* h, const void* id128);
+int mpas_b200_dycore_init(void* h);             /* atm_mpas_init_block + exchanges, mpas_atm_core.F:145-186, 311-402 */
+int mpas_b200_dycore_step(void* h, int nsteps); /* atm_srk3 + time-level shift, TI:142, mpas_atm_core.F:671 */
+int mpas_b200_dycore_get_field(void* h, int iLocal, const char* name, void* host_out, size_t bytes);
+int mpas_b200_dycore_set_field(void* h, int iLocal, const char* name, const void* host_in, size_t bytes);
+void* mpas_b200_dycore_field_device_ptr(void* h, int iLocal, const char* name);
+int mpas_b200_dycore_exchange(void* h, const char* name, int layer /* 0 = all */);
+/* run ONE work routine on the model's current fields (tests): name = "acoustic", "divdamp", "recover",
+ * "dyn_tend", "mono", "advance_scalars", "solve_diagnostics", "vert_imp_coefs", "smlstep", "rk_setup",
+ * "moist", "substep_finish"; params as documented in dycore.cu */
+int mpas_b200_dycore_call(void* h, const char* routine, const double* params, int nparams);
+long mpas_b200_dycore_exchange_count(void* h);
+int mpas_b200_dycore_set_option(void* h, const char* name, int value); /* "timing", "graph", "aggregate" */
+int mpas_b200_dycore_timer_count(void* h);
+int mpas_b200_dycore_timer_get(void* h, int idx, char* name, int cap, double* ms, long* calls);
+int mpas_b200_dycore_timer_reset(void* h);
+double mpas_b200_dycore_global_max_abs(void* h, const char* name); /* summarize_timestep analogue, TI:6675 */
+
+/* ---- Layer 0: host harness (mesh, partition, JW initial state) ---- */
+void* mpas_host_case_create(int level, int lloyd_iters, int sfc);
+void mpas_host_case_destroy(void* h);
+int mpas_host_case_dims(void* h, int* nCells, int* nEdges, int* nVertices, int* maxEdges, int* maxEdges2);
+int mpas_host_case_permutation(void* h, int kind, int* out);
+int mpas_host_case_partition(void* h, int nBlocks, int method, const char* prefix);
+int mpas_host_case_get_partition(void* h, int* out);
+int mpas_host_case_build_block(void* h, int iBlock, int nVertLevels, int init_case, int num_scalars, int full_fields, int keep_zb);
+void* mpas_host_case_block(void* h, int iBlock);
+int mpas_host_block_nfields(void* b);
+int mpas_host_block_field_info(void* b, int idx, char* name, int name_cap, int* kind, int* loc, int* ndims, long long* dims);
+void* mpas_host_block_field_ptr(void* b, const char* name);
+int mpas_host_block_ncfg(void* b);
+int mpas_host_block_cfg_info(void* b, int idx, char* name, int name_cap, double* value);
+int mpas_host_block_nexch(void* b, int kind, int which);
+int mpas_host_block_exch_info(void* b, int kind, int which, int idx, int* endPoint, int* haloLayer, int* nlist);
+int mpas_host_block_exch_lists(void* b, int kind, int which, int idx, int* srcList, int* destList);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

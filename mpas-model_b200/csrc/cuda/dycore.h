@@ -1,0 +1,83 @@
+// Device-resident dycore driver: the atm_srk3 call sequence (TI:142-1796) over fields that live in HBM.
+#pragma once
+#include <atomic>
+#include <condition_variable>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "halo.h"
+
+namespace mpasb200 {
+
+struct DField {
+    void* dev = nullptr;
+    size_t bytes = 0;
+    int kind = 0;   // 0 real, 1 int
+    int loc = 0;    // 0 none, 1 cell, 2 edge, 3 vertex
+    int inner = 1;  // product of all dims but the last
+    std::vector<long long> dims;
+};
+
+struct DBlock {
+    std::map<std::string, DField> f;
+    std::map<std::string, double> cfg;
+    HaloBlock halo;
+    real* R(const std::string& n);
+    real* Ropt(const std::string& n);
+    int* I(const std::string& n);
+    double c(const std::string& n) const;
+    double c(const std::string& n, double dflt) const;
+    void swap_levels(const std::string& n) { std::swap(f[n + "@1"].dev, f[n + "@2"].dev); }
+};
+
+struct PhaseTimer {
+    double ms = 0;
+    long calls = 0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
+};
+
+struct HostBarrier {
+    std::mutex m;
+    std::condition_variable cv;
+    int count = 0, gen = 0, n = 1;
+    void wait() {
+        std::unique_lock<std::mutex> lk(m);
+        int g = gen;
+        if (++count == n) { count = 0; ++gen; cv.notify_all(); }
+        else cv.wait(lk, [&] { return g != gen; });
+    }
+};
+
+struct Dycore {
+    std::vector<DBlock> blocks;
+    int rank = 0, nranks = 1;
+    Nccl nccl;
+    bool have_comm = false;
+    long nExchanges = 0;
+    bool timing = false;
+    bool aggregate = true;
+    bool use_graph = false;
+    std::map<std::string, PhaseTimer> timers;
+    std::vector<std::string> timer_order;
+    std::vector<cudaEvent_t> event_pool;
+    HostBarrier bar;
+    std::string err;
+    // captured step graph
+    cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};
+    int parity = 0;  // number of steps taken mod 2 (time levels swap every step)
+    real* d_reduce = nullptr;
+};
+
+struct XField {
+    std::string name;
+    int mask;  // halo layer mask, 0 = all
+};
+
+int dycore_exchange(Dycore& m, const std::vector<XField>& fields);
+int dycore_init(Dycore& m);
+int dycore_step(Dycore& m);
+int dycore_call(Dycore& m, const std::string& routine, const double* prm, int nprm);
+
+}  // namespace mpasb200

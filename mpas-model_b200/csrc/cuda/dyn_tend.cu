@@ -1,0 +1,456 @@
+// atm_compute_dyn_tend_work (TI:4481-5416), TI = src/core_atmosphere/dynamics/mpas_atm_time_integration.F.
+//
+// The reference routine is ~25 loop nests with OpenMP barriers between the ones that consume a
+// neighbour's result.  Grouped by those dependences it becomes 4 kernels on every RK stage plus 3
+// on rk_step 1 (forward-Euler mixing terms), each one thread per (k, element) with k fastest:
+//   dt_cell_pre_kernel   all cells   [rk1: Smagorinsky kdiff TI:4677-4720] h_divergence TI:4729-4748
+//                                    [rk1: tend_rho, dpdz TI:4755-4766]
+//   dt_edge_mix_kernel   all edges   rk1: pressure gradient into tend_u_euler TI:4781-4788, del2 u +
+//                                    delsq_u TI:4856-4883
+//   dt_vertex_mix_kernel all verts   rk1: delsq_vorticity TI:4893-4904
+//   dt_cell_mix_kernel   all cells   rk1: delsq_divergence TI:4908-4920, del2 w + delsq_w TI:5097-5128,
+//                                    del2 theta + delsq_theta TI:5276-5300
+//   dt_edge_kernel       owned edges vertical advection of u TI:4792-4807, nonlinear Coriolis TI:4811-4820,
+//                                    KE gradient TI:4823-4838, rk1: del4 u TI:4924-4944, vertical mixing
+//                                    TI:4949-5006, Rayleigh damping TI:5015-5028, final sum TI:5030-5036
+//   dt_cell_w_kernel     owned cells horizontal advection of w TI:5046-5074, rk1: del4 w TI:5134-5154,
+//                                    vertical advection, pgf + buoyancy, final sum TI:5167-5223
+//   dt_cell_theta_kernel owned cells horizontal advection of theta_m TI:5231-5269, rk1: del4 theta
+//                                    TI:5304-5325, vertical advection, diabatic, vertical mixing, final sum
+//                                    TI:5331-5414
+// Every sum over edgesOnCell / edgesOnEdge / advCellsForEdge keeps the reference's index order and
+// is a gather (no atomics), so results are independent of the launch geometry.
+#include "common.cuh"
+
+using namespace mpasb200;
+
+namespace {
+
+struct DtP {
+    int L, mE, mE2, vD, rk_step;
+    int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, edgeSolveStart, edgeSolveEnd, nEdgesSolveLoop;
+    int vertexStart, nVerticesLoop;
+    int mixing, mix_full, rayleigh_damp_u, n_rayleigh_levels;
+    real c_s, len_disp, invDt, cam_coef, h_theta_eddy_visc2_fixed, h_mom_eddy_visc4, h_theta_eddy_visc4, del4u_div_factor;
+    real v_mom_eddy_visc2, v_theta_eddy_visc2, coef_3rd_order, rayleigh_coef_inverse, prandtl_inv;
+    const real *fEdge, *dvEdge, *dcEdge, *invDcEdge, *invDvEdge, *invAreaCell, *invAreaTriangle, *meshScalingDel2, *meshScalingDel4;
+    const real *weightsOnEdge, *zgrid, *rho_edge, *rho_zz, *ru, *u, *v, *divergence, *vorticity, *ke, *pv_edge, *theta_m, *rw;
+    const real *rt_diabatic_tend, *w, *cqw, *rb, *pp, *zz, *zxu, *cqu, *edgesOnCell_sign, *edgesOnVertex_sign, *rw_save, *ru_save;
+    const real *theta_m_save, *rr_save, *angleEdge, *u_init, *v_init, *adv_coefs, *adv_coefs_3rd, *rdzu, *rdzw, *fzm, *fzp, *t_init;
+    const real *defc_a, *defc_b, *qtot, *tend_ru_physics, *tend_rtheta_physics, *tend_rho_physics;
+    const int *cellsOnEdge, *verticesOnEdge, *edgesOnCell, *edgesOnEdge, *edgesOnVertex, *nEdgesOnCell, *nEdgesOnEdge, *advCellsForEdge,
+        *nAdvCellsForEdge;
+    real *tend_u, *tend_rho, *tend_theta, *tend_w, *h_divergence, *kdiff, *tend_u_euler, *tend_w_euler, *tend_theta_euler;
+    real *tend_rtheta_adv, *rthdynten, *delsq_theta, *delsq_w, *delsq_divergence, *delsq_u, *delsq_vorticity, *dpdz;
+};
+
+__global__ void __launch_bounds__(256) dt_cell_pre_kernel(DtP p) {
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    FLAT_KC(p.nCellsLoop, L);
+    const int iCell = p.cellStart + _c0;
+    const size_t ic = IX2(k, iCell, L);
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    real hdiv = 0.0, d_diag = 0.0, d_off_diag = 0.0;
+    const bool smag = (p.rk_step == 1 && p.mixing == 1);
+    for (int i = 1; i <= ne; ++i) {
+        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+        const size_t ie = IX2(k, iEdge, L);
+        const real edge_sign = p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.dvEdge[iEdge - 1];
+        hdiv = hdiv + edge_sign * p.ru[ie];
+        if (smag) {
+            const real a = p.defc_a[IX2(i, iCell, mE)], b = p.defc_b[IX2(i, iCell, mE)];
+            const real ue = p.u[ie], ve = p.v[ie];
+            d_diag = d_diag + a * ue - b * ve;
+            d_off_diag = d_off_diag + b * ue + a * ve;
+        }
+    }
+    hdiv = hdiv * p.invAreaCell[iCell - 1];
+    p.h_divergence[ic] = hdiv;
+    if (p.rk_step == 1) {
+        if (p.mixing == 1 || p.mixing == 2) {
+            real kd;
+            if (p.mixing == 1) {
+                const real cl = (p.c_s * p.len_disp);
+                kd = fmin((cl * cl) * sqrt(d_diag * d_diag + d_off_diag * d_off_diag), ((real)0.01 * (p.len_disp * p.len_disp)) * p.invDt);
+            } else {
+                kd = p.h_theta_eddy_visc2_fixed;
+            }
+            if (p.cam_coef > (real)0.0) {  // TI:4708-4720
+                if (k == L - 2) kd = fmax(kd, (real)2.0833 * p.len_disp * p.cam_coef);
+                if (k == L - 1) kd = fmax(kd, (real)2.0 * (real)2.0833 * p.len_disp * p.cam_coef);
+                if (k == L) kd = fmax(kd, (real)4.0 * (real)2.0833 * p.len_disp * p.cam_coef);
+            }
+            p.kdiff[ic] = kd;
+        } else if (p.cam_coef > (real)0.0) {
+            real kd = p.kdiff[ic];
+            if (k == L - 2) kd = fmax(kd, (real)2.0833 * p.len_disp * p.cam_coef);
+            if (k == L - 1) kd = fmax(kd, (real)2.0 * (real)2.0833 * p.len_disp * p.cam_coef);
+            if (k == L) kd = fmax(kd, (real)4.0 * (real)2.0833 * p.len_disp * p.cam_coef);
+            p.kdiff[ic] = kd;
+        }
+        p.tend_rho[ic] = -hdiv - p.rdzw[k - 1] * (p.rw[IX2(k + 1, iCell, L1)] - p.rw[IX2(k, iCell, L1)]) +
+                         (p.tend_rho_physics ? p.tend_rho_physics[ic] : (real)0.0);
+        const real qt = p.qtot[ic];
+        p.dpdz[ic] = -MPAS_GRAVITY * (p.rb[ic] * (qt) + p.rr_save[ic] * ((real)1. + qt));
+    }
+}
+
+__global__ void __launch_bounds__(256) dt_edge_mix_kernel(DtP p) {  // rk_step == 1 only
+    const int L = p.L;
+    FLAT_KC(p.nEdgesLoop, L);
+    const int iEdge = p.edgeStart + _c0;
+    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    const int vertex1 = p.verticesOnEdge[IX2(1, iEdge, 2)], vertex2 = p.verticesOnEdge[IX2(2, iEdge, 2)];
+    const size_t ie = IX2(k, iEdge, L), i1 = IX2(k, cell1, L), i2 = IX2(k, cell2, L);
+    const real idc = p.invDcEdge[iEdge - 1];
+    real te;
+    if (iEdge >= p.edgeSolveStart && iEdge <= p.edgeSolveEnd) {
+        te = -p.cqu[ie] * ((p.pp[i2] - p.pp[i1]) * idc / ((real).5 * (p.zz[i2] + p.zz[i1])) - (real)0.5 * p.zxu[ie] * (p.dpdz[i1] + p.dpdz[i2]));
+    } else {
+        te = p.tend_u_euler[ie];
+    }
+    const real r_dc = idc;
+    const real r_dv = fmin(p.invDvEdge[iEdge - 1], 4 * idc);
+    const real u_diffusion = (p.divergence[i2] - p.divergence[i1]) * r_dc - (p.vorticity[IX2(k, vertex2, L)] - p.vorticity[IX2(k, vertex1, L)]) * r_dv;
+    p.delsq_u[ie] = (real)0.0 + u_diffusion;
+    const real kdiffu = (real)0.5 * (p.kdiff[i1] + p.kdiff[i2]);
+    te = te + p.rho_edge[ie] * kdiffu * u_diffusion * p.meshScalingDel2[iEdge - 1];
+    p.tend_u_euler[ie] = te;
+}
+
+__global__ void __launch_bounds__(256) dt_vertex_mix_kernel(DtP p) {  // rk_step == 1, h_mom_eddy_visc4 > 0
+    const int L = p.L, vD = p.vD;
+    FLAT_KC(p.nVerticesLoop, L);
+    const int iVertex = p.vertexStart + _c0;
+    real s = 0.0;
+    const real iat = p.invAreaTriangle[iVertex - 1];
+    for (int i = 1; i <= vD; ++i) {
+        const int iEdge = p.edgesOnVertex[IX2(i, iVertex, vD)];
+        const real edge_sign = iat * p.dcEdge[iEdge - 1] * p.edgesOnVertex_sign[IX2(i, iVertex, vD)];
+        s = s + edge_sign * p.delsq_u[IX2(k, iEdge, L)];
+    }
+    p.delsq_vorticity[IX2(k, iVertex, L)] = s;
+}
+
+__global__ void __launch_bounds__(256) dt_cell_mix_kernel(DtP p) {  // rk_step == 1
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    FLAT_KC(p.nCellsLoop, L1);
+    const int iCell = p.cellStart + _c0;
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const real r_areaCell = p.invAreaCell[iCell - 1];
+    if (k == L1) {
+        p.tend_w_euler[IX2(k, iCell, L1)] = 0.0;
+        return;
+    }
+    real dsq_div = 0.0, dsq_w = 0.0, twe = 0.0, dsq_th = 0.0, tte = 0.0;
+    for (int i = 1; i <= ne; ++i) {
+        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+        const real sgn = p.edgesOnCell_sign[IX2(i, iCell, mE)];
+        const real dv = p.dvEdge[iEdge - 1], idc = p.invDcEdge[iEdge - 1];
+        const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+        const size_t ie = IX2(k, iEdge, L), i1 = IX2(k, cell1, L), i2 = IX2(k, cell2, L);
+        const real ms2 = p.meshScalingDel2[iEdge - 1];
+        const real rho_e = p.rho_edge[ie];
+        const real kd1 = p.kdiff[i1], kd2 = p.kdiff[i2];
+        if (p.h_mom_eddy_visc4 > (real)0.0) {
+            const real edge_sign = r_areaCell * dv * sgn;
+            dsq_div = dsq_div + edge_sign * p.delsq_u[ie];
+        }
+        if (k >= 2) {
+            const real edge_sign = (real)0.5 * r_areaCell * sgn * dv * idc;
+            real w_turb_flux = edge_sign * (rho_e + p.rho_edge[IX2(k - 1, iEdge, L)]) * (p.w[IX2(k, cell2, L1)] - p.w[IX2(k, cell1, L1)]);
+            dsq_w = dsq_w + w_turb_flux;
+            w_turb_flux = w_turb_flux * ms2 * (real)0.25 * (kd1 + kd2 + p.kdiff[IX2(k - 1, cell1, L)] + p.kdiff[IX2(k - 1, cell2, L)]);
+            twe = twe + w_turb_flux;
+        }
+        {
+            const real edge_sign = r_areaCell * sgn * dv * idc;
+            const real pr_scale = p.prandtl_inv * ms2;
+            real theta_turb_flux = edge_sign * (p.theta_m[i2] - p.theta_m[i1]) * rho_e;
+            dsq_th = dsq_th + theta_turb_flux;
+            theta_turb_flux = theta_turb_flux * (real)0.5 * (kd1 + kd2) * pr_scale;
+            tte = tte + theta_turb_flux;
+        }
+    }
+    const size_t ic = IX2(k, iCell, L);
+    if (p.h_mom_eddy_visc4 > (real)0.0) p.delsq_divergence[ic] = dsq_div;
+    p.delsq_w[ic] = dsq_w;
+    p.tend_w_euler[IX2(k, iCell, L1)] = twe;
+    p.delsq_theta[ic] = dsq_th;
+    p.tend_theta_euler[ic] = tte;
+}
+
+__device__ __forceinline__ real wduz_at(const DtP& p, int kk, int iEdge, int cell1, int cell2) {
+    const int L = p.L, L1 = L + 1;
+    if (kk == 1 || kk == L1) return (real)0.;
+    const real rwe = (real)0.5 * (p.rw[IX2(kk, cell1, L1)] + p.rw[IX2(kk, cell2, L1)]);
+    if (kk == 2 || kk == L) return rwe * (p.fzm[kk - 1] * p.u[IX2(kk, iEdge, L)] + p.fzp[kk - 1] * p.u[IX2(kk - 1, iEdge, L)]);
+    return flux3(p.u[IX2(kk - 2, iEdge, L)], p.u[IX2(kk - 1, iEdge, L)], p.u[IX2(kk, iEdge, L)], p.u[IX2(kk + 1, iEdge, L)], rwe, (real)1.0);
+}
+
+__global__ void __launch_bounds__(256) dt_edge_kernel(DtP p) {
+    const int L = p.L, L1 = L + 1, mE2 = p.mE2;
+    FLAT_KC(p.nEdgesSolveLoop, L);
+    const int iEdge = p.edgeSolveStart + _c0;
+    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    const size_t ie = IX2(k, iEdge, L), i1 = IX2(k, cell1, L), i2 = IX2(k, cell2, L);
+    const real wlo = wduz_at(p, k, iEdge, cell1, cell2), whi = wduz_at(p, k + 1, iEdge, cell1, cell2);
+    real tu = -p.rdzw[k - 1] * (whi - wlo);
+    real q = 0.0;
+    const int neoe = p.nEdgesOnEdge[iEdge - 1];
+    const real pv_e = p.pv_edge[ie];
+    for (int j = 1; j <= neoe; ++j) {
+        const int eoe = p.edgesOnEdge[IX2(j, iEdge, mE2)];
+        const size_t io = IX2(k, eoe, L);
+        const real workpv = (real)0.5 * (pv_e + p.pv_edge[io]);
+        q = q + p.weightsOnEdge[IX2(j, iEdge, mE2)] * p.u[io] * workpv;
+    }
+    const real ue = p.u[ie], rho_e = p.rho_edge[ie], idc = p.invDcEdge[iEdge - 1];
+    tu = tu + rho_e * (q - (p.ke[i2] - p.ke[i1]) * idc) - ue * (real)0.5 * (p.h_divergence[i1] + p.h_divergence[i2]);
+    real te = p.tend_u_euler[ie];
+    if (p.rk_step == 1) {
+        bool changed = false;
+        if (p.h_mom_eddy_visc4 > (real)0.0) {  // TI:4924-4944
+            const int vertex1 = p.verticesOnEdge[IX2(1, iEdge, 2)], vertex2 = p.verticesOnEdge[IX2(2, iEdge, 2)];
+            const real u_mix_scale = p.meshScalingDel4[iEdge - 1] * p.h_mom_eddy_visc4;
+            const real r_dc = u_mix_scale * p.del4u_div_factor * idc;
+            const real r_dv = u_mix_scale * fmin(p.invDvEdge[iEdge - 1], 4 * idc);
+            const real u_diffusion = rho_e * ((p.delsq_divergence[i2] - p.delsq_divergence[i1]) * r_dc -
+                                              (p.delsq_vorticity[IX2(k, vertex2, L)] - p.delsq_vorticity[IX2(k, vertex1, L)]) * r_dv);
+            te = te - u_diffusion;
+            changed = true;
+        }
+        if (p.v_mom_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:4949-5006
+            real um[3];
+            for (int d = -1; d <= 1; ++d) {
+                const int kk = k + d;
+                real x = p.u[IX2(kk, iEdge, L)];
+                if (!p.mix_full) x = x - p.u_init[kk - 1] * cos(p.angleEdge[iEdge - 1]) - p.v_init[kk - 1] * sin(p.angleEdge[iEdge - 1]);
+                um[d + 1] = x;
+            }
+            const real z1 = (real)0.5 * (p.zgrid[IX2(k - 1, cell1, L1)] + p.zgrid[IX2(k - 1, cell2, L1)]);
+            const real z2 = (real)0.5 * (p.zgrid[IX2(k, cell1, L1)] + p.zgrid[IX2(k, cell2, L1)]);
+            const real z3 = (real)0.5 * (p.zgrid[IX2(k + 1, cell1, L1)] + p.zgrid[IX2(k + 1, cell2, L1)]);
+            const real z4 = (real)0.5 * (p.zgrid[IX2(k + 2, cell1, L1)] + p.zgrid[IX2(k + 2, cell2, L1)]);
+            const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
+            te = te + rho_e * p.v_mom_eddy_visc2 * ((um[2] - um[1]) / (zp - z0) - (um[1] - um[0]) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+            changed = true;
+        }
+        if (changed) p.tend_u_euler[ie] = te;
+    }
+    if (p.rayleigh_damp_u && k >= L - p.n_rayleigh_levels + 1) {  // TI:5015-5028
+        const real coef = (real)(k - (L - p.n_rayleigh_levels)) * p.rayleigh_coef_inverse;
+        tu = tu - rho_e * ue * coef;
+    }
+    p.tend_u[ie] = tu + te + (p.tend_ru_physics ? p.tend_ru_physics[ie] : (real)0.0);
+}
+
+__device__ __forceinline__ real wdwz_at(const DtP& p, int kk, int iCell) {
+    const int L = p.L, L1 = L + 1;
+    if (kk == 1 || kk == L1) return (real)0.0;
+    const real rwk = p.rw[IX2(kk, iCell, L1)], rwkm = p.rw[IX2(kk - 1, iCell, L1)];
+    const real wk = p.w[IX2(kk, iCell, L1)], wkm = p.w[IX2(kk - 1, iCell, L1)];
+    if (kk == 2 || kk == L) return (real)0.25 * (rwk + rwkm) * (wk + wkm);
+    return flux3(p.w[IX2(kk - 2, iCell, L1)], wkm, wk, p.w[IX2(kk + 1, iCell, L1)], (real)0.5 * (rwk + rwkm), (real)1.0);
+}
+
+__global__ void __launch_bounds__(256) dt_cell_w_kernel(DtP p) {
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    FLAT_KC(p.nCellsSolveLoop, L1);
+    const int iCell = p.cellSolveStart + _c0;
+    const size_t iw = IX2(k, iCell, L1);
+    if (k == 1 || k == L1) {
+        p.tend_w[iw] = 0.0;
+        return;
+    }
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const real fm = p.fzm[k - 1], fp = p.fzp[k - 1];
+    const real invArea = p.invAreaCell[iCell - 1];
+    real tw = 0.0;
+    real twe = p.tend_w_euler[iw];
+    const bool del4 = (p.rk_step == 1 && p.h_mom_eddy_visc4 > (real)0.0);
+    for (int i = 1; i <= ne; ++i) {
+        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+        const real sgn = p.edgesOnCell_sign[IX2(i, iCell, mE)];
+        const real ru_edge_w = fm * p.ru[IX2(k, iEdge, L)] + fp * p.ru[IX2(k - 1, iEdge, L)];
+        const real s3 = fsign((real)1.0, ru_edge_w);
+        real flux = 0.0;
+        const int n = p.nAdvCellsForEdge[iEdge - 1];
+        for (int j = 1; j <= n; ++j) {
+            const int iAdvCell = p.advCellsForEdge[IX2(j, iEdge, 15)];
+            const real scalar_weight = p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)];
+            flux = flux + scalar_weight * p.w[IX2(k, iAdvCell, L1)];
+        }
+        tw = tw - sgn * ru_edge_w * flux;
+        if (del4) {  // TI:5134-5154
+            const real r_areaCell = p.h_mom_eddy_visc4 * invArea;
+            const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+            const real edge_sign = p.meshScalingDel4[iEdge - 1] * r_areaCell * p.dvEdge[iEdge - 1] * sgn * p.invDcEdge[iEdge - 1];
+            twe = twe - edge_sign * (p.delsq_w[IX2(k, cell2, L)] - p.delsq_w[IX2(k, cell1, L)]);
+        }
+    }
+    const real flo = wdwz_at(p, k, iCell), fhi = wdwz_at(p, k + 1, iCell);
+    tw = tw * invArea - p.rdzu[k - 1] * (fhi - flo);
+    if (p.rk_step == 1) {
+        const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L);
+        twe = twe - p.cqw[ic] * (p.rdzu[k - 1] * (p.pp[ic] - p.pp[icm]) - (fm * p.dpdz[ic] + fp * p.dpdz[icm]));
+        if (p.v_mom_eddy_visc2 > (real)0.0) {
+            const real wk = p.w[iw];
+            twe = twe + p.v_mom_eddy_visc2 * (real)0.5 * (p.rho_zz[ic] + p.rho_zz[icm]) *
+                            ((p.w[IX2(k + 1, iCell, L1)] - wk) * p.rdzw[k - 1] - (wk - p.w[IX2(k - 1, iCell, L1)]) * p.rdzw[k - 2]) * p.rdzu[k - 1];
+        }
+        p.tend_w_euler[iw] = twe;
+    }
+    p.tend_w[iw] = tw + twe;
+}
+
+__device__ __forceinline__ real wdtz_at(const DtP& p, int kk, int iCell) {
+    const int L = p.L, L1 = L + 1;
+    if (kk == 1 || kk == L1) return (real)0.0;
+    const real fm = p.fzm[kk - 1], fp = p.fzp[kk - 1];
+    const real th_k = p.theta_m[IX2(kk, iCell, L)], th_km = p.theta_m[IX2(kk - 1, iCell, L)];
+    if (kk == L) return p.rw_save[IX2(kk, iCell, L1)] * (fm * th_k + fp * th_km);
+    const real rwk = p.rw[IX2(kk, iCell, L1)];
+    real f;
+    if (kk == 2) f = rwk * (fm * th_k + fp * th_km);
+    else f = flux3(p.theta_m[IX2(kk - 2, iCell, L)], th_km, th_k, p.theta_m[IX2(kk + 1, iCell, L)], rwk, p.coef_3rd_order);
+    return f + (p.rw_save[IX2(kk, iCell, L1)] - rwk) * (fm * p.theta_m_save[IX2(kk, iCell, L)] + fp * p.theta_m_save[IX2(kk - 1, iCell, L)]);
+}
+
+__global__ void __launch_bounds__(256) dt_cell_theta_kernel(DtP p) {
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    FLAT_KC(p.nCellsSolveLoop, L);
+    const int iCell = p.cellSolveStart + _c0;
+    const size_t ic = IX2(k, iCell, L);
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const real invArea = p.invAreaCell[iCell - 1];
+    real tt = 0.0;
+    real tte = p.tend_theta_euler[ic];
+    const bool del4 = (p.rk_step == 1 && p.h_theta_eddy_visc4 > (real)0.0);
+    for (int i = 1; i <= ne; ++i) {
+        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+        const real sgn = p.edgesOnCell_sign[IX2(i, iCell, mE)];
+        const real rue = p.ru[IX2(k, iEdge, L)];
+        const real s3 = fsign((real)1.0, rue);
+        real flux = 0.0;
+        const int n = p.nAdvCellsForEdge[iEdge - 1];
+        for (int j = 1; j <= n; ++j) {
+            const int iAdvCell = p.advCellsForEdge[IX2(j, iEdge, 15)];
+            const real scalar_weight = p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)];
+            flux = flux + scalar_weight * p.theta_m[IX2(k, iAdvCell, L)];
+        }
+        tt = tt - sgn * rue * flux;
+    }
+    if (p.rk_step > 1) {  // TI:5256-5269
+        for (int i = 1; i <= ne; ++i) {
+            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+            const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+            const size_t ie = IX2(k, iEdge, L);
+            const real flux = p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.dvEdge[iEdge - 1] * (p.ru_save[ie] - p.ru[ie]) * (real)0.5 *
+                              (p.theta_m_save[IX2(k, cell2, L)] + p.theta_m_save[IX2(k, cell1, L)]);
+            tt = tt - flux;
+        }
+    }
+    if (del4) {  // TI:5304-5325
+        const real r_areaCell = p.h_theta_eddy_visc4 * p.prandtl_inv * invArea;
+        for (int i = 1; i <= ne; ++i) {
+            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+            const real edge_sign = p.meshScalingDel4[iEdge - 1] * r_areaCell * p.dvEdge[iEdge - 1] * p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.invDcEdge[iEdge - 1];
+            const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+            tte = tte - edge_sign * (p.delsq_theta[IX2(k, cell2, L)] - p.delsq_theta[IX2(k, cell1, L)]);
+        }
+    }
+    const real flo = wdtz_at(p, k, iCell), fhi = wdtz_at(p, k + 1, iCell);
+    tt = tt * invArea - p.rdzw[k - 1] * (fhi - flo);
+    const real rho = p.rho_zz[ic];
+    if (p.tend_rtheta_adv) p.tend_rtheta_adv[ic] = tt;
+    if (p.rthdynten) p.rthdynten[ic] = tt / rho;
+    tt = tt + rho * (p.rt_diabatic_tend ? p.rt_diabatic_tend[ic] : (real)0.0);
+    if (p.rk_step == 1 && p.v_theta_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:5360-5406
+        const real z1 = p.zgrid[IX2(k - 1, iCell, L1)], z2 = p.zgrid[IX2(k, iCell, L1)], z3 = p.zgrid[IX2(k + 1, iCell, L1)], z4 = p.zgrid[IX2(k + 2, iCell, L1)];
+        const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
+        real a = p.theta_m[IX2(k + 1, iCell, L)], b = p.theta_m[ic], c = p.theta_m[IX2(k - 1, iCell, L)];
+        if (p.mix_full) {
+            tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * ((a - b) / (zp - z0) - (b - c) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+        } else {
+            const real ta = p.t_init[IX2(k + 1, iCell, L)], tb = p.t_init[ic], tc = p.t_init[IX2(k - 1, iCell, L)];
+            tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * (((a - ta) - (b - tb)) / (zp - z0) - ((b - tb) - (c - tc)) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+        }
+    }
+    if (p.rk_step == 1 && (del4 || p.v_theta_eddy_visc2 > (real)0.0)) p.tend_theta_euler[ic] = tte;
+    p.tend_theta[ic] = tt + tte + (p.tend_rtheta_physics ? p.tend_rtheta_physics[ic] : (real)0.0);
+}
+
+}  // namespace
+
+extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
+    (void)nCells; (void)nEdges; (void)nVertices; (void)nCellsSolve; (void)nEdgesSolve; (void)num_scalars; (void)moist_start; (void)moist_end;
+    (void)fEdge; (void)rr; (void)pressure_b; (void)exner; (void)scalars; (void)deriv_two; (void)cellsOnCell; (void)latCell; (void)latEdge;
+    (void)qv_init; (void)r_earth; (void)ur_cell; (void)vr_cell; (void)tend_w_pgf; (void)tend_w_buoy; (void)vertexSolveStart; (void)vertexSolveEnd;
+    if (nVertLevels < 4) return fail_msg("mpas_b200_compute_dyn_tend_work: nVertLevels must be >= 4");
+    if (vertexDegree != 3) return fail_msg("mpas_b200_compute_dyn_tend_work: vertexDegree must be 3");
+    DtP p;
+    p.L = nVertLevels; p.mE = maxEdges; p.mE2 = maxEdges2; p.vD = vertexDegree; p.rk_step = rk_step;
+    p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
+    p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.edgeSolveStart = edgeSolveStart; p.edgeSolveEnd = edgeSolveEnd;
+    p.nEdgesSolveLoop = edgeSolveEnd - edgeSolveStart + 1; p.vertexStart = vertexStart; p.nVerticesLoop = vertexEnd - vertexStart + 1;
+    p.mixing = config_horiz_mixing; p.mix_full = config_mix_full; p.rayleigh_damp_u = config_rayleigh_damp_u;
+    p.n_rayleigh_levels = config_number_rayleigh_damp_u_levels;
+    p.c_s = c_s; p.len_disp = config_len_disp; p.invDt = (real)1.0 / dt; p.cam_coef = config_mpas_cam_coef;
+    p.h_theta_eddy_visc2_fixed = config_h_theta_eddy_visc2; p.del4u_div_factor = config_del4u_div_factor;
+    p.h_mom_eddy_visc4 = 0.0; p.h_theta_eddy_visc4 = 0.0;
+    if (rk_step == 1) {  // TI:4697-4704: locals set only on the first RK stage
+        if (config_horiz_mixing == 1) {
+            p.h_mom_eddy_visc4 = config_visc4_2dsmag * (config_len_disp * config_len_disp * config_len_disp);
+            p.h_theta_eddy_visc4 = p.h_mom_eddy_visc4;
+        } else if (config_horiz_mixing == 2) {
+            p.h_mom_eddy_visc4 = config_h_mom_eddy_visc4;
+            p.h_theta_eddy_visc4 = config_h_theta_eddy_visc4;
+        }
+    }
+    (void)config_h_mom_eddy_visc2;
+    p.v_mom_eddy_visc2 = config_v_mom_eddy_visc2; p.v_theta_eddy_visc2 = config_v_theta_eddy_visc2; p.coef_3rd_order = coef_3rd_order;
+    p.rayleigh_coef_inverse = config_rayleigh_damp_u
+                                  ? (real)1.0 / ((real)config_number_rayleigh_damp_u_levels * (config_rayleigh_damp_u_timescale_days * (real)86400.0))
+                                  : (real)0.0;
+    p.prandtl_inv = (real)1.0 / MPAS_PRANDTL;
+    p.fEdge = X(fEdge); p.dvEdge = X(dvEdge); p.dcEdge = X(dcEdge); p.invDcEdge = X(invDcEdge); p.invDvEdge = X(invDvEdge); p.invAreaCell = X(invAreaCell);
+    p.invAreaTriangle = X(invAreaTriangle); p.meshScalingDel2 = X(meshScalingDel2); p.meshScalingDel4 = X(meshScalingDel4);
+    p.weightsOnEdge = X(weightsOnEdge); p.zgrid = X(zgrid); p.rho_edge = X(rho_edge); p.rho_zz = X(rho_zz); p.ru = X(ru); p.u = X(u); p.v = X(v);
+    p.divergence = X(divergence); p.vorticity = X(vorticity); p.ke = X(ke); p.pv_edge = X(pv_edge); p.theta_m = X(theta_m); p.rw = X(rw);
+    p.rt_diabatic_tend = X(rt_diabatic_tend); p.w = X(w); p.cqw = X(cqw); p.rb = X(rb); p.pp = X(pp); p.zz = X(zz); p.zxu = X(zxu); p.cqu = X(cqu);
+    p.edgesOnCell_sign = X(edgesOnCell_sign); p.edgesOnVertex_sign = X(edgesOnVertex_sign); p.rw_save = X(rw_save); p.ru_save = X(ru_save);
+    p.theta_m_save = X(theta_m_save); p.rr_save = X(rr_save); p.angleEdge = X(angleEdge); p.u_init = X(u_init); p.v_init = X(v_init);
+    p.adv_coefs = X(adv_coefs); p.adv_coefs_3rd = X(adv_coefs_3rd); p.rdzu = X(rdzu); p.rdzw = X(rdzw); p.fzm = X(fzm); p.fzp = X(fzp); p.t_init = X(t_init);
+    p.defc_a = X(defc_a); p.defc_b = X(defc_b); p.qtot = X(qtot); p.tend_ru_physics = X(tend_ru_physics); p.tend_rtheta_physics = X(tend_rtheta_physics);
+    p.tend_rho_physics = X(tend_rho_physics);
+    p.cellsOnEdge = X(cellsOnEdge); p.verticesOnEdge = X(verticesOnEdge); p.edgesOnCell = X(edgesOnCell); p.edgesOnEdge = X(edgesOnEdge);
+    p.edgesOnVertex = X(edgesOnVertex); p.nEdgesOnCell = X(nEdgesOnCell); p.nEdgesOnEdge = X(nEdgesOnEdge); p.advCellsForEdge = X(advCellsForEdge);
+    p.nAdvCellsForEdge = X(nAdvCellsForEdge);
+    p.tend_u = X(tend_u); p.tend_rho = X(tend_rho); p.tend_theta = X(tend_theta); p.tend_w = X(tend_w); p.h_divergence = X(h_divergence); p.kdiff = X(kdiff);
+    p.tend_u_euler = X(tend_u_euler); p.tend_w_euler = X(tend_w_euler); p.tend_theta_euler = X(tend_theta_euler); p.tend_rtheta_adv = X(tend_rtheta_adv);
+    p.rthdynten = X(rthdynten); p.delsq_theta = X(delsq_theta); p.delsq_w = X(delsq_w); p.delsq_divergence = X(delsq_divergence); p.delsq_u = X(delsq_u);
+    p.delsq_vorticity = X(delsq_vorticity); p.dpdz = X(dpdz);
+    if (!p.mix_full && (p.v_mom_eddy_visc2 > 0 || p.v_theta_eddy_visc2 > 0) && (!u_init || !v_init || !angleEdge || !t_init))
+        return fail_msg("mpas_b200_compute_dyn_tend_work: config_mix_full=false needs u_init, v_init, angleEdge, t_init");
+    const int L = p.L;
+    KLAUNCH(dt_cell_pre_kernel, (long long)p.nCellsLoop * L, 256, p);
+    KCHECK("dt_cell_pre_kernel");
+    if (rk_step == 1) {
+        KLAUNCH(dt_edge_mix_kernel, (long long)p.nEdgesLoop * L, 256, p);
+        KCHECK("dt_edge_mix_kernel");
+        if (p.h_mom_eddy_visc4 > (real)0.0) {
+            KLAUNCH(dt_vertex_mix_kernel, (long long)p.nVerticesLoop * L, 256, p);
+            KCHECK("dt_vertex_mix_kernel");
+        }
+        KLAUNCH(dt_cell_mix_kernel, (long long)p.nCellsLoop * (L + 1), 256, p);
+        KCHECK("dt_cell_mix_kernel");
+    }
+    KLAUNCH(dt_edge_kernel, (long long)p.nEdgesSolveLoop * L, 256, p);
+    KCHECK("dt_edge_kernel");
+    KLAUNCH(dt_cell_w_kernel, (long long)p.nCellsSolveLoop * (L + 1), 256, p);
+    KCHECK("dt_cell_w_kernel");
+    KLAUNCH(dt_cell_theta_kernel, (long long)p.nCellsSolveLoop * L, 256, p);
+    KCHECK("dt_cell_theta_kernel");
+    return 0;
+}

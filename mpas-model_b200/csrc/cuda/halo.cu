@@ -1,0 +1,202 @@
+// Halo exchange layer (see halo.h): plan construction from the reference-order exchange lists,
+// pack / unpack kernels, NCCL binding through dlopen.
+#include "halo.h"
+
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cstring>
+#include <set>
+
+namespace mpasb200 {
+
+namespace {
+
+// buf[pos[e] + j] = array[(idx[e]-1)*inner + j]   (PACK)   or the reverse (UNPACK); j fastest
+template <bool PACK>
+__global__ void __launch_bounds__(256) halo_copy_kernel(real* __restrict__ array, real* __restrict__ buf, const int* __restrict__ idx,
+                                                        const long long* __restrict__ pos, long long n, int inner) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * inner) return;
+    const long long e = t / inner;
+    const int j = (int)(t - e * inner);
+    const size_t ia = (size_t)(idx[e] - 1) * inner + j;
+    const size_t ib = (size_t)pos[e] + j;
+    if (PACK) buf[ib] = array[ia];
+    else array[ia] = buf[ib];
+}
+
+bool layer_selected(int mask, int layer) { return mask == 0 || (mask & (1 << (layer - 1))); }
+
+void build_side(const std::vector<HaloItem>& items, const std::vector<HaloList> lists[4], bool is_send, HaloSide& side) {
+    std::set<int> nb;
+    for (const HaloItem& it : items)
+        for (const HaloList& l : lists[it.loc])
+            if (layer_selected(it.mask, l.layer) && !l.src.empty()) nb.insert(l.endPoint);
+    side.nbr.assign(nb.begin(), nb.end());
+    const size_t nI = items.size();
+    std::vector<std::vector<int>> idx(nI);
+    std::vector<std::vector<long long>> pos(nI);
+    long long cursor = 0;
+    for (int n : side.nbr) {
+        side.off.push_back(cursor);
+        for (size_t i = 0; i < nI; ++i) {
+            const HaloItem& it = items[i];
+            // layers ascending; lists are stored sorted by (endPoint, layer) but do not rely on it
+            std::vector<const HaloList*> sel;
+            for (const HaloList& l : lists[it.loc])
+                if (l.endPoint == n && layer_selected(it.mask, l.layer)) sel.push_back(&l);
+            std::sort(sel.begin(), sel.end(), [](const HaloList* a, const HaloList* b) { return a->layer < b->layer; });
+            for (const HaloList* l : sel) {
+                for (size_t e = 0; e < l->src.size(); ++e) {
+                    // send: array(:, srcList) -> buffer slot destList ; recv: buffer slot srcList -> array(:, destList)
+                    const int local = is_send ? l->src[e] : l->dest[e];
+                    const int slot = is_send ? l->dest[e] : l->src[e];
+                    idx[i].push_back(local);
+                    pos[i].push_back(cursor + (long long)(slot - 1) * it.inner);
+                }
+                cursor += (long long)l->src.size() * it.inner;
+            }
+        }
+        side.cnt.push_back(cursor - side.off.back());
+    }
+    side.total = cursor;
+    for (size_t i = 0; i < nI; ++i) {
+        int* di = nullptr;
+        long long* dp = nullptr;
+        side.n.push_back((long long)idx[i].size());
+        if (!idx[i].empty()) {
+            cudaMalloc(&di, idx[i].size() * sizeof(int));
+            cudaMalloc(&dp, pos[i].size() * sizeof(long long));
+            cudaMemcpy(di, idx[i].data(), idx[i].size() * sizeof(int), cudaMemcpyHostToDevice);
+            cudaMemcpy(dp, pos[i].data(), pos[i].size() * sizeof(long long), cudaMemcpyHostToDevice);
+        }
+        side.d_idx.push_back(di);
+        side.d_pos.push_back(dp);
+    }
+    if (side.total > 0) cudaMalloc(&side.d_buf, side.total * sizeof(real));
+}
+
+void free_side(HaloSide& s) {
+    for (int* p : s.d_idx) cudaFree(p);
+    for (long long* p : s.d_pos) cudaFree(p);
+    cudaFree(s.d_buf);
+}
+
+}  // namespace
+
+HaloPlan* halo_build_plan(HaloBlock& blk, const std::vector<HaloItem>& items) {
+    HaloPlan* p = new HaloPlan();
+    p->items = items;
+    build_side(items, blk.send, true, p->send);
+    build_side(items, blk.recv, false, p->recv);
+    return p;
+}
+
+void halo_free_plan(HaloPlan* p) {
+    if (!p) return;
+    free_side(p->send);
+    free_side(p->recv);
+    delete p;
+}
+
+int halo_pack(HaloPlan* p) {
+    for (size_t i = 0; i < p->items.size(); ++i) {
+        const long long n = p->send.n[i];
+        if (n == 0) continue;
+        const HaloItem& it = p->items[i];
+        halo_copy_kernel<true><<<cdiv(n * it.inner, 256), 256, 0, stream()>>>(it.array, p->send.d_buf, p->send.d_idx[i], p->send.d_pos[i], n, it.inner);
+        count_launch();
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("halo_pack", e);
+    return 0;
+}
+
+int halo_unpack(HaloPlan* p) {
+    for (size_t i = 0; i < p->items.size(); ++i) {
+        const long long n = p->recv.n[i];
+        if (n == 0) continue;
+        const HaloItem& it = p->items[i];
+        halo_copy_kernel<false><<<cdiv(n * it.inner, 256), 256, 0, stream()>>>(it.array, p->recv.d_buf, p->recv.d_idx[i], p->recv.d_pos[i], n, it.inner);
+        count_launch();
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("halo_unpack", e);
+    return 0;
+}
+
+// ---- NCCL via dlopen ------------------------------------------------------------------------
+namespace {
+typedef struct { char internal[128]; } nccl_uid;  // ncclUniqueId (nccl.h: NCCL_UNIQUE_ID_BYTES 128)
+typedef int (*fn_getuid)(nccl_uid*);
+typedef int (*fn_initrank)(void**, int, nccl_uid, int);
+typedef int (*fn_void)();
+typedef int (*fn_sendrecv)(void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_allreduce)(const void*, void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*fn_destroy)(void*);
+typedef const char* (*fn_errstr)(int);
+fn_getuid p_getuid;
+fn_initrank p_initrank;
+fn_void p_gstart, p_gend;
+fn_sendrecv p_send, p_recv;
+fn_allreduce p_allreduce;
+fn_destroy p_destroy;
+fn_errstr p_errstr;
+int g_nccl_rc = 0;
+#ifdef SINGLE_PRECISION
+const int NCCL_REAL = 7;  // ncclFloat32
+#else
+const int NCCL_REAL = 8;  // ncclFloat64
+#endif
+}  // namespace
+
+bool Nccl::load(std::string& err) {
+    if (lib) return true;
+    // prefer a libnccl already mapped into the process (torch's bundled one) so only one copy is live
+    const char* names[] = {"libnccl.so.2", "libnccl.so"};
+    for (const char* n : names) {
+        lib = dlopen(n, RTLD_NOW | RTLD_GLOBAL);
+        if (lib) break;
+    }
+    if (!lib) {
+        err = std::string("cannot dlopen libnccl: ") + dlerror();
+        return false;
+    }
+    p_getuid = (fn_getuid)dlsym(lib, "ncclGetUniqueId");
+    p_initrank = (fn_initrank)dlsym(lib, "ncclCommInitRank");
+    p_gstart = (fn_void)dlsym(lib, "ncclGroupStart");
+    p_gend = (fn_void)dlsym(lib, "ncclGroupEnd");
+    p_send = (fn_sendrecv)dlsym(lib, "ncclSend");
+    p_recv = (fn_sendrecv)dlsym(lib, "ncclRecv");
+    p_allreduce = (fn_allreduce)dlsym(lib, "ncclAllReduce");
+    p_destroy = (fn_destroy)dlsym(lib, "ncclCommDestroy");
+    p_errstr = (fn_errstr)dlsym(lib, "ncclGetErrorString");
+    if (!p_getuid || !p_initrank || !p_gstart || !p_gend || !p_send || !p_recv || !p_destroy) {
+        err = "libnccl lacks a required symbol";
+        return false;
+    }
+    return true;
+}
+int Nccl::get_unique_id(void* id128) { return g_nccl_rc = p_getuid((nccl_uid*)id128); }
+int Nccl::init_rank(const void* id128, int nranks_, int rank_) {
+    nccl_uid id;
+    std::memcpy(&id, id128, sizeof(id));
+    rank = rank_;
+    nranks = nranks_;
+    return g_nccl_rc = p_initrank(&comm, nranks_, id, rank_);
+}
+int Nccl::group_start() { return g_nccl_rc = p_gstart(); }
+int Nccl::group_end() { return g_nccl_rc = p_gend(); }
+int Nccl::send(const void* buf, size_t count, int peer, cudaStream_t s) { return g_nccl_rc = p_send((void*)buf, count, NCCL_REAL, peer, comm, s); }
+int Nccl::recv(void* buf, size_t count, int peer, cudaStream_t s) { return g_nccl_rc = p_recv(buf, count, NCCL_REAL, peer, comm, s); }
+int Nccl::allreduce_max(const void* in, void* out, size_t count, cudaStream_t s) {
+    return g_nccl_rc = p_allreduce(in, out, count, NCCL_REAL, 2 /* ncclMax */, comm, s);
+}
+void Nccl::destroy() {
+    if (comm && p_destroy) p_destroy(comm);
+    comm = nullptr;
+}
+const char* Nccl::last_error() { return p_errstr ? p_errstr(g_nccl_rc) : "nccl error"; }
+
+}  // namespace mpasb200

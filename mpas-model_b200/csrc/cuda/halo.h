@@ -1,0 +1,74 @@
+// Halo exchange layer: replaces mpas_dmpar_exch_halo_field (src/framework/mpas_dmpar.F:5386-5552 2-D real,
+// :5565-5748 3-D real) with persistent device index tables, packed device buffers and either NCCL
+// grouped send/recv over NVLink (one process per GPU) or device-to-device copies (several blocks in one
+// process: the reference's own no-MPI path, mpas_dmpar.F:5481-5504).
+//
+// Message layout per (sender, receiver): for each field of the exchange group, for each selected halo
+// layer in ascending order, the elements of that layer's exchange list at position (destList-1)*inner
+// (sender) / (srcList-1)*inner (receiver), exactly the reference's buffer addressing (mpas_dmpar.F:5462,
+// 5521) -- i.e. ascending global ID within a layer (mpas_dmpar.F:1782-1784, 1861-1867).
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+
+namespace mpasb200 {
+
+struct HaloList {  // one reference exchange list (mpas_dmpar_types.inc mpas_exchange_list)
+    int endPoint, layer;
+    std::vector<int> src, dest;  // 1-based, reference semantics (see decomp.h)
+};
+
+struct HaloItem {  // one field of an exchange group
+    real* array;
+    int loc;    // 1 cell, 2 edge, 3 vertex
+    int inner;  // product of the dimensions in front of the decomposed one
+    int mask;   // bit (l-1) set = exchange halo layer l; 0 = all layers
+};
+
+struct HaloSide {                      // send or recv side of a plan
+    std::vector<int> nbr;              // neighbour block ids, ascending
+    std::vector<long long> off, cnt;   // per neighbour: offset / count in the packed buffer (elements)
+    std::vector<int*> d_idx;           // per item: local element index (1-based) per list element
+    std::vector<long long*> d_pos;     // per item: buffer offset (elements) per list element
+    std::vector<long long> n;          // per item: number of list elements
+    real* d_buf = nullptr;
+    long long total = 0;
+};
+
+struct HaloPlan {
+    std::vector<HaloItem> items;
+    HaloSide send, recv;
+};
+
+struct HaloBlock {  // exchange lists of one block, by location (index 1..3)
+    int blockID = 0;
+    std::vector<HaloList> send[4], recv[4];
+    std::map<std::string, HaloPlan*> plans;
+};
+
+// NCCL through dlopen (no link-time dependency; a single-GPU run never loads it)
+struct Nccl {
+    void* lib = nullptr;
+    void* comm = nullptr;
+    int rank = 0, nranks = 1;
+    bool load(std::string& err);
+    int get_unique_id(void* id128);                    // fills 128 bytes
+    int init_rank(const void* id128, int nranks, int rank);
+    int group_start();
+    int group_end();
+    int send(const void* buf, size_t count, int peer, cudaStream_t s);
+    int recv(void* buf, size_t count, int peer, cudaStream_t s);
+    int allreduce_max(const void* in, void* out, size_t count, cudaStream_t s);
+    void destroy();
+    const char* last_error();
+};
+
+HaloPlan* halo_build_plan(HaloBlock& blk, const std::vector<HaloItem>& items);
+void halo_free_plan(HaloPlan* p);
+int halo_pack(HaloPlan* p);    // launches the pack kernels on stream()
+int halo_unpack(HaloPlan* p);  // launches the unpack kernels on stream()
+
+}  // namespace mpasb200

@@ -1,0 +1,147 @@
+// Library lifecycle and the host-array <-> device-mirror registry behind the drop-in C ABI
+// (SURVEY.md section 8b "Lifecycle"; no reference analogue -- the reference owns its arrays through
+// mpas_pool_type, src/framework/mpas_pool_routines.F:4282, and never leaves the host).
+// A Fortran host registers each pool array once (mpas_b200_register_field), uploads it, then calls
+// the *_work entry points with the SAME host addresses it always passed; every entry point maps
+// them to the device mirrors.  Device pointers pass through untouched, so the device-resident
+// dycore driver (dycore.cu) uses the identical entry points.
+#include <cstdio>
+#include <map>
+#include <mutex>
+
+#include "common.cuh"
+
+namespace mpas {
+extern std::string g_last_error;  // host_api.cpp
+}
+
+namespace mpasb200 {
+
+namespace {
+struct Mirror {
+    size_t bytes;
+    void* dev;
+};
+std::map<uintptr_t, Mirror> g_reg;  // host base address -> mirror
+std::mutex g_mu;
+cudaStream_t g_stream = nullptr;
+bool g_own_stream = false;
+long long g_launches = 0;
+}  // namespace
+
+cudaStream_t stream() {
+    if (!g_stream) {
+        cudaStreamCreateWithFlags(&g_stream, cudaStreamNonBlocking);
+        g_own_stream = true;
+    }
+    return g_stream;
+}
+void set_stream(cudaStream_t s) {
+    if (g_own_stream && g_stream) cudaStreamDestroy(g_stream);
+    g_stream = s;
+    g_own_stream = false;
+}
+int fail(const char* where, cudaError_t e) {
+    mpas::g_last_error = std::string(where) + ": " + cudaGetErrorString(e);
+    return 1000 + (int)e;
+}
+int fail_msg(const std::string& msg) {
+    mpas::g_last_error = msg;
+    return 1;
+}
+long long launches() { return g_launches; }
+void count_launch(int n) { g_launches += n; }
+
+void* xlate(const void* p) {
+    if (!p || g_reg.empty()) return (void*)p;
+    uintptr_t a = (uintptr_t)p;
+    auto it = g_reg.upper_bound(a);
+    if (it == g_reg.begin()) return (void*)p;
+    --it;
+    if (a < it->first + it->second.bytes) return (char*)it->second.dev + (a - it->first);
+    return (void*)p;
+}
+
+}  // namespace mpasb200
+
+using namespace mpasb200;
+
+extern "C" {
+
+// Select the CUDA device of this rank (one process per GPU) and create the library stream.
+int mpas_b200_set_device(int device) {
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return fail("mpas_b200_set_device", e);
+    stream();
+    return 0;
+}
+
+int mpas_b200_device_count() {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+// Register a host array (any pool array of SURVEY.md Appendix D): allocates its device mirror.
+int mpas_b200_register_field(const void* host, size_t bytes) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    uintptr_t a = (uintptr_t)host;
+    auto it = g_reg.find(a);
+    if (it != g_reg.end()) {
+        if (it->second.bytes == bytes) return 0;
+        cudaFree(it->second.dev);
+        g_reg.erase(it);
+    }
+    Mirror m;
+    m.bytes = bytes;
+    cudaError_t e = cudaMalloc(&m.dev, bytes ? bytes : 8);
+    if (e != cudaSuccess) return fail("mpas_b200_register_field", e);
+    g_reg[a] = m;
+    return 0;
+}
+
+int mpas_b200_unregister_field(const void* host) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    auto it = g_reg.find((uintptr_t)host);
+    if (it == g_reg.end()) return fail_msg("mpas_b200_unregister_field: address not registered");
+    cudaFree(it->second.dev);
+    g_reg.erase(it);
+    return 0;
+}
+
+// host -> device mirror (asynchronous on the library stream when the host memory is pinned)
+int mpas_b200_upload(const void* host) {
+    auto it = g_reg.find((uintptr_t)host);
+    if (it == g_reg.end()) return fail_msg("mpas_b200_upload: address not registered");
+    cudaError_t e = cudaMemcpyAsync(it->second.dev, host, it->second.bytes, cudaMemcpyHostToDevice, stream());
+    if (e != cudaSuccess) return fail("mpas_b200_upload", e);
+    return 0;
+}
+
+// device mirror -> host (the reference's sync point before output / restart / physics)
+int mpas_b200_download(void* host) {
+    auto it = g_reg.find((uintptr_t)host);
+    if (it == g_reg.end()) return fail_msg("mpas_b200_download: address not registered");
+    cudaError_t e = cudaMemcpyAsync(host, it->second.dev, it->second.bytes, cudaMemcpyDeviceToHost, stream());
+    if (e != cudaSuccess) return fail("mpas_b200_download", e);
+    return 0;
+}
+
+void* mpas_b200_device_ptr(const void* host) { return xlate(host); }
+
+int mpas_b200_synchronize() {
+    cudaError_t e = cudaStreamSynchronize(stream());
+    if (e != cudaSuccess) return fail("mpas_b200_synchronize", e);
+    return 0;
+}
+
+long long mpas_b200_launch_count() { return launches(); }
+
+int mpas_b200_finalize() {
+    std::lock_guard<std::mutex> lk(g_mu);
+    for (auto& kv : g_reg) cudaFree(kv.second.dev);
+    g_reg.clear();
+    return 0;
+}
+
+}  // extern "C"

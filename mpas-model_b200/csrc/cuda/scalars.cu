@@ -1,0 +1,434 @@
+// Scalar transport: atm_advance_scalars_work (TI:3238-3506) and the flux-corrected monotonic
+// atm_advance_scalars_mono_work (TI:3612-4214).  TI = src/core_atmosphere/dynamics/mpas_atm_time_integration.F.
+//
+// scalars arrays are (num_scalars, nVertLevels, nCells+1) with the scalar index fastest (TI:3685).
+//
+// advance_scalars:   as_edge_kernel (q,k,edge)   high-order horizontal flux for every scalar   TI:3330-3387
+//                    as_cell_kernel (q,k,cell)   flux divergence + vertical flux3 + update     TI:3400-3500
+// mono, once:        mono_pre_kernel             scalars_old += dt*tend/rho, tend = 0          TI:3737-3752
+//                    mono_rho_int_kernel         rho_zz_int                                    TI:3772-3792
+//       per scalar:  mono_copy_kernel            2-D working copies                            TI:3800-3812
+//                    mono_bounds_kernel          vertical hi-order flux wdtn, s_min/s_max      TI:3843-3908
+//                    mono_edge_flux_kernel       flux_arr (hi-order), flux_upwind_tmp, flux_tmp TI:3916-3961, 4007-4022
+//                    mono_limiter_kernel         upwind update + scale factors                 TI:3969-4000, 4024-4076
+//                    [halo exchange of scale_arr, TI:4098]
+//                    mono_rescale_edge_kernel    limited horizontal fluxes                     TI:4102-4138
+//                    mono_update_kernel          limited vertical fluxes, final update, store  TI:4145-4210
+// One thread per (k, element) everywhere; all neighbour sums are gathers in the reference's order.
+#include "common.cuh"
+
+using namespace mpasb200;
+
+namespace {
+
+const bool config_apply_lbcs = false;  // regional LBCs are out of scope
+
+struct AsP {
+    int L, mE, ns, edgeStart, nEdgesLoop, cellSolveStart, nCellsSolveLoop;
+    real dt, coef_3rd_order, weight_time_old, weight_time_new;
+    const real *scalar_old, *rho_zz_old, *rho_zz_new, *uhAvg, *wwAvg, *edgesOnCell_sign, *invAreaCell, *fnm, *fnp, *rdnw, *adv_coefs, *adv_coefs_3rd;
+    const int *edgesOnCell, *nEdgesOnCell, *bdyMaskCell, *bdyMaskEdge, *nAdvCellsForEdge, *advCellsForEdge;
+    const real* scalar_tend_save;
+    real *scalar_new, *horiz_flux_arr;
+};
+
+__global__ void __launch_bounds__(256) as_edge_kernel(AsP p) {
+    const int L = p.L, ns = p.ns;
+    FLAT_KC(p.nEdgesLoop, L * ns);
+    const int iEdge = p.edgeStart + _c0;
+    if (config_apply_lbcs && !(p.bdyMaskEdge[iEdge - 1] < MPAS_NRELAXZONE - 1)) return;
+    const int kk = (k - 1) / ns + 1, q = (k - 1) % ns + 1;
+    const int n = p.nAdvCellsForEdge[iEdge - 1];
+    const real s3 = fsign((real)1.0, p.uhAvg[IX2(kk, iEdge, L)]);
+    real s;
+    if (n == 10) {  // TI:3339-3360: first term assigned, not added to zero
+        s = (p.adv_coefs[IX2(1, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(1, iEdge, 15)]) * p.scalar_new[IX3(q, kk, p.advCellsForEdge[IX2(1, iEdge, 15)], ns, L)];
+        for (int j = 2; j <= 10; ++j)
+            s = s + (p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)]) * p.scalar_new[IX3(q, kk, p.advCellsForEdge[IX2(j, iEdge, 15)], ns, L)];
+    } else {
+        s = 0.0;
+        for (int j = 1; j <= n; ++j) {
+            const real scalar_weight = p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)];
+            s = s + scalar_weight * p.scalar_new[IX3(q, kk, p.advCellsForEdge[IX2(j, iEdge, 15)], ns, L)];
+        }
+    }
+    p.horiz_flux_arr[IX3(q, kk, iEdge, ns, L)] = s;
+}
+
+__device__ __forceinline__ real as_wdtn_at(const AsP& p, int q, int kk, int iCell) {
+    const int L = p.L, L1 = L + 1, ns = p.ns;
+    if (kk == 1 || kk == L1) return (real)0.0;
+    const real ww = p.wwAvg[IX2(kk, iCell, L1)];
+    if (kk == 2 || kk == L) return ww * (p.fnm[kk - 1] * p.scalar_new[IX3(q, kk, iCell, ns, L)] + p.fnp[kk - 1] * p.scalar_new[IX3(q, kk - 1, iCell, ns, L)]);
+    return flux3(p.scalar_new[IX3(q, kk - 2, iCell, ns, L)], p.scalar_new[IX3(q, kk - 1, iCell, ns, L)], p.scalar_new[IX3(q, kk, iCell, ns, L)],
+                 p.scalar_new[IX3(q, kk + 1, iCell, ns, L)], ww, p.coef_3rd_order);
+}
+
+// Each thread writes scalar_new(q,k,iCell) while its vertical neighbours read it, and the reference
+// evaluates every flux of a column from the pre-update values (TI:3436-3470 fill wdtn for the whole
+// column before TI:3474-3500 updates).  A block therefore owns AS_COLS whole columns: all results go
+// to shared memory first, the block synchronises, then they are stored.
+#define AS_COLS 8
+__global__ void __launch_bounds__(256) as_cell_kernel(AsP p) {
+    extern __shared__ real as_hold[];
+    const int L = p.L, mE = p.mE, ns = p.ns;
+    const int n = L * ns;
+    const int col0 = blockIdx.x * AS_COLS;
+    const int ncols = min(AS_COLS, p.nCellsSolveLoop - col0);
+    for (int t = threadIdx.x; t < ncols * n; t += blockDim.x) {
+        const int c = t / n, r = t - c * n;
+        const int kk = r / ns + 1, q = r - (kk - 1) * ns + 1;
+        const int iCell = p.cellSolveStart + col0 + c;
+        if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) continue;
+        const int ne = p.nEdgesOnCell[iCell - 1];
+        real col = 0.0;
+        for (int i = 1; i <= ne; ++i) {
+            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+            col = col - p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.uhAvg[IX2(kk, iEdge, L)] * p.horiz_flux_arr[IX3(q, kk, iEdge, ns, L)];
+        }
+        col = col * p.invAreaCell[iCell - 1] + p.scalar_tend_save[IX3(q, kk, iCell, ns, L)];
+        const real flo = as_wdtn_at(p, q, kk, iCell), fhi = as_wdtn_at(p, q, kk + 1, iCell);
+        const real rho_old = p.rho_zz_old[IX2(kk, iCell, L)];
+        const real rho_zz_new_inv = (real)1.0 / (p.weight_time_old * rho_old + p.weight_time_new * p.rho_zz_new[IX2(kk, iCell, L)]);
+        as_hold[t] = (p.scalar_old[IX3(q, kk, iCell, ns, L)] * rho_old + p.dt * (col - p.rdnw[kk - 1] * (fhi - flo))) * rho_zz_new_inv;
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < ncols * n; t += blockDim.x) {
+        const int c = t / n, r = t - c * n;
+        const int kk = r / ns + 1, q = r - (kk - 1) * ns + 1;
+        const int iCell = p.cellSolveStart + col0 + c;
+        if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) continue;
+        p.scalar_new[IX3(q, kk, iCell, ns, L)] = as_hold[t];
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+struct MonoP {
+    int L, mE, ns, iScalar, nCells;
+    int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, nCellsSolve;
+    int advance_density;
+    real dt, coef_3rd_order;
+    const real *uhAvg, *wwAvg, *rho_zz_old, *rho_lim, *invAreaCell, *dvEdge, *edgesOnCell_sign, *fnm, *fnp, *rdnw, *adv_coefs, *adv_coefs_3rd;
+    const int *cellsOnEdge, *cellsOnCell, *edgesOnCell, *nEdgesOnCell, *nAdvCellsForEdge, *advCellsForEdge, *bdyMaskCell, *bdyMaskEdge;
+    real *scalar_tend, *scalars_old, *scalars_new, *scalar_old, *scalar_new, *s_max, *s_min, *wdtn, *scale_arr, *flux_arr, *flux_upwind_tmp, *flux_tmp,
+        *rho_zz_int;
+};
+
+__global__ void __launch_bounds__(256) mono_pre_kernel(MonoP p) {
+    const int L = p.L, ns = p.ns;
+    FLAT_KC(p.nCellsSolveLoop, L * ns);
+    const int iCell = p.cellSolveStart + _c0;
+    const int kk = (k - 1) / ns + 1, q = (k - 1) % ns + 1;
+    const size_t is = IX3(q, kk, iCell, ns, L);
+    p.scalars_old[is] = p.scalars_old[is] + p.dt * p.scalar_tend[is] / p.rho_zz_old[IX2(kk, iCell, L)];
+    p.scalar_tend[is] = 0.0;
+}
+
+__global__ void __launch_bounds__(256) mono_rho_int_kernel(MonoP p) {
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    FLAT_KC(p.nCellsLoop, L);
+    const int iCell = p.cellStart + _c0;
+    const size_t ic = IX2(k, iCell, L);
+    if (iCell < p.cellSolveStart || iCell >= p.cellSolveStart + p.nCellsSolveLoop) {
+        p.rho_zz_int[ic] = 0.0;
+        return;
+    }
+    real r = 0.0;
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const real invArea = p.invAreaCell[iCell - 1];
+    for (int i = 1; i <= ne; ++i) {
+        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+        r = r - p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.uhAvg[IX2(k, iEdge, L)] * p.dvEdge[iEdge - 1] * invArea;
+    }
+    p.rho_zz_int[ic] = p.rho_zz_old[ic] + p.dt * (r - p.rdnw[k - 1] * (p.wwAvg[IX2(k + 1, iCell, L1)] - p.wwAvg[IX2(k, iCell, L1)]));
+}
+
+__global__ void __launch_bounds__(256) mono_copy_kernel(MonoP p) {
+    const int L = p.L, ns = p.ns;
+    FLAT_KC(p.nCellsLoop + 1, L);  // + the garbage column, zeroed (TI:3808-3812)
+    const int iCell = p.cellStart + _c0;
+    const size_t ic = IX2(k, iCell, L);
+    if (iCell == p.nCells + 1) {
+        p.scalar_old[ic] = 0.;
+        p.scalar_new[ic] = 0.;
+        return;
+    }
+    p.scalar_old[ic] = p.scalars_old[IX3(p.iScalar, k, iCell, ns, L)];
+    p.scalar_new[ic] = p.scalars_new[IX3(p.iScalar, k, iCell, ns, L)];
+}
+
+__global__ void __launch_bounds__(256) mono_bounds_kernel(MonoP p) {
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    FLAT_KC(p.nCellsSolveLoop, L1);
+    const int iCell = p.cellSolveStart + _c0;
+    const size_t iw = IX2(k, iCell, L1);
+    // vertical high-order flux at interface k
+    real f;
+    if (k == 1 || k == L1) f = 0.0;
+    else if (k == 2 || k == L) f = p.wwAvg[iw] * (p.fnm[k - 1] * p.scalar_new[IX2(k, iCell, L)] + p.fnp[k - 1] * p.scalar_new[IX2(k - 1, iCell, L)]);
+    else
+        f = flux3(p.scalar_new[IX2(k - 2, iCell, L)], p.scalar_new[IX2(k - 1, iCell, L)], p.scalar_new[IX2(k, iCell, L)], p.scalar_new[IX2(k + 1, iCell, L)],
+                  p.wwAvg[iw], p.coef_3rd_order);
+    p.wdtn[iw] = f;
+    if (k > L) return;
+    const size_t ic = IX2(k, iCell, L);
+    real smax, smin;
+    const real s0 = p.scalar_old[ic];
+    if (k == 1) {
+        const real s1 = p.scalar_old[IX2(2, iCell, L)];
+        smax = fmax(s0, s1);
+        smin = fmin(s0, s1);
+    } else if (k == L) {
+        const real sm = p.scalar_old[IX2(k - 1, iCell, L)];
+        smax = fmax(s0, sm);
+        smin = fmin(s0, sm);
+    } else {
+        const real sm = p.scalar_old[IX2(k - 1, iCell, L)], sp = p.scalar_old[IX2(k + 1, iCell, L)];
+        smax = fmax(fmax(sm, s0), sp);
+        smin = fmin(fmin(sm, s0), sp);
+    }
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    for (int i = 1; i <= ne; ++i) {
+        const real sc = p.scalar_old[IX2(k, p.cellsOnCell[IX2(i, iCell, mE)], L)];
+        smax = fmax(smax, sc);
+        smin = fmin(smin, sc);
+    }
+    p.s_max[ic] = smax;
+    p.s_min[ic] = smin;
+}
+
+__global__ void __launch_bounds__(256) mono_edge_flux_kernel(MonoP p) {
+    const int L = p.L;
+    FLAT_KC(p.nEdgesLoop, L);
+    const int iEdge = p.edgeStart + _c0;
+    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    const size_t ie = IX2(k, iEdge, L);
+    const real uh = p.uhAvg[ie];
+    real fa;
+    if (cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve) {
+        const int n = p.nAdvCellsForEdge[iEdge - 1];
+        if (n == 10) {  // TI:3925-3945: weights pre-combined, merge(1,2,uhAvg>0)
+            const bool pos = uh > 0;
+            real s;
+            {
+                const real c = p.adv_coefs[IX2(1, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(1, iEdge, 15)];
+                s = (pos ? (c + c3) : (c - c3)) * p.scalar_new[IX2(k, p.advCellsForEdge[IX2(1, iEdge, 15)], L)];
+            }
+            for (int jj = 2; jj <= 10; ++jj) {
+                const real c = p.adv_coefs[IX2(jj, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(jj, iEdge, 15)];
+                s = s + (pos ? (c + c3) : (c - c3)) * p.scalar_new[IX2(k, p.advCellsForEdge[IX2(jj, iEdge, 15)], L)];
+            }
+            fa = uh * s;
+        } else {
+            fa = 0.0;
+            const real s3 = fsign((real)1.0, uh);
+            for (int i = 1; i <= n; ++i) {
+                const real scalar_weight = uh * (p.adv_coefs[IX2(i, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(i, iEdge, 15)]);
+                fa = fa + scalar_weight * p.scalar_new[IX2(k, p.advCellsForEdge[IX2(i, iEdge, 15)], L)];
+            }
+        }
+    } else {
+        fa = 0.0;
+    }
+    // TI:4007-4022 (all edges)
+    const real fup = p.dvEdge[iEdge - 1] * p.dt * (fmax((real)0.0, uh) * p.scalar_old[IX2(k, cell1, L)] + fmin((real)0.0, uh) * p.scalar_old[IX2(k, cell2, L)]);
+    real ft = p.dt * fa - fup;
+    const int bm = p.bdyMaskEdge[iEdge - 1];
+    if ((config_apply_lbcs && (bm == MPAS_NRELAXZONE)) || (bm == MPAS_NRELAXZONE - 1)) {
+        ft = 0.;
+        fa = fup;
+    }
+    p.flux_arr[ie] = fa;
+    p.flux_upwind_tmp[ie] = fup;
+    p.flux_tmp[ie] = ft;
+}
+
+__device__ __forceinline__ real mono_upwind_at(const MonoP& p, int kk, int iCell) {  // flux_upwind_arr(kk), kk in 2..L
+    const int L = p.L, L1 = L + 1;
+    const real ww = p.wwAvg[IX2(kk, iCell, L1)];
+    return p.dt * (fmax((real)0.0, ww) * p.scalar_old[IX2(kk - 1, iCell, L)] + fmin((real)0.0, ww) * p.scalar_old[IX2(kk, iCell, L)]);
+}
+
+// vertical upwind update (TI:3969-4000) + horizontal accumulation + scale factors (TI:4024-4076).
+// The reference rewrites wdtn(k) = dt*wdtn(k) - flux_upwind(k) in place; thread k needs the rewritten
+// wdtn(k) and wdtn(k+1): both are recomputed in registers from the high-order values still in memory,
+// and the in-place rewrite itself is done afterwards by mono_wdtn_store_kernel.
+__global__ void __launch_bounds__(256) mono_limiter_kernel(MonoP p) {
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    const real eps = 1.e-20;
+    {
+        FLAT_KC(p.nCellsSolveLoop, L);
+        const int iCell = p.cellSolveStart + _c0;
+        const size_t ic = IX2(k, iCell, L);
+        const size_t iw = IX2(k, iCell, L1);
+        const real so = p.scalar_old[ic];
+        real sn = so * p.rho_zz_old[ic];
+        const real fu_k = (k >= 2) ? mono_upwind_at(p, k, iCell) : (real)0.0;
+        const real fu_kp = (k <= L - 1) ? mono_upwind_at(p, k + 1, iCell) : (real)0.0;
+        const real rd = p.rdnw[k - 1];
+        if (k <= L - 1) sn = sn - fu_kp * rd;
+        if (k >= 2) sn = sn + fu_k * rd;
+        const real wd_k = (k >= 2) ? (p.dt * p.wdtn[iw] - fu_k) : p.wdtn[iw];
+        const real wd_kp = (k <= L - 1) ? (p.dt * p.wdtn[IX2(k + 1, iCell, L1)] - fu_kp) : p.wdtn[IX2(k + 1, iCell, L1)];
+        real sc_in = -rd * (fmin((real)0.0, wd_kp) - fmax((real)0.0, wd_k));
+        real sc_out = -rd * (fmax((real)0.0, wd_kp) - fmin((real)0.0, wd_k));
+        const int ne = p.nEdgesOnCell[iCell - 1];
+        const real invArea = p.invAreaCell[iCell - 1];
+        for (int i = 1; i <= ne; ++i) {
+            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+            const real sgn = p.edgesOnCell_sign[IX2(i, iCell, mE)];
+            const size_t ie = IX2(k, iEdge, L);
+            sn = sn - sgn * p.flux_upwind_tmp[ie] * invArea;
+            const real sf = sgn * p.flux_tmp[ie];
+            sc_out = sc_out - fmax((real)0.0, sf) * invArea;
+            sc_in = sc_in - fmin((real)0.0, sf) * invArea;
+        }
+        p.scalar_new[ic] = sn;
+        const real rl = p.rho_lim[ic];
+        real scale_factor = (p.s_max[ic] * rl - sn) / (sc_in + eps);
+        p.scale_arr[IX3(k, 1, iCell, L, 2)] = fmin((real)1.0, fmax((real)0.0, scale_factor));
+        scale_factor = (p.s_min[ic] * rl - sn) / (sc_out - eps);
+        p.scale_arr[IX3(k, 2, iCell, L, 2)] = fmin((real)1.0, fmax((real)0.0, scale_factor));
+    }
+}
+
+// second half of TI:3990-3993: wdtn(k) = dt*wdtn(k) - flux_upwind_arr(k), k = 2..L, run after mono_limiter_kernel
+__global__ void __launch_bounds__(256) mono_wdtn_store_kernel(MonoP p) {
+    const int L = p.L, L1 = L + 1;
+    FLAT_KC(p.nCellsSolveLoop, L);
+    if (k < 2) return;
+    const int iCell = p.cellSolveStart + _c0;
+    const size_t iw = IX2(k, iCell, L1);
+    p.wdtn[iw] = p.dt * p.wdtn[iw] - mono_upwind_at(p, k, iCell);
+}
+
+__global__ void __launch_bounds__(256) mono_rescale_edge_kernel(MonoP p) {
+    const int L = p.L;
+    FLAT_KC(p.nEdgesLoop, L);
+    const int iEdge = p.edgeStart + _c0;
+    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    if (!(cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve)) return;
+    const size_t ie = IX2(k, iEdge, L);
+    const real uh = p.uhAvg[ie];
+    const real flux_upwind = p.dvEdge[iEdge - 1] * p.dt * (fmax((real)0.0, uh) * p.scalar_old[IX2(k, cell1, L)] + fmin((real)0.0, uh) * p.scalar_old[IX2(k, cell2, L)]);
+    real flux = p.dt * p.flux_arr[ie] - flux_upwind;
+    const int bm = p.bdyMaskEdge[iEdge - 1];
+    if ((config_apply_lbcs && (bm == MPAS_NRELAXZONE)) || (bm == MPAS_NRELAXZONE - 1)) flux = 0.;
+    flux = fmax((real)0.0, flux) * fmin(p.scale_arr[IX3(k, 2, cell1, L, 2)], p.scale_arr[IX3(k, 1, cell2, L, 2)]) +
+           fmin((real)0.0, flux) * fmin(p.scale_arr[IX3(k, 1, cell1, L, 2)], p.scale_arr[IX3(k, 2, cell2, L, 2)]);
+    p.flux_arr[ie] = flux;
+}
+
+__device__ __forceinline__ real mono_wdtn_limited(const MonoP& p, int kk, int iCell) {  // TI:4145-4153
+    const int L = p.L, L1 = L + 1;
+    const real flux = p.wdtn[IX2(kk, iCell, L1)];
+    if (kk < 2 || kk > L) return flux;
+    return fmax((real)0.0, flux) * fmin(p.scale_arr[IX3(kk - 1, 2, iCell, L, 2)], p.scale_arr[IX3(kk, 1, iCell, L, 2)]) +
+           fmin((real)0.0, flux) * fmin(p.scale_arr[IX3(kk, 2, iCell, L, 2)], p.scale_arr[IX3(kk - 1, 1, iCell, L, 2)]);
+}
+
+__global__ void __launch_bounds__(256) mono_update_kernel(MonoP p) {
+    const int L = p.L, mE = p.mE, ns = p.ns;
+    FLAT_KC(p.nCellsLoop, L);
+    const int iCell = p.cellStart + _c0;
+    const size_t ic = IX2(k, iCell, L);
+    real sn = p.scalar_new[ic];
+    if (iCell >= p.cellSolveStart && iCell < p.cellSolveStart + p.nCellsSolveLoop) {
+        const real wlo = mono_wdtn_limited(p, k, iCell), whi = mono_wdtn_limited(p, k + 1, iCell);
+        const int ne = p.nEdgesOnCell[iCell - 1];
+        const real invArea = p.invAreaCell[iCell - 1];
+        for (int i = 1; i <= ne; ++i) {
+            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+            sn = sn - p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.flux_arr[IX2(k, iEdge, L)] * invArea;
+        }
+        sn = (sn + (-p.rdnw[k - 1] * (whi - wlo))) / p.rho_lim[ic];
+        p.scalar_new[ic] = sn;
+    }
+    if (p.bdyMaskCell[iCell - 1] <= MPAS_NSPECZONE) p.scalars_new[IX3(p.iScalar, k, iCell, ns, L)] = fmax((real)0.0, sn);
+}
+
+}  // namespace
+
+extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
+    (void)nCells; (void)nEdges; (void)nCellsSolve; (void)kdiff; (void)deriv_two; (void)dvEdge; (void)cellsOnEdge; (void)meshScalingDel2; (void)meshScalingDel4;
+    (void)rho_edge; (void)qv_init; (void)zgrid; (void)cellStart; (void)cellEnd; (void)vertexStart; (void)vertexEnd; (void)vertexSolveStart; (void)vertexSolveEnd;
+    (void)edgeSolveStart; (void)edgeSolveEnd;
+    AsP p;
+    p.L = nVertLevels; p.mE = maxEdges; p.ns = num_scalars; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1;
+    p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
+    real weight_time_new = 1.;
+    if (advance_density) {  // TI:3296-3304
+        if ((rk_step == 1) && config_time_integration_order == 3) weight_time_new = (real)1. / 3;
+        if ((rk_step == 1) && config_time_integration_order == 2) weight_time_new = (real)1. / 2;
+        if (rk_step == 2) weight_time_new = (real)1. / 2;
+        if (rk_step == 3) weight_time_new = 1.;
+    }
+    p.weight_time_new = weight_time_new; p.weight_time_old = (real)1. - weight_time_new;
+    p.dt = dt; p.coef_3rd_order = coef_3rd_order;
+    p.scalar_old = X(scalar_old); p.rho_zz_old = X(rho_zz_old); p.rho_zz_new = X(rho_zz_new); p.uhAvg = X(uhAvg); p.wwAvg = X(wwAvg);
+    p.edgesOnCell_sign = X(edgesOnCell_sign); p.invAreaCell = X(invAreaCell); p.fnm = X(fnm); p.fnp = X(fnp); p.rdnw = X(rdnw);
+    p.adv_coefs = X(adv_coefs); p.adv_coefs_3rd = X(adv_coefs_3rd); p.edgesOnCell = X(edgesOnCell); p.nEdgesOnCell = X(nEdgesOnCell);
+    p.bdyMaskCell = X(bdyMaskCell); p.bdyMaskEdge = X(bdyMaskEdge); p.nAdvCellsForEdge = X(nAdvCellsForEdge); p.advCellsForEdge = X(advCellsForEdge);
+    p.scalar_tend_save = X(scalar_tend_save); p.scalar_new = X(scalar_new); p.horiz_flux_arr = X(horiz_flux_arr);
+    KLAUNCH(as_edge_kernel, (long long)p.nEdgesLoop * p.L * p.ns, 256, p);
+    KCHECK("as_edge_kernel");
+    if (p.nCellsSolveLoop > 0) {
+        const size_t shm = (size_t)AS_COLS * p.L * p.ns * sizeof(real);
+        if (shm > 48 * 1024) return fail_msg("mpas_b200_advance_scalars_work: nVertLevels*num_scalars too large for the column staging");
+        as_cell_kernel<<<cdiv(p.nCellsSolveLoop, AS_COLS), 256, shm, stream()>>>(p);
+        count_launch();
+        KCHECK("as_cell_kernel");
+    }
+    return 0;
+}
+
+extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
+    (void)nEdges; (void)vertexStart; (void)vertexEnd; (void)vertexSolveStart; (void)vertexSolveEnd; (void)edgeSolveStart; (void)edgeSolveEnd;
+    MonoP p;
+    p.L = nVertLevels; p.mE = maxEdges; p.ns = num_scalars; p.iScalar = 0; p.nCells = nCells;
+    p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
+    p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.nCellsSolve = nCellsSolve; p.advance_density = advance_density;
+    p.dt = dt; p.coef_3rd_order = coef_3rd_order;
+    p.uhAvg = X(uhAvg); p.wwAvg = X(wwAvg); p.rho_zz_old = X(rho_zz_old); p.invAreaCell = X(invAreaCell); p.dvEdge = X(dvEdge);
+    p.edgesOnCell_sign = X(edgesOnCell_sign); p.fnm = X(fnm); p.fnp = X(fnp); p.rdnw = X(rdnw); p.adv_coefs = X(adv_coefs); p.adv_coefs_3rd = X(adv_coefs_3rd);
+    p.cellsOnEdge = X(cellsOnEdge); p.cellsOnCell = X(cellsOnCell); p.edgesOnCell = X(edgesOnCell); p.nEdgesOnCell = X(nEdgesOnCell);
+    p.nAdvCellsForEdge = X(nAdvCellsForEdge); p.advCellsForEdge = X(advCellsForEdge); p.bdyMaskCell = X(bdyMaskCell); p.bdyMaskEdge = X(bdyMaskEdge);
+    p.scalar_tend = X(scalar_tend); p.scalars_old = X(scalars_old); p.scalars_new = X(scalars_new); p.scalar_old = X(scalar_old); p.scalar_new = X(scalar_new);
+    p.s_max = X(s_max); p.s_min = X(s_min); p.wdtn = X(wdtn); p.scale_arr = X(scale_arr); p.flux_arr = X(flux_arr); p.flux_upwind_tmp = X(flux_upwind_tmp);
+    p.flux_tmp = X(flux_tmp); p.rho_zz_int = X(rho_zz_int);
+    p.rho_lim = advance_density ? p.rho_zz_int : X(rho_zz_new);
+    if (advance_density && !rho_zz_int) return fail_msg("mpas_b200_advance_scalars_mono_work: advance_density needs rho_zz_int (TI:3768)");
+    const int L = p.L;
+    KLAUNCH(mono_pre_kernel, (long long)p.nCellsSolveLoop * L * p.ns, 256, p);
+    KCHECK("mono_pre_kernel");
+    if (halo_fn) {
+        int rc = halo_fn(halo_ctx, 0, scalars_old);  // TI:3757
+        if (rc) return rc;
+    }
+    if (advance_density) {
+        KLAUNCH(mono_rho_int_kernel, (long long)p.nCellsLoop * L, 256, p);
+        KCHECK("mono_rho_int_kernel");
+    }
+    for (int iScalar = 1; iScalar <= num_scalars; ++iScalar) {
+        p.iScalar = iScalar;
+        KLAUNCH(mono_copy_kernel, (long long)(p.nCellsLoop + 1) * L, 256, p);
+        KCHECK("mono_copy_kernel");
+        KLAUNCH(mono_bounds_kernel, (long long)p.nCellsSolveLoop * (L + 1), 256, p);
+        KCHECK("mono_bounds_kernel");
+        KLAUNCH(mono_edge_flux_kernel, (long long)p.nEdgesLoop * L, 256, p);
+        KCHECK("mono_edge_flux_kernel");
+        KLAUNCH(mono_limiter_kernel, (long long)p.nCellsSolveLoop * L, 256, p);
+        KCHECK("mono_limiter_kernel");
+        KLAUNCH(mono_wdtn_store_kernel, (long long)p.nCellsSolveLoop * L, 256, p);
+        KCHECK("mono_wdtn_store_kernel");
+        if (halo_fn) {
+            int rc = halo_fn(halo_ctx, 1, scale_arr);  // TI:4098
+            if (rc) return rc;
+        }
+        KLAUNCH(mono_rescale_edge_kernel, (long long)p.nEdgesLoop * L, 256, p);
+        KCHECK("mono_rescale_edge_kernel");
+        KLAUNCH(mono_update_kernel, (long long)p.nCellsLoop * L, 256, p);
+        KCHECK("mono_update_kernel");
+    }
+    return 0;
+}

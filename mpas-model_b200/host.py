@@ -43,6 +43,40 @@ def lib():
         _lib.mpas_host_block_nexch.argtypes = [C.c_void_p, C.c_int, C.c_int]
         _lib.mpas_host_block_exch_info.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_int)] * 3
         _lib.mpas_host_block_exch_lists.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        # device-resident dycore (include/mpas_b200.h, layer 2) and registry (layer 1 lifecycle)
+        _lib.mpas_b200_set_device.argtypes = [C.c_int]
+        _lib.mpas_b200_register_field.argtypes = [C.c_void_p, C.c_size_t]
+        _lib.mpas_b200_unregister_field.argtypes = [C.c_void_p]
+        _lib.mpas_b200_upload.argtypes = [C.c_void_p]
+        _lib.mpas_b200_download.argtypes = [C.c_void_p]
+        _lib.mpas_b200_device_ptr.restype = C.c_void_p
+        _lib.mpas_b200_device_ptr.argtypes = [C.c_void_p]
+        _lib.mpas_b200_launch_count.restype = C.c_longlong
+        _lib.mpas_b200_dycore_create.restype = C.c_void_p
+        _lib.mpas_b200_dycore_create.argtypes = [C.c_int, C.c_int, C.c_int]
+        _lib.mpas_b200_dycore_destroy.argtypes = [C.c_void_p]
+        _lib.mpas_b200_dycore_attach_block.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
+        _lib.mpas_b200_dycore_set_cfg.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_double]
+        _lib.mpas_b200_dycore_get_cfg.restype = C.c_double
+        _lib.mpas_b200_dycore_get_cfg.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
+        _lib.mpas_b200_nccl_unique_id.argtypes = [C.c_void_p]
+        _lib.mpas_b200_dycore_comm_init.argtypes = [C.c_void_p, C.c_void_p]
+        _lib.mpas_b200_dycore_init.argtypes = [C.c_void_p]
+        _lib.mpas_b200_dycore_step.argtypes = [C.c_void_p, C.c_int]
+        _lib.mpas_b200_dycore_get_field.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_void_p, C.c_size_t]
+        _lib.mpas_b200_dycore_set_field.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_void_p, C.c_size_t]
+        _lib.mpas_b200_dycore_field_device_ptr.restype = C.c_void_p
+        _lib.mpas_b200_dycore_field_device_ptr.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
+        _lib.mpas_b200_dycore_exchange.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        _lib.mpas_b200_dycore_call.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.c_int]
+        _lib.mpas_b200_dycore_exchange_count.restype = C.c_long
+        _lib.mpas_b200_dycore_exchange_count.argtypes = [C.c_void_p]
+        _lib.mpas_b200_dycore_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        _lib.mpas_b200_dycore_timer_count.argtypes = [C.c_void_p]
+        _lib.mpas_b200_dycore_timer_get.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]
+        _lib.mpas_b200_dycore_timer_reset.argtypes = [C.c_void_p]
+        _lib.mpas_b200_dycore_global_max_abs.restype = C.c_double
+        _lib.mpas_b200_dycore_global_max_abs.argtypes = [C.c_void_p, C.c_char_p]
     return _lib
 
 
@@ -158,3 +192,109 @@ class HostCase:
         if rc:
             raise RuntimeError(last_error())
         return Block(self, lib().mpas_host_case_block(self.h, iblock), iblock)
+
+
+class Dycore:
+    """Device-resident dycore (mpas_b200_dycore_*): the atm_srk3 sequence over fields living in HBM.
+
+    blocks: the host-harness Block objects this process owns (one per GPU rank, or several for the
+    single-process multi-block mode that mirrors the reference's no-MPI path)."""
+
+    def __init__(self, blocks, cfg=None, rank=0, nranks=1, device=None):
+        L = lib()
+        if L.mpas_b200_device_count() < 1:
+            raise RuntimeError("no CUDA device: the dycore has no CPU fallback")
+        if device is not None:
+            self._chk(L.mpas_b200_set_device(device))
+        self.blocks = blocks
+        self.h = L.mpas_b200_dycore_create(len(blocks), rank, nranks)
+        self.rank, self.nranks = rank, nranks
+        for i, b in enumerate(blocks):
+            self._chk(L.mpas_b200_dycore_attach_block(self.h, i, b.h))
+            for k, v in (cfg or {}).items():
+                L.mpas_b200_dycore_set_cfg(self.h, i, k.encode(), float(v))
+
+    @staticmethod
+    def _chk(rc):
+        if rc:
+            raise RuntimeError("mpas_b200 error %d: %s" % (rc, last_error()))
+
+    def comm_init(self, unique_id_bytes):
+        buf = C.create_string_buffer(bytes(unique_id_bytes), 128)
+        self._chk(lib().mpas_b200_dycore_comm_init(self.h, buf))
+
+    def init(self):
+        self._chk(lib().mpas_b200_dycore_init(self.h))
+
+    def step(self, n=1):
+        self._chk(lib().mpas_b200_dycore_step(self.h, n))
+
+    def sync(self):
+        self._chk(lib().mpas_b200_synchronize())
+
+    def set_option(self, name, value):
+        self._chk(lib().mpas_b200_dycore_set_option(self.h, name.encode(), int(value)))
+
+    def call(self, routine, *params):
+        arr = (C.c_double * max(1, len(params)))(*[float(p) for p in params])
+        self._chk(lib().mpas_b200_dycore_call(self.h, routine.encode(), arr, len(params)))
+
+    def exchange(self, name, layer=0):
+        self._chk(lib().mpas_b200_dycore_exchange(self.h, name.encode(), layer))
+
+    def field(self, ib, name, out=None):
+        kind, loc, dims = self.blocks[ib].info(name)
+        shape = tuple(reversed(dims))
+        if out is None:
+            out = np.empty(shape, dtype=np.float64 if kind == 0 else np.int32)
+        self._chk(lib().mpas_b200_dycore_get_field(self.h, ib, name.encode(), out.ctypes.data, out.nbytes))
+        return out
+
+    def set_field(self, ib, name, arr):
+        arr = np.ascontiguousarray(arr)
+        self._chk(lib().mpas_b200_dycore_set_field(self.h, ib, name.encode(), arr.ctypes.data, arr.nbytes))
+        self.sync()
+
+    def device_ptr(self, ib, name):
+        return lib().mpas_b200_dycore_field_device_ptr(self.h, ib, name.encode())
+
+    def exchange_count(self):
+        return lib().mpas_b200_dycore_exchange_count(self.h)
+
+    def launch_count(self):
+        return lib().mpas_b200_launch_count()
+
+    def max_abs(self, name):
+        return lib().mpas_b200_dycore_global_max_abs(self.h, name.encode())
+
+    def timers(self):
+        L = lib()
+        out = {}
+        name = C.create_string_buffer(128)
+        ms, calls = C.c_double(), C.c_long()
+        for i in range(L.mpas_b200_dycore_timer_count(self.h)):
+            L.mpas_b200_dycore_timer_get(self.h, i, name, 128, C.byref(ms), C.byref(calls))
+            out[name.value.decode()] = (ms.value, calls.value)
+        return out
+
+    def reset_timers(self):
+        lib().mpas_b200_dycore_timer_reset(self.h)
+
+    def close(self):
+        if self.h:
+            lib().mpas_b200_dycore_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def nccl_unique_id():
+    buf = C.create_string_buffer(128)
+    rc = lib().mpas_b200_nccl_unique_id(buf)
+    if rc:
+        raise RuntimeError(last_error())
+    return buf.raw

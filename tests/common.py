@@ -122,6 +122,20 @@ class OracleModel:
             pass
 
 
+class GpuModel(host.Dycore):
+    """The product dycore on cuda:0 (or the given device) for the given host blocks."""
+
+    def __init__(self, blocks, cfg, **kw):
+        super().__init__(blocks, dict(cfg), **kw)  # per-block dims/configs come from attach_block
+
+
+def has_gpu():
+    try:
+        return host.lib().mpas_b200_device_count() > 0
+    except Exception:
+        return False
+
+
 def make_case(level, nblocks=1, nVertLevels=26, init_case=2, num_scalars=1, method="sfc", lloyd=10, sfc=True):
     case = host.HostCase(level, lloyd_iters=lloyd, sfc=sfc)
     if nblocks > 1:
