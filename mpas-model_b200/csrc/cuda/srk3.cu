@@ -300,6 +300,15 @@ int xchg(Dycore& m, const std::vector<XField>& fields) {
 
 // atm_mpas_init_block + atm_core_init exchanges (mpas_atm_core.F:145, 163, 180-186, 390-402)
 int dycore_init(Dycore& m) {
+    // The reference reads the initial state INCLUDING halo elements from the global init file ('input' stream,
+    // mpas_atm_core.F:95).  The harness initialises each block on its own, so fields built with horizontal
+    // stencils are wrong in the outer halo; fill them from their owners first (not counted as a step exchange).
+    {
+        const long keep = m.nExchanges;
+        for (const char* n : {"w@1", "zb_cell", "zb3_cell", "zxu", "defc_a", "defc_b"})
+            if (m.blocks[0].f.count(n)) CK(dycore_exchange(m, {{n, 0}}));
+        m.nExchanges = keep;
+    }
     CK(dycore_exchange(m, {{"u@1", 0}}));  // :145
     for (auto& b : m.blocks) {
         CK(call_init_coupled(b));

@@ -280,6 +280,15 @@ namespace {
 
 // atm_mpas_init_block + atm_core_init exchanges (mpas_atm_core.F:145, 163, 180-186, 390-402)
 void model_init(OModel& m) {
+    // The reference reads the initial state INCLUDING halo elements from the global init file ('input' stream,
+    // mpas_atm_core.F:95).  The harness initialises each block on its own, so fields built with horizontal
+    // stencils are wrong in the outer halo; fill them from their owners first (not counted as a step exchange).
+    {
+        long keep = m.nExchanges;
+        for (const char* n : {"w@1", "zb_cell", "zb3_cell", "zxu", "defc_a", "defc_b"})
+            if (m.blocks[0].f.count(n)) m.exchange(n);
+        m.nExchanges = keep;
+    }
     m.exchange("u@1");  // :145
     for (auto& b : m.blocks) {
         Dims d = dims(b);
@@ -468,6 +477,60 @@ int oracle_model_init(void* h) {
 int oracle_model_step(void* h, int nsteps) {
     try {
         for (int i = 0; i < nsteps; ++i) srk3_step(*(OModel*)h);
+        return 0;
+    } catch (const std::exception& e) { g_oracle_err = e.what(); return 1; }
+}
+// run one work routine on the current fields of every block (routine-level parity tests); parameters as in
+// mpas-model_b200/csrc/cuda/srk3.cu dycore_call
+int oracle_model_call(void* h, const char* routine, const double* q, int nq) {
+    try {
+        OModel& m = *(OModel*)h;
+        std::string rt = routine;
+        auto need = [&](int n) { if (nq < n) throw std::runtime_error("oracle_model_call: too few parameters for " + rt); };
+        if (rt == "mono") { need(2); run_mono_all(m, (real)q[0], (int)q[1]); return 0; }
+        for (auto& b : m.blocks) {
+            Dims d = dims(b);
+            Ranges r = ranges(b);
+            if (rt == "acoustic") { need(2); call_acoustic(b, (real)q[0], (int)q[1]); }
+            else if (rt == "divdamp") {
+                need(1);
+                oracle_divergence_damping_3d(d.L, d.nC, d.nE, d.nCS, 1, d.nE, b.R("theta_m@1"), b.R("ru_p"), b.R("rtheta_pp"), b.R("rtheta_pp_old"),
+                                             b.I("cellsOnEdge"), b.R("specZoneMaskEdge"), (real)q[0], b.c("config_smdiv", 0.1), b.c("config_len_disp"));
+            }
+            else if (rt == "recover") { need(3); call_recover(b, (real)q[0], (int)q[1], (int)q[2]); }
+            else if (rt == "dyn_tend") { need(2); call_dyn_tend(b, (int)q[0], (real)q[1]); }
+            else if (rt == "advance_scalars") { need(4); call_advance_scalars(b, (real)q[0], (int)q[1], (int)q[2], (int)q[3]); }
+            else if (rt == "solve_diagnostics") { need(3); call_solve_diagnostics(b, (int)q[0], (real)q[1], (int)q[2]); }
+            else if (rt == "vert_imp_coefs") { need(1); call_vert_imp_coefs(b, (real)q[0]); }
+            else if (rt == "smlstep") {
+                oracle_set_smlstep_pert_variables_work(d.L, d.mE, d.nC, d.nE, d.nCS, b.I("nEdgesOnCell"), b.I("cellsOnEdge"), b.I("edgesOnCell"), b.R("fzm"),
+                                                       b.R("fzp"), b.R("zb_cell"), b.R("zb3_cell"), b.R("zz"), b.R("tend_w"), b.R("tend_u"), b.I("bdyMaskCell"),
+                                                       b.R("edgesOnCell_sign"), r.cS, r.cE, r.eS, r.eE, r.csS, r.csE, r.esS, r.esE);
+            }
+            else if (rt == "rk_setup") {
+                oracle_rk_integration_setup(d.L, d.ns, d.nC, d.nE, RANGES, b.R("ru"), b.R("ru_save"), b.R("rw"), b.R("rw_save"), b.R("rtheta_p"), b.R("rtheta_p_save"),
+                                            b.R("rho_p"), b.R("rho_p_save"), b.R("rho_zz_old_split"), b.R("u@1"), b.R("u@2"), b.R("w@1"), b.R("w@2"), b.R("theta_m@1"),
+                                            b.R("theta_m@2"), b.R("rho_zz@1"), b.R("rho_zz@2"), b.R("scalars@1"), b.R("scalars@2"));
+            }
+            else if (rt == "moist") {
+                oracle_compute_moist_coefficients(d.L, d.ns, d.nC, d.nE, d.nCS, d.ms, d.me, RANGES, b.I("cellsOnEdge"), b.R("scalars@2"), b.R("cqw"), b.R("cqu"), b.R("qtot"));
+            }
+            else if (rt == "substep_finish") {
+                need(2);
+                oracle_rk_dynamics_substep_finish(d.L, d.nC, d.nE, (int)q[0], (int)q[1], RANGES, b.R("ru"), b.R("ru_save"), b.R("rw"), b.R("rw_save"),
+                                                  b.R("rtheta_p"), b.R("rtheta_p_save"), b.R("rho_p"), b.R("rho_p_save"), b.R("rho_zz_old_split"), b.R("ruAvg"),
+                                                  b.R("ruAvg_split"), b.R("wwAvg"), b.R("wwAvg_split"), b.R("u@1"), b.R("u@2"), b.R("w@1"), b.R("w@2"),
+                                                  b.R("theta_m@1"), b.R("theta_m@2"), b.R("rho_zz@1"), b.R("rho_zz@2"));
+            }
+            else if (rt == "init_coupled") {
+                oracle_init_coupled_diagnostics(d.L, d.mE, d.ns, (int)b.c("index_qv", 1), d.nC, d.nE, RANGES, b.I("cellsOnEdge"), b.I("nEdgesOnCell"), b.I("edgesOnCell"),
+                                                b.R("edgesOnCell_sign"), b.R("theta_m@1"), b.R("theta"), b.R("rho_zz@1"), b.R("rho"), b.R("rho_p"), b.R("rho_base"),
+                                                b.R("rtheta_base"), b.R("theta_base"), b.R("rtheta_p"), b.R("zz"), b.R("scalars@1"), b.R("ru"), b.R("rw"), b.R("u@1"),
+                                                b.R("w@1"), b.R("pressure_p"), b.R("pressure_base"), b.R("exner"), b.R("exner_base"), b.R("fzm"), b.R("fzp"),
+                                                b.R("zb_cell"), b.R("zb3_cell"));
+            }
+            else throw std::runtime_error("oracle_model_call: unknown routine " + rt);
+        }
         return 0;
     } catch (const std::exception& e) { g_oracle_err = e.what(); return 1; }
 }

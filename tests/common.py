@@ -56,6 +56,7 @@ def oracle():
         L.oracle_model_exchange.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.oracle_model_init.argtypes = [C.c_void_p]
         L.oracle_model_step.argtypes = [C.c_void_p, C.c_int]
+        L.oracle_model_call.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.c_int]
         L.oracle_model_exchange_count.restype = C.c_long
         L.oracle_model_exchange_count.argtypes = [C.c_void_p]
         L.oracle_model_get_field.restype = C.c_void_p
@@ -102,6 +103,10 @@ class OracleModel:
 
     def exchange(self, name, layer=0):
         self._chk(self.L.oracle_model_exchange(self.h, name.encode(), layer))
+
+    def call(self, routine, *params):
+        arr = (C.c_double * max(1, len(params)))(*[float(p) for p in params])
+        self._chk(self.L.oracle_model_call(self.h, routine.encode(), arr, len(params)))
 
     def field(self, ib, name):
         """numpy view of the CURRENT array behind `name` (time levels swap every step)."""

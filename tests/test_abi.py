@@ -1,0 +1,54 @@
+"""The drop-in boundary: libmpas_b200.so loads on a CPU-only machine and exports every symbol that
+include/mpas_b200.h declares; the argument-list macros parse to the reference's dummy-argument counts."""
+import ctypes
+import os
+import re
+
+import common
+
+ROOT = common.ROOT
+
+
+def _declared():
+    src = open(os.path.join(ROOT, "include", "mpas_b200.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(mpas_(?:b200|host)_\w+)\s*\(", src)))
+
+
+def test_library_loads_and_exports_every_declared_symbol():
+    L = common.host.lib()
+    names = _declared()
+    assert len(names) > 50
+    missing = [n for n in names if not hasattr(L, n)]
+    assert not missing, missing
+
+
+def test_no_compute_without_gpu_is_loud():
+    if common.has_gpu():
+        return
+    case, blocks = common.make_case(3, 1, nVertLevels=4, num_scalars=1)
+    try:
+        common.GpuModel(blocks, common.level_config(3))
+    except RuntimeError as e:
+        assert "no CPU fallback" in str(e)
+    else:
+        raise AssertionError("dycore created without a CUDA device")
+
+
+def test_argument_lists_match_reference_dummy_argument_counts():
+    """MPAS_ACOUSTIC_ARGS = the 66 dummies of TI:2447-2455 + nVertLevels, maxEdges (module mpas_atm_dimensions)."""
+    src = open(os.path.join(ROOT, "include", "mpas_b200_args.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    src = src.replace("\\\n", " ")
+    macros = dict(re.findall(r"#define\s+(MPAS_\w+_ARGS)\s+(.*)", src))
+    rng = macros["MPAS_RANGE_ARGS"]
+
+    def count(name):
+        body = macros[name].replace("MPAS_RANGE_ARGS", rng)
+        return len([a for a in body.split(",") if a.strip()])
+
+    assert count("MPAS_RANGE_ARGS") == 12
+    assert count("MPAS_ACOUSTIC_ARGS") == 66 + 2
+    assert count("MPAS_DIVDAMP_ARGS") == 15
+    # TI:4481-4499 has 128 dummies; + the 10 host-associated module scratch arrays (TI:35-43) + num_scalars, moist_start/end are already dummies
+    assert count("MPAS_DYNTEND_ARGS") >= 128 + 10

@@ -1,0 +1,132 @@
+"""Pins for the CPU oracle (the reference ships no atmosphere test or golden vector: SURVEY.md F4, "parity
+unpinned" by the reference's own tests).  Analytic invariants of the discretisation + structural
+cross-checks."""
+import numpy as np
+import pytest
+
+import common
+
+
+def _mass(b, m, ib):
+    rho = m.field(ib, "rho_zz@1")
+    nown = int(b.cfg()["nCellsSolve"])
+    area = b.field("areaCell")[:nown]
+    rdzw = b.field("rdzw")
+    # rho_zz * dzw * area: column mass in the terrain-following coordinate (TI:4762 flux form)
+    return float(((rho[:nown] / rdzw[None, :]) * area[:, None]).sum())
+
+
+def test_exchange_count_matches_reference_sequence():
+    case, blocks = common.make_case(3, 2, nVertLevels=8, num_scalars=3)
+    m = common.OracleModel(blocks, common.level_config(3))
+    m.init()
+    c0 = m.exchange_count()
+    m.step(1)
+    # 121 + num_scalars exchanges per dt with Registry defaults
+    assert m.exchange_count() - c0 == 121 + 3
+
+
+def test_dry_mass_conserved_and_fields_finite():
+    case, blocks = common.make_case(4, 1, nVertLevels=26, num_scalars=1)
+    m = common.OracleModel(blocks, common.level_config(4))
+    m.init()
+    m0 = _mass(blocks[0], m, 0)
+    m.step(10)
+    m1 = _mass(blocks[0], m, 0)
+    assert abs(m1 - m0) / m0 < 1e-13
+    for n in ("u@1", "w@1", "theta_m@1", "rho_zz@1"):
+        assert np.isfinite(m.field(0, n)).all()
+    assert np.abs(m.field(0, "w@1")).max() < 1.0
+
+
+def test_steady_state_jw_case_stays_steady():
+    case, blocks = common.make_case(4, 1, nVertLevels=26, num_scalars=1, init_case=1)
+    m = common.OracleModel(blocks, common.level_config(4))
+    m.init()
+    u0 = m.field(0, "u@1").copy()
+    th0 = m.field(0, "theta_m@1").copy()
+    m.step(10)
+    assert common.rel_l2(m.field(0, "u@1"), u0) < 2e-2  # discretisation error of the balanced state only (480 km mesh)
+    assert common.rel_l2(m.field(0, "theta_m@1"), th0) < 1e-3
+
+
+def test_monotone_transport_bounds_mass_and_constancy():
+    case, blocks = common.make_case(4, 1, nVertLevels=26, num_scalars=4)
+    b = blocks[0]
+    s = b.field("scalars@1")
+    lat, lon = b.field("latCell"), b.field("lonCell")
+    r = np.arccos(np.clip(np.sin(0.6) * np.sin(lat) + np.cos(0.6) * np.cos(lat) * np.cos(lon - 1.0), -1, 1))
+    s[:-1, :, 1] = np.where(r < 0.8, 1.0, 0.0)[:-1, None]  # slotted-cylinder-like discontinuity
+    s[:-1, :, 2] = 1.0                                       # constant
+    s[:-1, :, 3] = (0.5 * (1 + np.cos(np.pi * np.minimum(r, 0.8) / 0.8)))[:-1, None]
+    m = common.OracleModel(blocks, common.level_config(4))
+    m.init()
+    nown = int(b.cfg()["nCellsSolve"])
+    area = b.field("areaCell")[:nown]
+    rdzw = b.field("rdzw")
+
+    def tracer_mass(q):
+        return float((m.field(0, "scalars@1")[:nown, :, q] * m.field(0, "rho_zz@1")[:nown] / rdzw[None, :] * area[:, None]).sum())
+
+    mass0 = [tracer_mass(q) for q in range(4)]
+    m.step(5)
+    sc = m.field(0, "scalars@1")[:nown]
+    # monotone: no new extrema (Zalesak limiter, TI:4048-4076)
+    assert sc[:, :, 1].min() >= 0.0 and sc[:, :, 1].max() <= 1.0 + 1e-12
+    assert sc[:, :, 3].min() >= 0.0 and sc[:, :, 3].max() <= 1.0 + 1e-12
+    # a constant stays constant when density is advanced consistently (rho_zz_int, TI:3772-3792)
+    assert np.abs(sc[:, :, 2] - 1.0).max() < 1e-11
+    for q in (1, 2, 3):
+        assert abs(tracer_mass(q) - mass0[q]) / mass0[q] < 1e-12
+
+
+def test_tridiagonal_coefficients_solve_the_system():
+    """a_tri/alpha_tri/gamma_tri are a pre-factorised Thomas solve (TI:2110-2127): rebuild b, c and check A x = rhs."""
+    case, blocks = common.make_case(3, 1, nVertLevels=12, num_scalars=1)
+    m = common.OracleModel(blocks, common.level_config(3))
+    m.init()
+    m.step(1)
+    a = m.field(0, "a_tri")[0]
+    al = m.field(0, "alpha_tri")[0]
+    ga = m.field(0, "gamma_tri")[0]
+    L = len(a)
+    b = np.ones(L)
+    c = np.zeros(L)
+    for k in range(1, L):
+        b[k] = 1.0 / al[k] + a[k] * ga[k - 1]
+        c[k] = ga[k] / al[k]
+    rng = np.random.default_rng(20240611)
+    rhs = rng.standard_normal(L)
+    rhs[0] = 0.0
+    x = rhs.copy()
+    for k in range(1, L):
+        x[k] = (x[k] - a[k] * x[k - 1]) * al[k]
+    xn = 0.0  # rw_p(L+1) = 0
+    for k in range(L - 1, -1, -1):
+        x[k] = x[k] - ga[k] * xn
+        xn = x[k]
+    A = np.diag(b) + np.diag(a[1:], -1) + np.diag(c[:-1], 1)
+    A[0, :] = 0
+    A[0, 0] = 1
+    assert np.allclose(A @ x, rhs, rtol=1e-10, atol=1e-12)
+
+
+@pytest.mark.parametrize("nblocks,method", [(2, "metis"), (5, "sfc")])
+def test_decomposition_test_P_blocks_equal_one_block_bitwise(nblocks, method):
+    case1, blocks1 = common.make_case(4, 1, nVertLevels=10, num_scalars=2)
+    caseP, blocksP = common.make_case(4, nblocks, nVertLevels=10, num_scalars=2, method=method)
+    for bl in (blocks1, blocksP):
+        for b in bl:
+            b.field("scalars@1")[:-1, :, 1] = (np.sin(2 * b.field("latCell")) ** 2)[:-1, None]
+    m1 = common.OracleModel(blocks1, common.level_config(4))
+    mP = common.OracleModel(blocksP, common.level_config(4))
+    m1.init(); mP.init()
+    m1.step(3); mP.step(3)
+    for ib, b in enumerate(blocksP):
+        nown = int(b.cfg()["nCellsSolve"])
+        ids = b.field("indexToCellID")[:nown]
+        for n in ("theta_m@1", "rho_zz@1", "w@1", "scalars@1"):
+            assert np.array_equal(mP.field(ib, n)[:nown], m1.field(0, n)[ids - 1]), (ib, n)
+        nE = int(b.cfg()["nEdgesSolve"])
+        eids = b.field("indexToEdgeID")[:nE]
+        assert np.array_equal(mP.field(ib, "u@1")[:nE], m1.field(0, "u@1")[eids - 1])
