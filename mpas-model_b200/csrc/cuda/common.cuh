@@ -38,6 +38,37 @@ __device__ __forceinline__ real flux3(real q_im2, real q_im1, real q_i, real q_i
     return flux4(q_im2, q_im1, q_i, q_ip1, ua) + coef3 * fabs(ua) * ((q_ip1 - q_im2) - (real)3. * (q_i - q_im1)) / (real)12.0;
 }
 
+// exner = x ** rcv with rcv = rgas/(cp-rgas) (TI:3027, 5980).  The reference's gfortran build calls libm pow, which
+// is (nearly always) correctly rounded; CUDA's pow is only within 2 ulp and differs from it in the last place
+// for ~17% of the arguments, which is the ONLY arithmetic difference between this library and the oracle.
+// In double precision rcv = fl(0.4) and 5*rcv - 2 = 2^-53 exactly, so r = x**rcv solves r^5 = x^2 * x^(2^-53):
+// one Newton step on CUDA's pow with the residual r0^5 - x^2 (1 + 2^-53 ln x) evaluated in double-double
+// (exact products through fma) gives the correctly rounded value except within ~1e-4 ulp of a rounding tie.
+__device__ __forceinline__ real pow_rcv(real x, real rcv) {
+#ifdef SINGLE_PRECISION
+    return powf(x, rcv);
+#else
+    const double r0 = pow(x, rcv);
+    const double eps = __fma_rn(5.0, rcv, -2.0);
+    if (eps != 0x1p-53 || !(x > 0.0) || !(r0 > 0.0) || isinf(r0)) return r0;
+    // r0^2, r0^4, r0^5 in double-double
+    const double h2 = r0 * r0, l2 = __fma_rn(r0, r0, -h2);
+    double p = h2 * h2, e = __fma_rn(h2, h2, -p);
+    e = e + (h2 * l2 + l2 * h2);
+    const double h4 = p + e, l4 = e - (h4 - p);
+    p = h4 * r0;
+    e = __fma_rn(h4, r0, -p);
+    e = e + l4 * r0;
+    const double h5 = p + e, l5 = e - (h5 - p);
+    // T = x^2 (1 + eps ln x)
+    const double xh = x * x, xl = __fma_rn(x, x, -xh);
+    const double tsmall = xh * (eps * log(x));
+    const double diff = (h5 - xh) + ((l5 - xl) - tsmall);
+    const double delta = diff / xh;
+    return r0 + (-r0 * delta / 5.0);
+#endif
+}
+
 // ---- library state ---------------------------------------------------------------------------
 cudaStream_t stream();                 // stream every kernel of the library is launched on
 void set_stream(cudaStream_t s);

@@ -47,7 +47,7 @@ __global__ void __launch_bounds__(256) recover_cell_kernel(RecCellP p) {
         p.theta_m[ic] = (rtheta_p + rtb) / rho_zz;
         if (p.rk_step == 3) {
             const real zzk = p.zz[ic];
-            const real ex = pow(zzk * (MPAS_RGAS / p0) * (rtheta_p + rtb), rcv);
+            const real ex = pow_rcv(zzk * (MPAS_RGAS / p0) * (rtheta_p + rtb), rcv);
             p.exner[ic] = ex;
             p.pressure_p[ic] = zzk * MPAS_RGAS * (ex * rtheta_p + rtb * (ex - p.exner_base[ic]));
         }

@@ -186,8 +186,8 @@ __global__ void __launch_bounds__(256) icd_cell1_kernel(IcdP p) {  // TI:5909-59
     p.rho_p[ic] = rho_p;
     p.rtheta_base[ic] = rtb;
     p.rtheta_p[ic] = rtp;
-    const real ex = pow(zzk * (MPAS_RGAS / p0) * (rtp + rtb), rcv);
-    const real exb = pow(zzk * (MPAS_RGAS / p0) * (rtb), rcv);
+    const real ex = pow_rcv(zzk * (MPAS_RGAS / p0) * (rtp + rtb), rcv);
+    const real exb = pow_rcv(zzk * (MPAS_RGAS / p0) * (rtb), rcv);
     p.exner[ic] = ex;
     p.exner_base[ic] = exb;
     p.pressure_p[ic] = zzk * MPAS_RGAS * (ex * rtp + rtb * (ex - exb));

@@ -56,6 +56,7 @@ def oracle():
         L.oracle_model_exchange.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         L.oracle_model_init.argtypes = [C.c_void_p]
         L.oracle_model_step.argtypes = [C.c_void_p, C.c_int]
+        L.oracle_set_option.argtypes = [C.c_char_p, C.c_int]
         L.oracle_model_call.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.c_int]
         L.oracle_model_exchange_count.restype = C.c_long
         L.oracle_model_exchange_count.argtypes = [C.c_void_p]
@@ -139,6 +140,11 @@ def has_gpu():
         return host.lib().mpas_b200_device_count() > 0
     except Exception:
         return False
+
+
+def oracle_set_option(name, value):
+    """cr_pow=1: the oracle evaluates exner with a correctly rounded pow instead of libm's (see oracle/dycore_oracle.cpp)"""
+    assert oracle().oracle_set_option(name.encode(), int(value)) == 0
 
 
 def make_case(level, nblocks=1, nVertLevels=26, init_case=2, num_scalars=1, method="sfc", lloyd=10, sfc=True):

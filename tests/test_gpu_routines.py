@@ -37,7 +37,9 @@ def _all_real_fields(blocks):
     return [n for n in blocks[0].names() if blocks[0].info(n)[0] == 0]
 
 
-def _check(blocks, gpu, ora, exact=True, tol=0.0, skip=()):
+# wdtn is per-scalar scratch of the mono routine: the reference stores the limited vertical flux back into it
+# (TI:4145-4153), the GPU path keeps that value in registers (mono_update_kernel) -- not an output
+def _check(blocks, gpu, ora, exact=True, tol=0.0, skip=("wdtn",)):
     bad = []
     for ib in range(len(blocks)):
         for n in _all_real_fields(blocks):
@@ -100,7 +102,9 @@ def test_recover_rk3_pow_within_last_place(state):
         g, o = gpu.field(ib, "exner"), ora.field(ib, "exner")
         ulp = np.abs(g - o) / np.spacing(np.abs(o))
         assert ulp.max() <= 1.0, ulp.max()
-        print("exner: fraction differing in the last place", float((ulp > 0).mean()))
+        frac = float((ulp > 0).mean())
+        print("exner: fraction differing in the last place", frac)
+        assert frac < 5e-3  # pow_rcv is correctly rounded; glibc's pow is not in ~1e-3 of the cases
     _check(blocks, gpu, ora, exact=False, tol=1e-13)
     # re-synchronise the two states so later tests start from identical inputs
     for ib in range(len(blocks)):

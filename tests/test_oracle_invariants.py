@@ -130,3 +130,25 @@ def test_decomposition_test_P_blocks_equal_one_block_bitwise(nblocks, method):
         nE = int(b.cfg()["nEdgesSolve"])
         eids = b.field("indexToEdgeID")[:nE]
         assert np.array_equal(mP.field(ib, "u@1")[:nE], m1.field(0, "u@1")[eids - 1])
+
+
+def test_libm_pow_noise_floor_of_the_reference_arithmetic():
+    """The reference calls libm pow for exner (TI:3027).  Swapping it for a correctly rounded pow changes exner in the
+    last place for ~1e-3 of the points; this measures how much of that the small residual field w amplifies -- the
+    floor below which 'parity with the reference' of w is libm-dependent, not implementation-dependent."""
+    case, blocks = common.make_case(4, 1, nVertLevels=26, num_scalars=1)
+    cfg = common.level_config(4)
+    a = common.OracleModel(blocks, cfg)
+    a.init(); a.step(10)
+    ua, wa, ta = a.field(0, "u@1").copy(), a.field(0, "w@1").copy(), a.field(0, "theta_m@1").copy()
+    case2, blocks2 = common.make_case(4, 1, nVertLevels=26, num_scalars=1)
+    common.oracle_set_option("cr_pow", 1)
+    try:
+        b = common.OracleModel(blocks2, cfg)
+        b.init(); b.step(10)
+    finally:
+        common.oracle_set_option("cr_pow", 0)
+    eu, ew, et = common.rel_l2(b.field(0, "u@1"), ua), common.rel_l2(b.field(0, "w@1"), wa), common.rel_l2(b.field(0, "theta_m@1"), ta)
+    print("libm vs correctly rounded pow after 10 steps: u %.2e  w %.2e  theta_m %.2e" % (eu, ew, et))
+    assert eu < 1e-13 and et < 1e-14
+    assert 0 < ew < 1e-9
