@@ -36,6 +36,8 @@ int mpas_b200_download(void* host);
 void* mpas_b200_device_ptr(const void* host);
 int mpas_b200_synchronize(void);
 long long mpas_b200_launch_count(void);
+int mpas_b200_timer_start(void);    /* CUDA-event stopwatch on the library stream */
+double mpas_b200_timer_stop(void);  /* elapsed ms since timer_start, after synchronising */
 int mpas_b200_finalize(void);
 
 /* ---- Layer 1: work routines ---- */

@@ -137,6 +137,25 @@ int mpas_b200_synchronize() {
 
 long long mpas_b200_launch_count() { return launches(); }
 
+// CUDA-event stopwatch on the library stream (bench.py times the step loop with it: torch.cuda.Event only sees
+// torch's current stream)
+static cudaEvent_t g_ev0 = nullptr, g_ev1 = nullptr;
+int mpas_b200_timer_start() {
+    if (!g_ev0) { cudaEventCreate(&g_ev0); cudaEventCreate(&g_ev1); }
+    cudaError_t e = cudaEventRecord(g_ev0, stream());
+    if (e != cudaSuccess) return fail("mpas_b200_timer_start", e);
+    return 0;
+}
+double mpas_b200_timer_stop() {
+    if (!g_ev0) return -1.0;
+    cudaEventRecord(g_ev1, stream());
+    cudaError_t e = cudaEventSynchronize(g_ev1);
+    if (e != cudaSuccess) { fail("mpas_b200_timer_stop", e); return -1.0; }
+    float ms = 0;
+    cudaEventElapsedTime(&ms, g_ev0, g_ev1);
+    return (double)ms;
+}
+
 int mpas_b200_finalize() {
     std::lock_guard<std::mutex> lk(g_mu);
     for (auto& kv : g_reg) cudaFree(kv.second.dev);

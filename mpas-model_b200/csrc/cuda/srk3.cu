@@ -447,10 +447,16 @@ int dycore_step(Dycore& m) {
         cudaGraphExec_t& ge = m.graph_exec[m.parity];
         if (!ge) {
             cudaGraph_t g;
+            const long long before = launches();
+            const long xbefore = m.nExchanges;
             cudaError_t e = cudaStreamBeginCapture(stream(), cudaStreamCaptureModeThreadLocal);
             if (e != cudaSuccess) return fail("cudaStreamBeginCapture", e);
             rc = srk3_body(m);
             e = cudaStreamEndCapture(stream(), &g);
+            m.graph_nodes[m.parity] = launches() - before;  // kernels / copies recorded, not yet executed
+            m.graph_exchanges[m.parity] = m.nExchanges - xbefore;
+            count_launch(-(int)m.graph_nodes[m.parity]);
+            m.nExchanges = xbefore;
             if (rc) return rc;
             if (e != cudaSuccess) return fail("cudaStreamEndCapture", e);
             e = cudaGraphInstantiate(&ge, g, 0);
@@ -459,7 +465,8 @@ int dycore_step(Dycore& m) {
         }
         cudaError_t e = cudaGraphLaunch(ge, stream());
         if (e != cudaSuccess) return fail("cudaGraphLaunch", e);
-        count_launch();
+        count_launch((int)m.graph_nodes[m.parity]);
+        m.nExchanges += m.graph_exchanges[m.parity];
     } else {
         rc = srk3_body(m);
         if (rc) return rc;

@@ -52,6 +52,7 @@ def lib():
         _lib.mpas_b200_device_ptr.restype = C.c_void_p
         _lib.mpas_b200_device_ptr.argtypes = [C.c_void_p]
         _lib.mpas_b200_launch_count.restype = C.c_longlong
+        _lib.mpas_b200_timer_stop.restype = C.c_double
         _lib.mpas_b200_dycore_create.restype = C.c_void_p
         _lib.mpas_b200_dycore_create.argtypes = [C.c_int, C.c_int, C.c_int]
         _lib.mpas_b200_dycore_destroy.argtypes = [C.c_void_p]

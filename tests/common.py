@@ -28,7 +28,9 @@ host = load_pkg_module("host")
 
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "liboracle.so")
+ORACLE_PERF_LIB = os.path.join(ORACLE_DIR, "_build", "liboracle_perf.so")  # -O3 -march=native: the timed CPU baseline
 _oracle = None
+_oracle_perf = None
 
 # nominal grid spacing (m) and time step (s) per icosahedral level; config_dt scales with dx from the
 # Registry default 720 s at 120 km (Registry.xml nhyd_model record)
@@ -40,12 +42,23 @@ def level_config(level):
     return dict(config_dt=720.0 * dx / 120000.0, config_len_disp=dx)
 
 
-def oracle():
-    global _oracle
+def oracle(perf=False):
+    global _oracle, _oracle_perf
+    if perf:
+        if _oracle_perf is None:
+            if not os.path.exists(ORACLE_PERF_LIB):
+                subprocess.check_call(["make", "-s", "-C", ORACLE_DIR])
+            _oracle_perf = _bind_oracle(C.CDLL(ORACLE_PERF_LIB))
+        return _oracle_perf
     if _oracle is None:
         if not os.path.exists(ORACLE_LIB):
             subprocess.check_call(["make", "-s", "-C", ORACLE_DIR])
-        L = C.CDLL(ORACLE_LIB)
+        _oracle = _bind_oracle(C.CDLL(ORACLE_LIB))
+    return _oracle
+
+
+def _bind_oracle(L):
+    if True:
         L.oracle_last_error.restype = C.c_char_p
         L.oracle_model_create.restype = C.c_void_p
         L.oracle_model_create.argtypes = [C.c_int]
@@ -62,15 +75,14 @@ def oracle():
         L.oracle_model_exchange_count.argtypes = [C.c_void_p]
         L.oracle_model_get_field.restype = C.c_void_p
         L.oracle_model_get_field.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
-        _oracle = L
-    return _oracle
+    return L
 
 
 class OracleModel:
     """P virtual ranks of the oracle dycore operating in place on the host blocks' pools."""
 
-    def __init__(self, blocks, cfg):
-        self.L = oracle()
+    def __init__(self, blocks, cfg, perf=False):
+        self.L = oracle(perf)
         self.blocks = blocks
         self.h = self.L.oracle_model_create(len(blocks))
         self._keep = []
