@@ -96,6 +96,7 @@ def parse():
     ap.add_argument("--scalars", type=int, default=4)
     ap.add_argument("--lloyd", type=int, default=5)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--ktime", action="store_true", help="also print per-kernel CUDA-event times of one eager step to stderr")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of the bounded cpu_baseline sample")
@@ -269,6 +270,19 @@ def run_b200(a):
     dy.step(nt)
     timers = dy.timers()
     dy.set_option("timing", 0)
+    if a.ktime and rank == 0:
+        import ctypes as C
+        L_.mpas_b200_ktime_enable(1)
+        dy.set_option("graph", 0)
+        dy.step(2)
+        buf = C.create_string_buffer(1 << 16)
+        L_.mpas_b200_ktime_report(buf, 1 << 16)
+        L_.mpas_b200_ktime_enable(0)
+        dy.set_option("graph", 1 if use_graph else 0)
+        rows = [ln.split() for ln in buf.value.decode().splitlines()]
+        tot = sum(float(r[1]) for r in rows)
+        for r in sorted(rows, key=lambda r: -float(r[1])):
+            print("KTIME %-28s %8.3f ms/step %5.1f calls/step %8.1f us/call %5.1f%%" % (r[0], float(r[1]) / 2, int(r[2]) / 2, 1e3 * float(r[1]) / int(r[2]), 100 * float(r[1]) / tot), file=sys.stderr)
     words = words_per_call(a.scalars)
     nCS_total = nCS
     phases = {}

@@ -38,6 +38,8 @@ int mpas_b200_synchronize(void);
 long long mpas_b200_launch_count(void);
 int mpas_b200_timer_start(void);    /* CUDA-event stopwatch on the library stream */
 double mpas_b200_timer_stop(void);  /* elapsed ms since timer_start, after synchronising */
+int mpas_b200_ktime_enable(int on);                /* per-kernel CUDA-event timing of eager launches */
+int mpas_b200_ktime_report(char* buf, int cap);    /* lines "kernel ms calls"; returns needed size if cap is too small */
 int mpas_b200_finalize(void);
 
 /* ---- Layer 1: work routines ---- */

@@ -254,7 +254,9 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
             }
             if (shm > 200 * 1024) return fail_msg("acoustic_cell_kernel: nVertLevels too large for the shared-memory staging");
             int nblocks = cdiv(ncols, wpb);
+            ktime_begin("acoustic_cell_kernel");
             acoustic_cell_kernel<<<nblocks, wpb * 32, shm, stream()>>>(p);
+            ktime_end();
             count_launch();
             KCHECK("acoustic_cell_kernel");
         }

@@ -77,6 +77,11 @@ int fail_msg(const std::string& msg);
 long long launches();                  // kernels launched by the library so far
 void count_launch(int n = 1);
 
+// Persistent device workspace owned by the library (the reference allocates/deallocates its scratch around every
+// phase, TI:592-626; here it lives for the life of the process).  Grows on demand; never call inside stream capture
+// before the first eager step has sized it.
+real* workspace(int slot, size_t count);
+
 // Translate a pointer handed over the C ABI: a registered host address (anywhere inside a
 // registered range) maps to its device mirror; anything else is taken to be a device pointer.
 void* xlate(const void* p);
@@ -87,11 +92,17 @@ inline const T* X(const T* p) { return (const T*)xlate((const void*)p); }
 
 inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 
+// optional per-kernel CUDA-event timing (mpas_b200_ktime_enable); no-ops when disabled or during stream capture
+void ktime_begin(const char* kernel_name);
+void ktime_end();
+
 #define KLAUNCH(kernel, nthreads_total, block, ...)                                          \
     do {                                                                                     \
         long long _n = (long long)(nthreads_total);                                          \
         if (_n > 0) {                                                                        \
+            mpasb200::ktime_begin(#kernel);                                                  \
             kernel<<<mpasb200::cdiv(_n, (block)), (block), 0, mpasb200::stream()>>>(__VA_ARGS__); \
+            mpasb200::ktime_end();                                                           \
             mpasb200::count_launch();                                                        \
         }                                                                                    \
     } while (0)
@@ -100,6 +111,23 @@ inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
     do {                                                       \
         cudaError_t _e = cudaGetLastError();                   \
         if (_e != cudaSuccess) return mpasb200::fail(where, _e); \
+    } while (0)
+
+// warp-per-column mapping: WPB warps per block, one mesh element (cell / edge / vertex) per warp, lanes along k
+#define WPB 8
+#define WARP_ENTITY(first, count)                                   \
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;     \
+    const int _ent0 = blockIdx.x * WPB + warp;                      \
+    if (_ent0 >= (count)) return;                                   \
+    const int ent = (first) + _ent0
+#define WLAUNCH(kernel, count, shmem, ...)                                                              \
+    do {                                                                                                \
+        if ((count) > 0) {                                                                              \
+            mpasb200::ktime_begin(#kernel);                                                             \
+            kernel<<<mpasb200::cdiv((count), WPB), WPB * 32, (shmem), mpasb200::stream()>>>(__VA_ARGS__); \
+            mpasb200::ktime_end();                                                                      \
+            mpasb200::count_launch();                                                                   \
+        }                                                                                               \
     } while (0)
 
 // flattened (k, column) thread mapping: k fastest so that a warp reads contiguous levels

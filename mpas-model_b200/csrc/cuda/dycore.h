@@ -68,6 +68,7 @@ struct Dycore {
     cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};
     long long graph_nodes[2] = {0, 0};
     long graph_exchanges[2] = {0, 0};
+    long steps_done = 0;
     int parity = 0;  // number of steps taken mod 2 (time levels swap every step)
     real* d_reduce = nullptr;
 };

@@ -10,14 +10,17 @@
 //   dt_vertex_mix_kernel all verts   rk1: delsq_vorticity TI:4893-4904
 //   dt_cell_mix_kernel   all cells   rk1: delsq_divergence TI:4908-4920, del2 w + delsq_w TI:5097-5128,
 //                                    del2 theta + delsq_theta TI:5276-5300
+//   dt_edge_flux_kernel  edges of    high-order horizontal fluxes of theta_m and w, once per edge (library workspace)
+//                        owned cells
 //   dt_edge_kernel       owned edges vertical advection of u TI:4792-4807, nonlinear Coriolis TI:4811-4820,
 //                                    KE gradient TI:4823-4838, rk1: del4 u TI:4924-4944, vertical mixing
 //                                    TI:4949-5006, Rayleigh damping TI:5015-5028, final sum TI:5030-5036
-//   dt_cell_w_kernel     owned cells horizontal advection of w TI:5046-5074, rk1: del4 w TI:5134-5154,
-//                                    vertical advection, pgf + buoyancy, final sum TI:5167-5223
-//   dt_cell_theta_kernel owned cells horizontal advection of theta_m TI:5231-5269, rk1: del4 theta
-//                                    TI:5304-5325, vertical advection, diabatic, vertical mixing, final sum
-//                                    TI:5331-5414
+//   dt_cell_kernel       owned cells w: flux divergence TI:5046-5074, rk1 del4 TI:5134-5154, vertical advection,
+//                                    pgf + buoyancy, final sum TI:5167-5223; theta_m: flux divergence TI:5231-5269,
+//                                    rk1 del4 TI:5304-5325, vertical advection, diabatic, vertical mixing, final
+//                                    sum TI:5331-5414
+// The last three are warp-per-column kernels (lanes along k, per-column stencil metadata staged once in shared
+// memory, vertical flux columns in shared memory); the others one thread per (k, element), k fastest.
 // Every sum over edgesOnCell / edgesOnEdge / advCellsForEdge keeps the reference's index order and
 // is a gather (no atomics), so results are independent of the launch geometry.
 #include "common.cuh"
@@ -27,7 +30,7 @@ using namespace mpasb200;
 namespace {
 
 struct DtP {
-    int L, mE, mE2, vD, rk_step;
+    int L, mE, mE2, vD, rk_step, nCellsSolve;
     int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, edgeSolveStart, edgeSolveEnd, nEdgesSolveLoop;
     int vertexStart, nVerticesLoop;
     int mixing, mix_full, rayleigh_damp_u, n_rayleigh_levels;
@@ -180,6 +183,53 @@ __global__ void __launch_bounds__(256) dt_cell_mix_kernel(DtP p) {  // rk_step =
     p.tend_theta_euler[ic] = tte;
 }
 
+// ---- warp-per-column kernels: one mesh element per warp, lanes along k.  The k-independent stencil metadata
+// (neighbour indices, weights, signs) is fetched ONCE per warp into shared memory instead of once per level. ----
+
+// High-order horizontal fluxes of theta_m and w through every edge of an owned cell, evaluated once per edge
+// (the reference evaluates each edge's stencil from both adjacent cells, TI:5046-5074, 5231-5252):
+//   ft (k,e) = ru(k,e)        * sum_j (adv_coefs(j,e) +- adv_coefs_3rd(j,e)) * theta_m(k, advCell_j)     k = 1..L
+//   fw (k,e) = ru_edge_w(k,e) * sum_j (adv_coefs(j,e) +- adv_coefs_3rd(j,e)) * w(k, advCell_j)           k = 2..L
+//   ft2(k,e) = dvEdge * (ru_save - ru) * 0.5 * (theta_m_save(c2) + theta_m_save(c1))   (rk_step > 1, TI:5256-5269)
+// +- is Fortran sign(1, flux); a + (+-1)*b == a +- b bit for bit, and multiplying by edgesOnCell_sign = +-1 later is
+// exact, so the cell kernels reproduce the reference's sums exactly.
+__global__ void __launch_bounds__(WPB * 32) dt_edge_flux_kernel(DtP p, real* __restrict__ ft, real* __restrict__ fw, real* __restrict__ ft2) {
+    __shared__ int s_cell[WPB][16];
+    __shared__ real s_cp[WPB][16], s_cm[WPB][16];
+    const int L = p.L, L1 = L + 1;
+    WARP_ENTITY(p.edgeStart, p.nEdgesLoop);
+    const int iEdge = ent;
+    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    if (!(cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve)) return;
+    const int n = p.nAdvCellsForEdge[iEdge - 1];
+    if (lane < n) {
+        s_cell[warp][lane] = p.advCellsForEdge[IX2(lane + 1, iEdge, 15)];
+        const real c = p.adv_coefs[IX2(lane + 1, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(lane + 1, iEdge, 15)];
+        s_cp[warp][lane] = c + c3;
+        s_cm[warp][lane] = c - c3;
+    }
+    __syncwarp();
+    const real dv = p.dvEdge[iEdge - 1];
+    for (int k = lane + 1; k <= L; k += 32) {
+        const size_t ie = IX2(k, iEdge, L);
+        const real rue = p.ru[ie];
+        {
+            const real* tab = signbit(rue) ? s_cm[warp] : s_cp[warp];
+            real flux = 0.0;
+            for (int j = 0; j < n; ++j) flux = flux + tab[j] * p.theta_m[IX2(k, s_cell[warp][j], L)];
+            ft[ie] = rue * flux;
+        }
+        if (k >= 2) {
+            const real ru_edge_w = p.fzm[k - 1] * rue + p.fzp[k - 1] * p.ru[ie - 1];
+            const real* tab = signbit(ru_edge_w) ? s_cm[warp] : s_cp[warp];
+            real flux = 0.0;
+            for (int j = 0; j < n; ++j) flux = flux + tab[j] * p.w[IX2(k, s_cell[warp][j], L1)];
+            fw[ie] = ru_edge_w * flux;
+        }
+        if (p.rk_step > 1) ft2[ie] = dv * (p.ru_save[ie] - rue) * (real)0.5 * (p.theta_m_save[IX2(k, cell2, L)] + p.theta_m_save[IX2(k, cell1, L)]);
+    }
+}
+
 __device__ __forceinline__ real wduz_at(const DtP& p, int kk, int iEdge, int cell1, int cell2) {
     const int L = p.L, L1 = L + 1;
     if (kk == 1 || kk == L1) return (real)0.;
@@ -188,61 +238,79 @@ __device__ __forceinline__ real wduz_at(const DtP& p, int kk, int iEdge, int cel
     return flux3(p.u[IX2(kk - 2, iEdge, L)], p.u[IX2(kk - 1, iEdge, L)], p.u[IX2(kk, iEdge, L)], p.u[IX2(kk + 1, iEdge, L)], rwe, (real)1.0);
 }
 
-__global__ void __launch_bounds__(256) dt_edge_kernel(DtP p) {
+// dynamic shared memory: WPB * (L + 2) reals (vertical flux column of each warp)
+__global__ void __launch_bounds__(WPB * 32) dt_edge_kernel(DtP p) {
+    extern __shared__ real s_dyn[];
+    __shared__ int s_eoe[WPB][16];
+    __shared__ real s_wt[WPB][16];
     const int L = p.L, L1 = L + 1, mE2 = p.mE2;
-    FLAT_KC(p.nEdgesSolveLoop, L);
-    const int iEdge = p.edgeSolveStart + _c0;
+    WARP_ENTITY(p.edgeSolveStart, p.nEdgesSolveLoop);
+    const int iEdge = ent;
+    real* wz = s_dyn + (size_t)warp * (L + 2);
     const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
-    const size_t ie = IX2(k, iEdge, L), i1 = IX2(k, cell1, L), i2 = IX2(k, cell2, L);
-    const real wlo = wduz_at(p, k, iEdge, cell1, cell2), whi = wduz_at(p, k + 1, iEdge, cell1, cell2);
-    real tu = -p.rdzw[k - 1] * (whi - wlo);
-    real q = 0.0;
     const int neoe = p.nEdgesOnEdge[iEdge - 1];
-    const real pv_e = p.pv_edge[ie];
-    for (int j = 1; j <= neoe; ++j) {
-        const int eoe = p.edgesOnEdge[IX2(j, iEdge, mE2)];
-        const size_t io = IX2(k, eoe, L);
-        const real workpv = (real)0.5 * (pv_e + p.pv_edge[io]);
-        q = q + p.weightsOnEdge[IX2(j, iEdge, mE2)] * p.u[io] * workpv;
+    if (lane < neoe) {
+        s_eoe[warp][lane] = p.edgesOnEdge[IX2(lane + 1, iEdge, mE2)];
+        s_wt[warp][lane] = p.weightsOnEdge[IX2(lane + 1, iEdge, mE2)];
     }
-    const real ue = p.u[ie], rho_e = p.rho_edge[ie], idc = p.invDcEdge[iEdge - 1];
-    tu = tu + rho_e * (q - (p.ke[i2] - p.ke[i1]) * idc) - ue * (real)0.5 * (p.h_divergence[i1] + p.h_divergence[i2]);
-    real te = p.tend_u_euler[ie];
-    if (p.rk_step == 1) {
-        bool changed = false;
-        if (p.h_mom_eddy_visc4 > (real)0.0) {  // TI:4924-4944
-            const int vertex1 = p.verticesOnEdge[IX2(1, iEdge, 2)], vertex2 = p.verticesOnEdge[IX2(2, iEdge, 2)];
-            const real u_mix_scale = p.meshScalingDel4[iEdge - 1] * p.h_mom_eddy_visc4;
-            const real r_dc = u_mix_scale * p.del4u_div_factor * idc;
-            const real r_dv = u_mix_scale * fmin(p.invDvEdge[iEdge - 1], 4 * idc);
-            const real u_diffusion = rho_e * ((p.delsq_divergence[i2] - p.delsq_divergence[i1]) * r_dc -
-                                              (p.delsq_vorticity[IX2(k, vertex2, L)] - p.delsq_vorticity[IX2(k, vertex1, L)]) * r_dv);
-            te = te - u_diffusion;
-            changed = true;
+    for (int k = lane + 1; k <= L1; k += 32) wz[k] = wduz_at(p, k, iEdge, cell1, cell2);
+    __syncwarp();
+    const real idc = p.invDcEdge[iEdge - 1];
+    const bool del4 = (p.rk_step == 1 && p.h_mom_eddy_visc4 > (real)0.0);
+    int vertex1 = 0, vertex2 = 0;
+    real r_dc = 0, r_dv = 0;
+    if (del4) {  // TI:4924-4944
+        vertex1 = p.verticesOnEdge[IX2(1, iEdge, 2)];
+        vertex2 = p.verticesOnEdge[IX2(2, iEdge, 2)];
+        const real u_mix_scale = p.meshScalingDel4[iEdge - 1] * p.h_mom_eddy_visc4;
+        r_dc = u_mix_scale * p.del4u_div_factor * idc;
+        r_dv = u_mix_scale * fmin(p.invDvEdge[iEdge - 1], 4 * idc);
+    }
+    for (int k = lane + 1; k <= L; k += 32) {
+        const size_t ie = IX2(k, iEdge, L), i1 = IX2(k, cell1, L), i2 = IX2(k, cell2, L);
+        real tu = -p.rdzw[k - 1] * (wz[k + 1] - wz[k]);
+        real q = 0.0;
+        const real pv_e = p.pv_edge[ie];
+        for (int j = 0; j < neoe; ++j) {
+            const size_t io = IX2(k, s_eoe[warp][j], L);
+            const real workpv = (real)0.5 * (pv_e + p.pv_edge[io]);
+            q = q + s_wt[warp][j] * p.u[io] * workpv;
         }
-        if (p.v_mom_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:4949-5006
-            real um[3];
-            for (int d = -1; d <= 1; ++d) {
-                const int kk = k + d;
-                real x = p.u[IX2(kk, iEdge, L)];
-                if (!p.mix_full) x = x - p.u_init[kk - 1] * cos(p.angleEdge[iEdge - 1]) - p.v_init[kk - 1] * sin(p.angleEdge[iEdge - 1]);
-                um[d + 1] = x;
+        const real ue = p.u[ie], rho_e = p.rho_edge[ie];
+        tu = tu + rho_e * (q - (p.ke[i2] - p.ke[i1]) * idc) - ue * (real)0.5 * (p.h_divergence[i1] + p.h_divergence[i2]);
+        real te = p.tend_u_euler[ie];
+        if (p.rk_step == 1) {
+            bool changed = false;
+            if (del4) {
+                const real u_diffusion = rho_e * ((p.delsq_divergence[i2] - p.delsq_divergence[i1]) * r_dc -
+                                                  (p.delsq_vorticity[IX2(k, vertex2, L)] - p.delsq_vorticity[IX2(k, vertex1, L)]) * r_dv);
+                te = te - u_diffusion;
+                changed = true;
             }
-            const real z1 = (real)0.5 * (p.zgrid[IX2(k - 1, cell1, L1)] + p.zgrid[IX2(k - 1, cell2, L1)]);
-            const real z2 = (real)0.5 * (p.zgrid[IX2(k, cell1, L1)] + p.zgrid[IX2(k, cell2, L1)]);
-            const real z3 = (real)0.5 * (p.zgrid[IX2(k + 1, cell1, L1)] + p.zgrid[IX2(k + 1, cell2, L1)]);
-            const real z4 = (real)0.5 * (p.zgrid[IX2(k + 2, cell1, L1)] + p.zgrid[IX2(k + 2, cell2, L1)]);
-            const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
-            te = te + rho_e * p.v_mom_eddy_visc2 * ((um[2] - um[1]) / (zp - z0) - (um[1] - um[0]) / (z0 - zm)) / ((real)0.5 * (zp - zm));
-            changed = true;
+            if (p.v_mom_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:4949-5006
+                real um[3];
+                for (int d = -1; d <= 1; ++d) {
+                    const int kk = k + d;
+                    real x = p.u[IX2(kk, iEdge, L)];
+                    if (!p.mix_full) x = x - p.u_init[kk - 1] * cos(p.angleEdge[iEdge - 1]) - p.v_init[kk - 1] * sin(p.angleEdge[iEdge - 1]);
+                    um[d + 1] = x;
+                }
+                const real z1 = (real)0.5 * (p.zgrid[IX2(k - 1, cell1, L1)] + p.zgrid[IX2(k - 1, cell2, L1)]);
+                const real z2 = (real)0.5 * (p.zgrid[IX2(k, cell1, L1)] + p.zgrid[IX2(k, cell2, L1)]);
+                const real z3 = (real)0.5 * (p.zgrid[IX2(k + 1, cell1, L1)] + p.zgrid[IX2(k + 1, cell2, L1)]);
+                const real z4 = (real)0.5 * (p.zgrid[IX2(k + 2, cell1, L1)] + p.zgrid[IX2(k + 2, cell2, L1)]);
+                const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
+                te = te + rho_e * p.v_mom_eddy_visc2 * ((um[2] - um[1]) / (zp - z0) - (um[1] - um[0]) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+                changed = true;
+            }
+            if (changed) p.tend_u_euler[ie] = te;
         }
-        if (changed) p.tend_u_euler[ie] = te;
+        if (p.rayleigh_damp_u && k >= L - p.n_rayleigh_levels + 1) {  // TI:5015-5028
+            const real coef = (real)(k - (L - p.n_rayleigh_levels)) * p.rayleigh_coef_inverse;
+            tu = tu - rho_e * ue * coef;
+        }
+        p.tend_u[ie] = tu + te + (p.tend_ru_physics ? p.tend_ru_physics[ie] : (real)0.0);
     }
-    if (p.rayleigh_damp_u && k >= L - p.n_rayleigh_levels + 1) {  // TI:5015-5028
-        const real coef = (real)(k - (L - p.n_rayleigh_levels)) * p.rayleigh_coef_inverse;
-        tu = tu - rho_e * ue * coef;
-    }
-    p.tend_u[ie] = tu + te + (p.tend_ru_physics ? p.tend_ru_physics[ie] : (real)0.0);
 }
 
 __device__ __forceinline__ real wdwz_at(const DtP& p, int kk, int iCell) {
@@ -252,56 +320,6 @@ __device__ __forceinline__ real wdwz_at(const DtP& p, int kk, int iCell) {
     const real wk = p.w[IX2(kk, iCell, L1)], wkm = p.w[IX2(kk - 1, iCell, L1)];
     if (kk == 2 || kk == L) return (real)0.25 * (rwk + rwkm) * (wk + wkm);
     return flux3(p.w[IX2(kk - 2, iCell, L1)], wkm, wk, p.w[IX2(kk + 1, iCell, L1)], (real)0.5 * (rwk + rwkm), (real)1.0);
-}
-
-__global__ void __launch_bounds__(256) dt_cell_w_kernel(DtP p) {
-    const int L = p.L, L1 = L + 1, mE = p.mE;
-    FLAT_KC(p.nCellsSolveLoop, L1);
-    const int iCell = p.cellSolveStart + _c0;
-    const size_t iw = IX2(k, iCell, L1);
-    if (k == 1 || k == L1) {
-        p.tend_w[iw] = 0.0;
-        return;
-    }
-    const int ne = p.nEdgesOnCell[iCell - 1];
-    const real fm = p.fzm[k - 1], fp = p.fzp[k - 1];
-    const real invArea = p.invAreaCell[iCell - 1];
-    real tw = 0.0;
-    real twe = p.tend_w_euler[iw];
-    const bool del4 = (p.rk_step == 1 && p.h_mom_eddy_visc4 > (real)0.0);
-    for (int i = 1; i <= ne; ++i) {
-        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-        const real sgn = p.edgesOnCell_sign[IX2(i, iCell, mE)];
-        const real ru_edge_w = fm * p.ru[IX2(k, iEdge, L)] + fp * p.ru[IX2(k - 1, iEdge, L)];
-        const real s3 = fsign((real)1.0, ru_edge_w);
-        real flux = 0.0;
-        const int n = p.nAdvCellsForEdge[iEdge - 1];
-        for (int j = 1; j <= n; ++j) {
-            const int iAdvCell = p.advCellsForEdge[IX2(j, iEdge, 15)];
-            const real scalar_weight = p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)];
-            flux = flux + scalar_weight * p.w[IX2(k, iAdvCell, L1)];
-        }
-        tw = tw - sgn * ru_edge_w * flux;
-        if (del4) {  // TI:5134-5154
-            const real r_areaCell = p.h_mom_eddy_visc4 * invArea;
-            const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
-            const real edge_sign = p.meshScalingDel4[iEdge - 1] * r_areaCell * p.dvEdge[iEdge - 1] * sgn * p.invDcEdge[iEdge - 1];
-            twe = twe - edge_sign * (p.delsq_w[IX2(k, cell2, L)] - p.delsq_w[IX2(k, cell1, L)]);
-        }
-    }
-    const real flo = wdwz_at(p, k, iCell), fhi = wdwz_at(p, k + 1, iCell);
-    tw = tw * invArea - p.rdzu[k - 1] * (fhi - flo);
-    if (p.rk_step == 1) {
-        const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L);
-        twe = twe - p.cqw[ic] * (p.rdzu[k - 1] * (p.pp[ic] - p.pp[icm]) - (fm * p.dpdz[ic] + fp * p.dpdz[icm]));
-        if (p.v_mom_eddy_visc2 > (real)0.0) {
-            const real wk = p.w[iw];
-            twe = twe + p.v_mom_eddy_visc2 * (real)0.5 * (p.rho_zz[ic] + p.rho_zz[icm]) *
-                            ((p.w[IX2(k + 1, iCell, L1)] - wk) * p.rdzw[k - 1] - (wk - p.w[IX2(k - 1, iCell, L1)]) * p.rdzw[k - 2]) * p.rdzu[k - 1];
-        }
-        p.tend_w_euler[iw] = twe;
-    }
-    p.tend_w[iw] = tw + twe;
 }
 
 __device__ __forceinline__ real wdtz_at(const DtP& p, int kk, int iCell) {
@@ -317,80 +335,105 @@ __device__ __forceinline__ real wdtz_at(const DtP& p, int kk, int iCell) {
     return f + (p.rw_save[IX2(kk, iCell, L1)] - rwk) * (fm * p.theta_m_save[IX2(kk, iCell, L)] + fp * p.theta_m_save[IX2(kk - 1, iCell, L)]);
 }
 
-__global__ void __launch_bounds__(256) dt_cell_theta_kernel(DtP p) {
+// w and theta_m tendencies of one owned cell per warp.  dynamic shared memory: WPB * 2 * (L + 2) reals.
+__global__ void __launch_bounds__(WPB * 32) dt_cell_kernel(DtP p, const real* __restrict__ ft, const real* __restrict__ fw, const real* __restrict__ ft2) {
+    extern __shared__ real s_dyn[];
+    __shared__ int s_edge[WPB][8], s_c1[WPB][8], s_c2[WPB][8];
+    __shared__ real s_sign[WPB][8], s_esw[WPB][8], s_est[WPB][8];
     const int L = p.L, L1 = L + 1, mE = p.mE;
-    FLAT_KC(p.nCellsSolveLoop, L);
-    const int iCell = p.cellSolveStart + _c0;
-    const size_t ic = IX2(k, iCell, L);
+    WARP_ENTITY(p.cellSolveStart, p.nCellsSolveLoop);
+    const int iCell = ent;
+    real* wdw = s_dyn + (size_t)warp * 2 * (L + 2);
+    real* wdt = wdw + (L + 2);
     const int ne = p.nEdgesOnCell[iCell - 1];
     const real invArea = p.invAreaCell[iCell - 1];
-    real tt = 0.0;
-    real tte = p.tend_theta_euler[ic];
-    const bool del4 = (p.rk_step == 1 && p.h_theta_eddy_visc4 > (real)0.0);
-    for (int i = 1; i <= ne; ++i) {
-        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-        const real sgn = p.edgesOnCell_sign[IX2(i, iCell, mE)];
-        const real rue = p.ru[IX2(k, iEdge, L)];
-        const real s3 = fsign((real)1.0, rue);
-        real flux = 0.0;
-        const int n = p.nAdvCellsForEdge[iEdge - 1];
-        for (int j = 1; j <= n; ++j) {
-            const int iAdvCell = p.advCellsForEdge[IX2(j, iEdge, 15)];
-            const real scalar_weight = p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)];
-            flux = flux + scalar_weight * p.theta_m[IX2(k, iAdvCell, L)];
-        }
-        tt = tt - sgn * rue * flux;
-    }
-    if (p.rk_step > 1) {  // TI:5256-5269
-        for (int i = 1; i <= ne; ++i) {
-            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-            const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
-            const size_t ie = IX2(k, iEdge, L);
-            const real flux = p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.dvEdge[iEdge - 1] * (p.ru_save[ie] - p.ru[ie]) * (real)0.5 *
-                              (p.theta_m_save[IX2(k, cell2, L)] + p.theta_m_save[IX2(k, cell1, L)]);
-            tt = tt - flux;
+    const bool del4w = (p.rk_step == 1 && p.h_mom_eddy_visc4 > (real)0.0);
+    const bool del4t = (p.rk_step == 1 && p.h_theta_eddy_visc4 > (real)0.0);
+    if (lane < ne) {
+        const int iEdge = p.edgesOnCell[IX2(lane + 1, iCell, mE)];
+        const real sgn = p.edgesOnCell_sign[IX2(lane + 1, iCell, mE)];
+        s_edge[warp][lane] = iEdge;
+        s_sign[warp][lane] = sgn;
+        if (del4w || del4t) {
+            s_c1[warp][lane] = p.cellsOnEdge[IX2(1, iEdge, 2)];
+            s_c2[warp][lane] = p.cellsOnEdge[IX2(2, iEdge, 2)];
+            const real ms4 = p.meshScalingDel4[iEdge - 1], dv = p.dvEdge[iEdge - 1], idc = p.invDcEdge[iEdge - 1];
+            s_esw[warp][lane] = ms4 * (p.h_mom_eddy_visc4 * invArea) * dv * sgn * idc;                    // TI:5141-5146
+            s_est[warp][lane] = ms4 * (p.h_theta_eddy_visc4 * p.prandtl_inv * invArea) * dv * sgn * idc;  // TI:5309-5315
         }
     }
-    if (del4) {  // TI:5304-5325
-        const real r_areaCell = p.h_theta_eddy_visc4 * p.prandtl_inv * invArea;
-        for (int i = 1; i <= ne; ++i) {
-            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-            const real edge_sign = p.meshScalingDel4[iEdge - 1] * r_areaCell * p.dvEdge[iEdge - 1] * p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.invDcEdge[iEdge - 1];
-            const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
-            tte = tte - edge_sign * (p.delsq_theta[IX2(k, cell2, L)] - p.delsq_theta[IX2(k, cell1, L)]);
-        }
+    for (int k = lane + 1; k <= L1; k += 32) {
+        wdw[k] = wdwz_at(p, k, iCell);
+        wdt[k] = wdtz_at(p, k, iCell);
     }
-    const real flo = wdtz_at(p, k, iCell), fhi = wdtz_at(p, k + 1, iCell);
-    tt = tt * invArea - p.rdzw[k - 1] * (fhi - flo);
-    const real rho = p.rho_zz[ic];
-    if (p.tend_rtheta_adv) p.tend_rtheta_adv[ic] = tt;
-    if (p.rthdynten) p.rthdynten[ic] = tt / rho;
-    tt = tt + rho * (p.rt_diabatic_tend ? p.rt_diabatic_tend[ic] : (real)0.0);
-    if (p.rk_step == 1 && p.v_theta_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:5360-5406
-        const real z1 = p.zgrid[IX2(k - 1, iCell, L1)], z2 = p.zgrid[IX2(k, iCell, L1)], z3 = p.zgrid[IX2(k + 1, iCell, L1)], z4 = p.zgrid[IX2(k + 2, iCell, L1)];
-        const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
-        real a = p.theta_m[IX2(k + 1, iCell, L)], b = p.theta_m[ic], c = p.theta_m[IX2(k - 1, iCell, L)];
-        if (p.mix_full) {
-            tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * ((a - b) / (zp - z0) - (b - c) / (z0 - zm)) / ((real)0.5 * (zp - zm));
-        } else {
-            const real ta = p.t_init[IX2(k + 1, iCell, L)], tb = p.t_init[ic], tc = p.t_init[IX2(k - 1, iCell, L)];
-            tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * (((a - ta) - (b - tb)) / (zp - z0) - ((b - tb) - (c - tc)) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+    __syncwarp();
+    // ---- w, TI:5046-5074, 5134-5154, 5167-5223
+    for (int k = lane + 1; k <= L1; k += 32) {
+        const size_t iw = IX2(k, iCell, L1);
+        if (k == 1 || k == L1) {
+            p.tend_w[iw] = 0.0;
+            continue;
         }
+        real tw = 0.0;
+        real twe = p.tend_w_euler[iw];
+        for (int i = 0; i < ne; ++i) {
+            tw = tw - s_sign[warp][i] * fw[IX2(k, s_edge[warp][i], L)];
+            if (del4w) twe = twe - s_esw[warp][i] * (p.delsq_w[IX2(k, s_c2[warp][i], L)] - p.delsq_w[IX2(k, s_c1[warp][i], L)]);
+        }
+        tw = tw * invArea - p.rdzu[k - 1] * (wdw[k + 1] - wdw[k]);
+        if (p.rk_step == 1) {
+            const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L);
+            twe = twe - p.cqw[ic] * (p.rdzu[k - 1] * (p.pp[ic] - p.pp[icm]) - (p.fzm[k - 1] * p.dpdz[ic] + p.fzp[k - 1] * p.dpdz[icm]));
+            if (p.v_mom_eddy_visc2 > (real)0.0) {
+                const real wk = p.w[iw];
+                twe = twe + p.v_mom_eddy_visc2 * (real)0.5 * (p.rho_zz[ic] + p.rho_zz[icm]) *
+                                ((p.w[IX2(k + 1, iCell, L1)] - wk) * p.rdzw[k - 1] - (wk - p.w[IX2(k - 1, iCell, L1)]) * p.rdzw[k - 2]) * p.rdzu[k - 1];
+            }
+            p.tend_w_euler[iw] = twe;
+        }
+        p.tend_w[iw] = tw + twe;
     }
-    if (p.rk_step == 1 && (del4 || p.v_theta_eddy_visc2 > (real)0.0)) p.tend_theta_euler[ic] = tte;
-    p.tend_theta[ic] = tt + tte + (p.tend_rtheta_physics ? p.tend_rtheta_physics[ic] : (real)0.0);
+    // ---- theta_m, TI:5231-5269, 5304-5325, 5331-5414
+    for (int k = lane + 1; k <= L; k += 32) {
+        const size_t ic = IX2(k, iCell, L);
+        real tt = 0.0;
+        real tte = p.tend_theta_euler[ic];
+        for (int i = 0; i < ne; ++i) tt = tt - s_sign[warp][i] * ft[IX2(k, s_edge[warp][i], L)];
+        if (p.rk_step > 1)
+            for (int i = 0; i < ne; ++i) tt = tt - s_sign[warp][i] * ft2[IX2(k, s_edge[warp][i], L)];
+        if (del4t)
+            for (int i = 0; i < ne; ++i) tte = tte - s_est[warp][i] * (p.delsq_theta[IX2(k, s_c2[warp][i], L)] - p.delsq_theta[IX2(k, s_c1[warp][i], L)]);
+        tt = tt * invArea - p.rdzw[k - 1] * (wdt[k + 1] - wdt[k]);
+        const real rho = p.rho_zz[ic];
+        if (p.tend_rtheta_adv) p.tend_rtheta_adv[ic] = tt;
+        if (p.rthdynten) p.rthdynten[ic] = tt / rho;
+        tt = tt + rho * (p.rt_diabatic_tend ? p.rt_diabatic_tend[ic] : (real)0.0);
+        if (p.rk_step == 1 && p.v_theta_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:5360-5406
+            const real z1 = p.zgrid[IX2(k - 1, iCell, L1)], z2 = p.zgrid[IX2(k, iCell, L1)], z3 = p.zgrid[IX2(k + 1, iCell, L1)], z4 = p.zgrid[IX2(k + 2, iCell, L1)];
+            const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
+            real a = p.theta_m[IX2(k + 1, iCell, L)], b = p.theta_m[ic], c = p.theta_m[IX2(k - 1, iCell, L)];
+            if (p.mix_full) {
+                tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * ((a - b) / (zp - z0) - (b - c) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+            } else {
+                const real ta = p.t_init[IX2(k + 1, iCell, L)], tb = p.t_init[ic], tc = p.t_init[IX2(k - 1, iCell, L)];
+                tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * (((a - ta) - (b - tb)) / (zp - z0) - ((b - tb) - (c - tc)) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+            }
+        }
+        if (p.rk_step == 1 && (del4t || p.v_theta_eddy_visc2 > (real)0.0)) p.tend_theta_euler[ic] = tte;
+        p.tend_theta[ic] = tt + tte + (p.tend_rtheta_physics ? p.tend_rtheta_physics[ic] : (real)0.0);
+    }
 }
 
 }  // namespace
 
 extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
-    (void)nCells; (void)nEdges; (void)nVertices; (void)nCellsSolve; (void)nEdgesSolve; (void)num_scalars; (void)moist_start; (void)moist_end;
+    (void)nCells; (void)nVertices; (void)nEdgesSolve; (void)num_scalars; (void)moist_start; (void)moist_end;
     (void)fEdge; (void)rr; (void)pressure_b; (void)exner; (void)scalars; (void)deriv_two; (void)cellsOnCell; (void)latCell; (void)latEdge;
     (void)qv_init; (void)r_earth; (void)ur_cell; (void)vr_cell; (void)tend_w_pgf; (void)tend_w_buoy; (void)vertexSolveStart; (void)vertexSolveEnd;
     if (nVertLevels < 4) return fail_msg("mpas_b200_compute_dyn_tend_work: nVertLevels must be >= 4");
     if (vertexDegree != 3) return fail_msg("mpas_b200_compute_dyn_tend_work: vertexDegree must be 3");
     DtP p;
-    p.L = nVertLevels; p.mE = maxEdges; p.mE2 = maxEdges2; p.vD = vertexDegree; p.rk_step = rk_step;
+    p.L = nVertLevels; p.mE = maxEdges; p.mE2 = maxEdges2; p.vD = vertexDegree; p.rk_step = rk_step; p.nCellsSolve = nCellsSolve;
     p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
     p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.edgeSolveStart = edgeSolveStart; p.edgeSolveEnd = edgeSolveEnd;
     p.nEdgesSolveLoop = edgeSolveEnd - edgeSolveStart + 1; p.vertexStart = vertexStart; p.nVerticesLoop = vertexEnd - vertexStart + 1;
@@ -446,11 +489,17 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
         KLAUNCH(dt_cell_mix_kernel, (long long)p.nCellsLoop * (L + 1), 256, p);
         KCHECK("dt_cell_mix_kernel");
     }
-    KLAUNCH(dt_edge_kernel, (long long)p.nEdgesSolveLoop * L, 256, p);
+    if (maxEdges > 8 || maxEdges2 > 16) return fail_msg("mpas_b200_compute_dyn_tend_work: maxEdges > 8 or maxEdges2 > 16 not supported");
+    const size_t nEL = (size_t)(nEdges + 1) * L;
+    real* ft = workspace(0, nEL);
+    real* fw = workspace(1, nEL);
+    real* ft2 = workspace(2, nEL);
+    if (!ft || !fw || !ft2) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace");
+    WLAUNCH(dt_edge_flux_kernel, p.nEdgesLoop, 0, p, ft, fw, ft2);
+    KCHECK("dt_edge_flux_kernel");
+    WLAUNCH(dt_edge_kernel, p.nEdgesSolveLoop, (size_t)WPB * (L + 2) * sizeof(real), p);
     KCHECK("dt_edge_kernel");
-    KLAUNCH(dt_cell_w_kernel, (long long)p.nCellsSolveLoop * (L + 1), 256, p);
-    KCHECK("dt_cell_w_kernel");
-    KLAUNCH(dt_cell_theta_kernel, (long long)p.nCellsSolveLoop * L, 256, p);
-    KCHECK("dt_cell_theta_kernel");
+    WLAUNCH(dt_cell_kernel, p.nCellsSolveLoop, (size_t)WPB * 2 * (L + 2) * sizeof(real), p, ft, fw, ft2);
+    KCHECK("dt_cell_kernel");
     return 0;
 }

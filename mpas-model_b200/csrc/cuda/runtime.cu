@@ -6,8 +6,10 @@
 // them to the device mirrors.  Device pointers pass through untouched, so the device-resident
 // dycore driver (dycore.cu) uses the identical entry points.
 #include <cstdio>
+#include <cstring>
 #include <map>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -51,6 +53,79 @@ int fail_msg(const std::string& msg) {
 }
 long long launches() { return g_launches; }
 void count_launch(int n) { g_launches += n; }
+
+namespace {
+struct Ws {
+    real* p = nullptr;
+    size_t count = 0;
+};
+Ws g_ws[16];
+}  // namespace
+real* workspace(int slot, size_t count) {
+    Ws& w = g_ws[slot];
+    if (w.count < count) {
+        if (w.p) {
+            cudaStreamSynchronize(stream());
+            cudaFree(w.p);
+        }
+        if (cudaMalloc(&w.p, count * sizeof(real)) != cudaSuccess) {
+            w.p = nullptr;
+            w.count = 0;
+            return nullptr;
+        }
+        w.count = count;
+    }
+    return w.p;
+}
+
+namespace {
+bool g_ktime = false;
+struct KRec {
+    const char* name;
+    cudaEvent_t e0, e1;
+};
+std::vector<KRec> g_krecs;
+std::vector<cudaEvent_t> g_kpool;
+std::map<std::string, std::pair<double, long>> g_ktot;
+const char* g_kcur = nullptr;
+cudaEvent_t g_ke0 = nullptr;
+cudaEvent_t kev() {
+    if (!g_kpool.empty()) { cudaEvent_t e = g_kpool.back(); g_kpool.pop_back(); return e; }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+void kflush() {
+    if (g_krecs.empty()) return;
+    cudaStreamSynchronize(stream());
+    for (auto& r : g_krecs) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, r.e0, r.e1);
+        auto& t = g_ktot[r.name];
+        t.first += ms;
+        t.second += 1;
+        g_kpool.push_back(r.e0);
+        g_kpool.push_back(r.e1);
+    }
+    g_krecs.clear();
+}
+}  // namespace
+void ktime_begin(const char* name) {
+    if (!g_ktime) return;
+    cudaStreamCaptureStatus st;
+    if (cudaStreamIsCapturing(stream(), &st) != cudaSuccess || st != cudaStreamCaptureStatusNone) return;
+    g_kcur = name;
+    g_ke0 = kev();
+    cudaEventRecord(g_ke0, stream());
+}
+void ktime_end() {
+    if (!g_ktime || !g_kcur) return;
+    cudaEvent_t e1 = kev();
+    cudaEventRecord(e1, stream());
+    g_krecs.push_back({g_kcur, g_ke0, e1});
+    g_kcur = nullptr;
+    if (g_krecs.size() > 4096) kflush();
+}
 
 void* xlate(const void* p) {
     if (!p || g_reg.empty()) return (void*)p;
@@ -156,10 +231,35 @@ double mpas_b200_timer_stop() {
     return (double)ms;
 }
 
+// per-kernel timing: enable, run eager steps, then read "name ms calls" lines
+int mpas_b200_ktime_enable(int on) {
+    kflush();
+    g_ktime = on != 0;
+    if (on) g_ktot.clear();
+    return 0;
+}
+int mpas_b200_ktime_report(char* buf, int cap) {
+    kflush();
+    std::string out;
+    for (auto& kv : g_ktot) {
+        char line[256];
+        snprintf(line, sizeof(line), "%s %.6f %ld\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        out += line;
+    }
+    if ((int)out.size() + 1 > cap) return (int)out.size() + 1;
+    std::memcpy(buf, out.c_str(), out.size() + 1);
+    return 0;
+}
+
 int mpas_b200_finalize() {
     std::lock_guard<std::mutex> lk(g_mu);
     for (auto& kv : g_reg) cudaFree(kv.second.dev);
     g_reg.clear();
+    for (auto& w : g_ws) {
+        if (w.p) cudaFree(w.p);
+        w.p = nullptr;
+        w.count = 0;
+    }
     return 0;
 }
 

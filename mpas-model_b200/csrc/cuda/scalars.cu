@@ -375,7 +375,9 @@ extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
     if (p.nCellsSolveLoop > 0) {
         const size_t shm = (size_t)AS_COLS * p.L * p.ns * sizeof(real);
         if (shm > 48 * 1024) return fail_msg("mpas_b200_advance_scalars_work: nVertLevels*num_scalars too large for the column staging");
+        ktime_begin("as_cell_kernel");
         as_cell_kernel<<<cdiv(p.nCellsSolveLoop, AS_COLS), 256, shm, stream()>>>(p);
+        ktime_end();
         count_launch();
         KCHECK("as_cell_kernel");
     }

@@ -282,7 +282,9 @@ extern "C" int mpas_b200_compute_vert_imp_coefs_work(MPAS_VERTIMP_ARGS) {
             attr_set = true;
         }
         if (shm > 200 * 1024) return fail_msg("vert_imp_kernel: nVertLevels too large for the shared-memory staging");
+        ktime_begin("vert_imp_kernel");
         vert_imp_kernel<<<cdiv(v.nCellsLoop, wpb), wpb * 32, shm, stream()>>>(v);
+        ktime_end();
         count_launch();
         KCHECK("vert_imp_kernel");
     }

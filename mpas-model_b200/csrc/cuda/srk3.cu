@@ -442,7 +442,9 @@ int dycore_step(Dycore& m) {
     int rc = 0;
     // The launch sequence of a step depends only on which buffer currently is time level 1: two graphs
     // (one per parity) replay the whole step with a single launch each.  NCCL send/recv are captured too.
-    const bool graphable = m.use_graph && !m.timing && m.blocks.size() == 1;
+    // The first step of each parity runs eagerly: it sizes the library workspace and builds the halo plans
+    // (both allocate, which a capture forbids).
+    const bool graphable = m.use_graph && !m.timing && m.blocks.size() == 1 && m.steps_done >= 2;
     if (graphable) {
         cudaGraphExec_t& ge = m.graph_exec[m.parity];
         if (!ge) {
@@ -475,6 +477,7 @@ int dycore_step(Dycore& m) {
     for (auto& b : m.blocks)
         for (const char* n : {"u", "w", "theta_m", "rho_zz", "scalars"}) b.swap_levels(n);
     m.parity ^= 1;
+    m.steps_done++;
     flush_timers(m);
     return 0;
 }
