@@ -1,0 +1,56 @@
+"""Decomposition test on real GPUs (COMPASS decomp_test idea): N ranks over NCCL must reproduce the 1-block result
+bit for bit on every owned element.  Launch: python -m torch.distributed.run --nproc-per-node N tools/multigpu_check.py [level] [steps] [graph]"""
+import os, sys
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+import numpy as np
+import torch
+import torch.distributed as dist
+import common
+
+def main():
+    level = int(sys.argv[1]) if len(sys.argv) > 1 else 5
+    steps = int(sys.argv[2]) if len(sys.argv) > 2 else 4
+    graph = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+    rank, lrank, world = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"]), int(os.environ["WORLD_SIZE"])
+    torch.cuda.set_device(lrank)
+    dist.init_process_group("nccl", device_id=torch.device("cuda", lrank))
+    host = common.host
+    L, ns = 26, 3
+    case = host.HostCase(level, lloyd_iters=5, sfc=True)
+    case.partition(world, "metis")
+    blk = case.build_block(rank, nVertLevels=L, init_case=2, num_scalars=ns, full_fields=True)
+    s = blk.field("scalars@1"); lat = blk.field("latCell")
+    s[:-1, :, 1] = (np.sin(2 * lat) ** 2)[:-1, None]; s[:-1, :, 2] = 1.0
+    cfg = common.level_config(level)
+    dy = host.Dycore([blk], cfg, rank=rank, nranks=world, device=lrank)
+    obj = [host.nccl_unique_id() if rank == 0 else None]
+    dist.broadcast_object_list(obj, src=0)
+    dy.comm_init(obj[0])
+    dy.set_option("graph", graph)
+    dy.init(); dy.step(steps)
+    # reference: the whole mesh as one block on this rank's GPU
+    case1 = host.HostCase(level, lloyd_iters=5, sfc=True)
+    b1 = case1.build_block(0, nVertLevels=L, init_case=2, num_scalars=ns, full_fields=True)
+    s1 = b1.field("scalars@1"); lat1 = b1.field("latCell")
+    s1[:-1, :, 1] = (np.sin(2 * lat1) ** 2)[:-1, None]; s1[:-1, :, 2] = 1.0
+    d1 = host.Dycore([b1], cfg, device=lrank)
+    d1.init(); d1.step(steps)
+    ok = True
+    nown = int(blk.cfg()["nCellsSolve"]); ids = blk.field("indexToCellID")[:nown]
+    for n in ("theta_m@1", "rho_zz@1", "w@1", "scalars@1"):
+        a = dy.field(0, n)[:nown]; b = d1.field(0, n)[ids - 1]
+        same = np.array_equal(a, b)
+        ok &= same
+        if not same: print("rank", rank, n, "max diff", np.abs(a - b).max(), flush=True)
+    nE = int(blk.cfg()["nEdgesSolve"]); eids = blk.field("indexToEdgeID")[:nE]
+    e1 = b1.field("indexToEdgeID")[:-1]; inv = np.empty(len(e1), dtype=np.int64); inv[e1 - 1] = np.arange(len(e1))
+    same = np.array_equal(dy.field(0, "u@1")[:nE], d1.field(0, "u@1")[inv[eids - 1]])
+    ok &= same
+    t = torch.tensor([1 if ok else 0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
+    if rank == 0:
+        print("MULTIGPU_CHECK world=%d level=%d steps=%d graph=%d exchanges/step=%.0f -> %s" % (world, level, steps, graph, dy.exchange_count() / steps, "BITWISE EQUAL" if t.item() == 1 else "MISMATCH"), flush=True)
+    dy.close(); d1.close()
+    dist.destroy_process_group()
+    sys.exit(0 if t.item() == 1 else 1)
+
+main()
