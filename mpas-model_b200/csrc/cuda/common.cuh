@@ -31,11 +31,32 @@ namespace mpasb200 {
 // Fortran sign(a,b): |a| with the sign bit of b (so sign(1,+0)=+1, sign(1,-0)=-1)
 __device__ __forceinline__ real fsign(real a, real b) { return copysign(a, b); }
 
+// x / 12 without the generic division sequence: with r = RN(1/12), q0 = RN(x r), rem = x - 12 q0 (exact in one fma),
+// RN(q0 + rem r) is the correctly rounded quotient (Markstein's correction step; for the divisor 3 * 2^2 the exact
+// quotient is never closer than 1/6 ulp to a rounding tie, so the O(2^-53 ulp) error of the correction cannot change
+// the rounding).  Outside [1e-290, 1e290] (underflow / overflow of the intermediates, zeros, NaN) the plain division
+// is used, so the result equals x / 12.0 bit for bit for every input.  3 instructions instead of ~12.
+__device__ __forceinline__ real div12(real x) {
+#ifdef SINGLE_PRECISION
+    return x / (real)12.0;
+#else
+    const double ax = fabs(x);
+    if (!(ax >= 1e-290 && ax <= 1e290)) {
+        if (ax == 0.0) return x;
+        return x / 12.0;
+    }
+    const double r = 1.0 / 12.0;
+    const double q0 = x * r;
+    const double rem = __fma_rn(-q0, 12.0, x);
+    return __fma_rn(rem, r, q0);
+#endif
+}
+
 __device__ __forceinline__ real flux4(real q_im2, real q_im1, real q_i, real q_ip1, real ua) {  // TI:4655
-    return ua * ((real)7. * (q_i + q_im1) - (q_ip1 + q_im2)) / (real)12.0;
+    return div12(ua * ((real)7. * (q_i + q_im1) - (q_ip1 + q_im2)));
 }
 __device__ __forceinline__ real flux3(real q_im2, real q_im1, real q_i, real q_ip1, real ua, real coef3) {  // TI:4658
-    return flux4(q_im2, q_im1, q_i, q_ip1, ua) + coef3 * fabs(ua) * ((q_ip1 - q_im2) - (real)3. * (q_i - q_im1)) / (real)12.0;
+    return flux4(q_im2, q_im1, q_i, q_ip1, ua) + div12(coef3 * fabs(ua) * ((q_ip1 - q_im2) - (real)3. * (q_i - q_im1)));
 }
 
 // exner = x ** rcv with rcv = rgas/(cp-rgas) (TI:3027, 5980).  The reference's gfortran build calls libm pow, which
@@ -69,6 +90,96 @@ __device__ __forceinline__ real pow_rcv(real x, real rcv) {
 #endif
 }
 
+// Software prefetch of one column (nlev consecutive reals starting at col) into L2 / L1, issued by a whole warp:
+// mode 1 = one prefetch.global.L2 per 128-byte line (lanes 0..), 2 = one bulk L2 prefetch by lane 0 (16-byte aligned
+// window around the column), 3 = prefetch.global.L1 per line.  Fire-and-forget: no register, no scoreboard.
+__device__ __forceinline__ void prefetch_col(const real* col, int nlev, int lane, int mode) {
+    if (mode == 2) {
+        if (lane == 0) {
+            const uintptr_t a = (uintptr_t)col, a0 = a & ~(uintptr_t)15;
+            const unsigned bytes = (unsigned)(((a + (size_t)nlev * sizeof(real) + 15) & ~(uintptr_t)15) - a0);
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"((const void*)a0), "r"(bytes) : "memory");
+        }
+    } else {
+        const int per_line = 128 / (int)sizeof(real);
+        if (lane * per_line < nlev + per_line - 1) {
+            const real* q = col + min(lane * per_line, nlev - 1);
+            if (mode == 3) asm volatile("prefetch.global.L1 [%0];" ::"l"(q));
+            else asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+        }
+    }
+}
+
+// Asynchronous staging of whole columns into shared memory (LDGSTS): every lane copies its levels of the column without
+// holding a register or a scoreboard, so a warp can have all the columns of its mesh element in flight at once and pays
+// ONE memory latency per element instead of one per loop nest.  Columns are only sizeof(real)-aligned (odd nVertLevels),
+// hence element-sized copies.
+__device__ __forceinline__ void cp_async_real(real* smem_dst, const real* gsrc) {
+    const unsigned s = (unsigned)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(s), "l"(gsrc), "n"(sizeof(real)) : "memory");
+}
+__device__ __forceinline__ void stage_col(real* smem_dst, const real* gcol, int n, int lane) {
+    for (int k = lane; k < n; k += 32) cp_async_real(smem_dst + k, gcol + k);
+}
+// same in straight-line form for the hot kernels: sdst_lane = shared-window address of element `lane` of the destination
+// column, gsrc_lane = &column[lane]; two predicated copies cover n <= 64 levels, a loop the rest.
+__device__ __forceinline__ void cp_async_s(unsigned sdst, const real* g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], %2;" ::"r"(sdst), "l"(g), "n"(sizeof(real)) : "memory");
+}
+__device__ __forceinline__ void stage_col_s(unsigned sdst_lane, const real* gsrc_lane, int n, int lane) {
+    if (lane < n) cp_async_s(sdst_lane, gsrc_lane);
+    if (lane + 32 < n) cp_async_s(sdst_lane + 32 * (unsigned)sizeof(real), gsrc_lane + 32);
+    if (n > 64)
+        for (int d = 64; lane + d < n; d += 32) cp_async_s(sdst_lane + d * (unsigned)sizeof(real), gsrc_lane + d);
+}
+__device__ __forceinline__ void stage_wait() {
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncwarp();
+}
+
+// ---- TMA column staging -------------------------------------------------------------------------------------------
+// One cp.async.bulk (UBLKCP) per column, issued by lane 0 of the warp that owns the mesh element, completing on a
+// per-warp mbarrier: the copy engine moves the column straight into shared memory, so staging costs the LSU / L1 data
+// path nothing and the warp one instruction per column.  Bulk copies need 16-byte aligned addresses and sizes while a
+// column is only sizeof(real)-aligned (odd nVertLevels): the copy covers the 16-byte aligned window around the column
+// (at most 8 bytes before and 15 after it, inside the array or the allocation granule) and the column's first element
+// lands at element `shift` = (address & 15) / sizeof(real) of its slot.  A slot is tma_slot(n) reals (multiple of 16 B).
+__host__ __device__ inline int tma_slot(int n) { return (int)((((size_t)n * sizeof(real) + 16 + 15) & ~(size_t)15) / sizeof(real)); }
+__device__ __forceinline__ void mbar_init(unsigned mbar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(mbar), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned mbar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(mbar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile(
+            "{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}"
+            : "=r"(ok)
+            : "r"(mbar), "r"(parity)
+            : "memory");
+    } while (!ok);
+}
+// Element shift of a column inside its slot (every lane), and the copy itself (issuing lane only; adds its size to total).
+__device__ __forceinline__ int tma_shift(const real* gcol) { return (int)(((unsigned)(unsigned long long)gcol & 15u) / (unsigned)sizeof(real)); }
+__device__ __forceinline__ void tma_issue_col(unsigned sslot, const real* gcol, int n, unsigned mbar, unsigned& total) {
+    const unsigned long long a = (unsigned long long)gcol;
+    const unsigned sh = (unsigned)a & 15u;
+    const unsigned bytes = (sh + (unsigned)n * (unsigned)sizeof(real) + 15u) & ~15u;
+    asm volatile("cp.async.bulk.shared::cta.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(sslot), "l"(a - sh), "r"(bytes), "r"(mbar)
+                 : "memory");
+    total += bytes;
+}
+// &base[off32] in one IMAD.WIDE.U32 (the compiler otherwise spends four instructions on the 64-bit shift-and-add)
+__device__ __forceinline__ const real* elem_ptr(const real* base, unsigned off) {
+    unsigned long long r;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(r) : "r"(off), "n"(sizeof(real)), "l"((unsigned long long)base));
+    return (const real*)r;
+}
+
 // ---- library state ---------------------------------------------------------------------------
 cudaStream_t stream();                 // stream every kernel of the library is launched on
 void set_stream(cudaStream_t s);
@@ -89,6 +200,12 @@ template <class T>
 inline T* X(T* p) { return (T*)xlate((const void*)p); }
 template <class T>
 inline const T* X(const T* p) { return (const T*)xlate((const void*)p); }
+
+// opt a kernel in to more than 48 KB of dynamic shared memory (cached per kernel); false if it cannot be granted
+bool ensure_dyn_smem(const void* kernel, size_t bytes);
+
+// developer knob: integer read from the environment variable MPAS_B200_TUNE_<name> (kernel-variant sweeps in one bench run)
+int tune(const char* name, int def);
 
 inline int cdiv(long long a, int b) { return (int)((a + b - 1) / b); }
 
@@ -122,6 +239,8 @@ void ktime_end();
     const int ent = (first) + _ent0
 #define WLAUNCH(kernel, count, shmem, ...)                                                              \
     do {                                                                                                \
+        if ((count) > 0 && !mpasb200::ensure_dyn_smem((const void*)kernel, (shmem)))                    \
+            return mpasb200::fail_msg(std::string(#kernel) + ": nVertLevels too large for the shared-memory staging"); \
         if ((count) > 0) {                                                                              \
             mpasb200::ktime_begin(#kernel);                                                             \
             kernel<<<mpasb200::cdiv((count), WPB), WPB * 32, (shmem), mpasb200::stream()>>>(__VA_ARGS__); \

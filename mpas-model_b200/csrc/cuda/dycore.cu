@@ -118,7 +118,7 @@ int add_field(DBlock& blk, const std::string& name, const void* host, int kind, 
     df.inner = 1;
     for (size_t k = 0; k + 1 < dims.size(); ++k) df.inner *= (int)dims[k];
     df.bytes = n * (kind == 0 ? sizeof(real) : sizeof(int));
-    cudaError_t e = cudaMalloc(&df.dev, df.bytes ? df.bytes : 8);
+    cudaError_t e = cudaMalloc(&df.dev, df.bytes + 64);  // +64: bulk column copies read a 16-byte aligned window around a column
     if (e != cudaSuccess) return fail(("cudaMalloc " + name).c_str(), e);
     if (host) {
         if (kind == 0 && sizeof(real) != sizeof(double)) {

@@ -33,7 +33,7 @@ struct DtP {
     int L, mE, mE2, vD, rk_step, nCellsSolve;
     int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, edgeSolveStart, edgeSolveEnd, nEdgesSolveLoop;
     int vertexStart, nVerticesLoop;
-    int mixing, mix_full, rayleigh_damp_u, n_rayleigh_levels;
+    int mixing, mix_full, rayleigh_damp_u, n_rayleigh_levels, pf;
     real c_s, len_disp, invDt, cam_coef, h_theta_eddy_visc2_fixed, h_mom_eddy_visc4, h_theta_eddy_visc4, del4u_div_factor;
     real v_mom_eddy_visc2, v_theta_eddy_visc2, coef_3rd_order, rayleigh_coef_inverse, prandtl_inv;
     const real *fEdge, *dvEdge, *dcEdge, *invDcEdge, *invDvEdge, *invAreaCell, *invAreaTriangle, *meshScalingDel2, *meshScalingDel4;
@@ -230,86 +230,195 @@ __global__ void __launch_bounds__(WPB * 32) dt_edge_flux_kernel(DtP p, real* __r
     }
 }
 
-__device__ __forceinline__ real wduz_at(const DtP& p, int kk, int iEdge, int cell1, int cell2) {
+// vertical mixing of u (TI:4949-5006), off by default: kept out of line so that it costs the common path no registers
+__device__ __noinline__ real u_vmix_term(const DtP& p, int k, int iEdge, int cell1, int cell2, real rho_e) {
     const int L = p.L, L1 = L + 1;
-    if (kk == 1 || kk == L1) return (real)0.;
-    const real rwe = (real)0.5 * (p.rw[IX2(kk, cell1, L1)] + p.rw[IX2(kk, cell2, L1)]);
-    if (kk == 2 || kk == L) return rwe * (p.fzm[kk - 1] * p.u[IX2(kk, iEdge, L)] + p.fzp[kk - 1] * p.u[IX2(kk - 1, iEdge, L)]);
-    return flux3(p.u[IX2(kk - 2, iEdge, L)], p.u[IX2(kk - 1, iEdge, L)], p.u[IX2(kk, iEdge, L)], p.u[IX2(kk + 1, iEdge, L)], rwe, (real)1.0);
+    real um[3];
+    for (int d = -1; d <= 1; ++d) {
+        const int kk = k + d;
+        real x = p.u[IX2(kk, iEdge, L)];
+        if (!p.mix_full) x = x - p.u_init[kk - 1] * cos(p.angleEdge[iEdge - 1]) - p.v_init[kk - 1] * sin(p.angleEdge[iEdge - 1]);
+        um[d + 1] = x;
+    }
+    const real z1 = (real)0.5 * (p.zgrid[IX2(k - 1, cell1, L1)] + p.zgrid[IX2(k - 1, cell2, L1)]);
+    const real z2 = (real)0.5 * (p.zgrid[IX2(k, cell1, L1)] + p.zgrid[IX2(k, cell2, L1)]);
+    const real z3 = (real)0.5 * (p.zgrid[IX2(k + 1, cell1, L1)] + p.zgrid[IX2(k + 1, cell2, L1)]);
+    const real z4 = (real)0.5 * (p.zgrid[IX2(k + 2, cell1, L1)] + p.zgrid[IX2(k + 2, cell2, L1)]);
+    const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
+    return rho_e * p.v_mom_eddy_visc2 * ((um[2] - um[1]) / (zp - z0) - (um[1] - um[0]) / (z0 - zm)) / ((real)0.5 * (zp - zm));
 }
 
-// dynamic shared memory: WPB * (L + 2) reals (vertical flux column of each warp)
-__global__ void __launch_bounds__(WPB * 32) dt_edge_kernel(DtP p) {
-    extern __shared__ real s_dyn[];
-    __shared__ int s_eoe[WPB][16];
-    __shared__ real s_wt[WPB][16];
-    const int L = p.L, L1 = L + 1, mE2 = p.mE2;
+// Shared-memory column slots of one warp of dt_edge_kernel (tma_slot(L + 1) reals each), filled by tma_stage_col.
+enum { EC_RW1, EC_RW2, EC_U, EC_PV, EC_RHO, EC_TE, EC_KE1, EC_KE2, EC_HD1, EC_HD2, EC_WZ, EC_NCOL_RK23, EC_DD1 = EC_NCOL_RK23, EC_DD2, EC_DV1, EC_DV2, EC_NCOL_RK1 };
+
+// One owned edge per warp.  Every column the edge reads exactly once per level (its own u, pv_edge, rho_edge,
+// tend_u_euler; rw, ke, h_divergence [, delsq_divergence] of its two cells [, delsq_vorticity of its two vertices]) is
+// staged into shared memory by one bulk (TMA) copy per column, all issued back to back by lane 0, so the warp waits for
+// memory once and the L1 data path carries only the gathers; the vertical stencils of u then read shared memory.
+// The edgesOnEdge gather (TI:4811-4820) stays a direct gather: each lane owns levels (lane, lane + 32) of a 64-level
+// chunk so one address serves two loads, the neighbour list holds element offsets and is padded with zero-weight self
+// references to a multiple of UNR (q + 0*x == q exactly, q is never -0), and the unrolled body issues 4*UNR
+// independent loads before the first dependent add.
+// dynamic shared memory: WPB * ncol * tma_slot(L + 1) reals.
+template <int UNR, bool RK1, bool VMIX>
+__global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) {
+    extern __shared__ __align__(16) real s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar[WPB];
+    __shared__ unsigned s_off[WPB][20];
+    __shared__ real s_wt[WPB][20];
+    const int L = p.L, L1 = L + 1, mE2 = p.mE2, LS = tma_slot(L1);
     WARP_ENTITY(p.edgeSolveStart, p.nEdgesSolveLoop);
     const int iEdge = ent;
-    real* wz = s_dyn + (size_t)warp * (L + 2);
+    real* sc = s_dyn + (size_t)warp * (RK1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * LS;
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+    if (lane == 0) mbar_init(mbar, 1);
     const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
-    const int neoe = p.nEdgesOnEdge[iEdge - 1];
-    if (lane < neoe) {
-        s_eoe[warp][lane] = p.edgesOnEdge[IX2(lane + 1, iEdge, mE2)];
-        s_wt[warp][lane] = p.weightsOnEdge[IX2(lane + 1, iEdge, mE2)];
-    }
-    for (int k = lane + 1; k <= L1; k += 32) wz[k] = wduz_at(p, k, iEdge, cell1, cell2);
-    __syncwarp();
-    const real idc = p.invDcEdge[iEdge - 1];
-    const bool del4 = (p.rk_step == 1 && p.h_mom_eddy_visc4 > (real)0.0);
+    const bool del4 = (RK1 && p.h_mom_eddy_visc4 > (real)0.0);
     int vertex1 = 0, vertex2 = 0;
-    real r_dc = 0, r_dv = 0;
-    if (del4) {  // TI:4924-4944
+    if (del4) {
         vertex1 = p.verticesOnEdge[IX2(1, iEdge, 2)];
         vertex2 = p.verticesOnEdge[IX2(2, iEdge, 2)];
+    }
+    const int neoe = p.nEdgesOnEdge[iEdge - 1];
+    const unsigned eoff = (unsigned)(iEdge - 1) * (unsigned)L;
+    const size_t c1off = (size_t)(cell1 - 1) * L, c2off = (size_t)(cell2 - 1) * L;
+    const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
+    const real* g_u = p.u + eoff;
+    const real* g_rw1 = p.rw + (c1off + (cell1 - 1));
+    const real* g_rw2 = p.rw + (c2off + (cell2 - 1));
+    const real* g_pv = p.pv_edge + eoff;
+    const real* g_rho = p.rho_edge + eoff;
+    const real* g_te = p.tend_u_euler + eoff;
+    const real* g_ke1 = p.ke + c1off;
+    const real* g_ke2 = p.ke + c2off;
+    const real* g_hd1 = p.h_divergence + c1off;
+    const real* g_hd2 = p.h_divergence + c2off;
+    const real *g_dd1 = nullptr, *g_dd2 = nullptr, *g_dv1 = nullptr, *g_dv2 = nullptr;
+    if (del4) {
+        g_dd1 = p.delsq_divergence + c1off;
+        g_dd2 = p.delsq_divergence + c2off;
+        g_dv1 = p.delsq_vorticity + (size_t)(vertex1 - 1) * L;
+        g_dv2 = p.delsq_vorticity + (size_t)(vertex2 - 1) * L;
+    }
+    if (lane == 0) {  // one bulk copy per column, all in flight together
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
+        unsigned total = 0;
+        tma_issue_col(s0 + EC_U * cs, g_u, L, mbar, total);
+        tma_issue_col(s0 + EC_RW1 * cs, g_rw1, L1, mbar, total);
+        tma_issue_col(s0 + EC_RW2 * cs, g_rw2, L1, mbar, total);
+        tma_issue_col(s0 + EC_PV * cs, g_pv, L, mbar, total);
+        tma_issue_col(s0 + EC_RHO * cs, g_rho, L, mbar, total);
+        tma_issue_col(s0 + EC_TE * cs, g_te, L, mbar, total);
+        tma_issue_col(s0 + EC_KE1 * cs, g_ke1, L, mbar, total);
+        tma_issue_col(s0 + EC_KE2 * cs, g_ke2, L, mbar, total);
+        tma_issue_col(s0 + EC_HD1 * cs, g_hd1, L, mbar, total);
+        tma_issue_col(s0 + EC_HD2 * cs, g_hd2, L, mbar, total);
+        if (del4) {
+            tma_issue_col(s0 + EC_DD1 * cs, g_dd1, L, mbar, total);
+            tma_issue_col(s0 + EC_DD2 * cs, g_dd2, L, mbar, total);
+            tma_issue_col(s0 + EC_DV1 * cs, g_dv1, L, mbar, total);
+            tma_issue_col(s0 + EC_DV2 * cs, g_dv2, L, mbar, total);
+        }
+        mbar_arrive_expect_tx(mbar, total);
+    }
+    // x_<col>: index of level 1 of the column inside sc[]
+    const int x_u = EC_U * LS + tma_shift(g_u), x_rw1 = EC_RW1 * LS + tma_shift(g_rw1), x_rw2 = EC_RW2 * LS + tma_shift(g_rw2);
+    const int x_pv = EC_PV * LS + tma_shift(g_pv), x_rho = EC_RHO * LS + tma_shift(g_rho), x_te = EC_TE * LS + tma_shift(g_te);
+    const int x_ke1 = EC_KE1 * LS + tma_shift(g_ke1), x_ke2 = EC_KE2 * LS + tma_shift(g_ke2);
+    const int x_hd1 = EC_HD1 * LS + tma_shift(g_hd1), x_hd2 = EC_HD2 * LS + tma_shift(g_hd2);
+    const int x_dd1 = EC_DD1 * LS + tma_shift(g_dd1), x_dd2 = EC_DD2 * LS + tma_shift(g_dd2);
+    const int x_dv1 = EC_DV1 * LS + tma_shift(g_dv1), x_dv2 = EC_DV2 * LS + tma_shift(g_dv2);
+    const int npad = (neoe + UNR - 1) / UNR * UNR;
+    if (lane < npad) {
+        const bool real_nb = lane < neoe;
+        s_off[warp][lane] = real_nb ? (unsigned)(p.edgesOnEdge[IX2(lane + 1, iEdge, mE2)] - 1) * (unsigned)L : eoff;
+        s_wt[warp][lane] = real_nb ? p.weightsOnEdge[IX2(lane + 1, iEdge, mE2)] : (real)0.0;
+    }
+    const real idc = p.invDcEdge[iEdge - 1];
+    real r_dc = 0, r_dv = 0;
+    if (del4) {  // TI:4924-4944
         const real u_mix_scale = p.meshScalingDel4[iEdge - 1] * p.h_mom_eddy_visc4;
         r_dc = u_mix_scale * p.del4u_div_factor * idc;
         r_dv = u_mix_scale * fmin(p.invDvEdge[iEdge - 1], 4 * idc);
     }
-    for (int k = lane + 1; k <= L; k += 32) {
-        const size_t ie = IX2(k, iEdge, L), i1 = IX2(k, cell1, L), i2 = IX2(k, cell2, L);
-        real tu = -p.rdzw[k - 1] * (wz[k + 1] - wz[k]);
-        real q = 0.0;
-        const real pv_e = p.pv_edge[ie];
-        for (int j = 0; j < neoe; ++j) {
-            const size_t io = IX2(k, s_eoe[warp][j], L);
-            const real workpv = (real)0.5 * (pv_e + p.pv_edge[io]);
-            q = q + s_wt[warp][j] * p.u[io] * workpv;
-        }
-        const real ue = p.u[ie], rho_e = p.rho_edge[ie];
-        tu = tu + rho_e * (q - (p.ke[i2] - p.ke[i1]) * idc) - ue * (real)0.5 * (p.h_divergence[i1] + p.h_divergence[i2]);
-        real te = p.tend_u_euler[ie];
-        if (p.rk_step == 1) {
-            bool changed = false;
-            if (del4) {
-                const real u_diffusion = rho_e * ((p.delsq_divergence[i2] - p.delsq_divergence[i1]) * r_dc -
-                                                  (p.delsq_vorticity[IX2(k, vertex2, L)] - p.delsq_vorticity[IX2(k, vertex1, L)]) * r_dv);
-                te = te - u_diffusion;
-                changed = true;
+    __syncwarp();
+    mbar_wait(mbar, 0);
+    const real* su = sc + x_u - 1;  // 1-based views: su[k] = u(k, iEdge)
+    const real* srw1 = sc + x_rw1 - 1;
+    const real* srw2 = sc + x_rw2 - 1;
+    real* wz = sc + EC_WZ * LS - 1;
+    for (int kk = lane + 1; kk <= L1; kk += 32) {  // vertical flux of u at the interfaces, TI:4792-4804
+        // branch-free: every lane evaluates both the 3rd-order flux (stencil indices clamped into the column) and the
+        // 2nd-order boundary form, then selects; a divergent if/else would make the warp execute both anyway
+        const int km2 = max(kk - 2, 1), km1 = max(kk - 1, 1), kc = min(kk, L), kp1 = min(kk + 1, L);
+        const real rwe = (real)0.5 * (srw1[kk] + srw2[kk]);
+        const real u_m2 = su[km2], u_m1 = su[km1], u_c = su[kc], u_p1 = su[kp1];
+        const real f3 = flux3(u_m2, u_m1, u_c, u_p1, rwe, (real)1.0);
+        const real f2 = rwe * (p.fzm[kc - 1] * u_c + p.fzp[kc - 1] * u_m1);
+        real f = (kk == 2 || kk == L) ? f2 : f3;
+        if (kk == 1 || kk == L1) f = 0.;
+        wz[kk] = f;
+    }
+    __syncwarp();
+    for (int ka = lane; ka < L; ka += 64) {  // 0-based levels ka and ka + 32
+        const bool vb = ka + 32 < L;
+        const int bo = vb ? 32 : 0;  // lanes without a second level recompute the first one (no predicated loads)
+        const real* __restrict__ pvp = p.pv_edge + ka;
+        const real* __restrict__ up = p.u + ka;
+        const real pv_a = sc[x_pv + ka], pv_b = sc[x_pv + ka + bo];
+        // q = sum_j w_j u_j (0.5 (pv + pv_j)): the factor 0.5 is a power of two, so it commutes with every rounding
+        // of the sum and is applied once at the end (identical bits unless an intermediate underflows).
+        real q_a = 0.0, q_b = 0.0;
+        for (int j = 0; j < npad; j += UNR) {  // TI:4811-4820
+            real pa[UNR], ua[UNR], pb[UNR], ub[UNR], wt[UNR];
+#pragma unroll
+            for (int t = 0; t < UNR; ++t) {
+                const unsigned o = s_off[warp][j + t];
+                const real* __restrict__ pj = elem_ptr(pvp, o);
+                const real* __restrict__ uj = elem_ptr(up, o);
+                wt[t] = s_wt[warp][j + t];
+                pa[t] = pj[0];
+                ua[t] = uj[0];
+                pb[t] = pj[bo];
+                ub[t] = uj[bo];
             }
-            if (p.v_mom_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:4949-5006
-                real um[3];
-                for (int d = -1; d <= 1; ++d) {
-                    const int kk = k + d;
-                    real x = p.u[IX2(kk, iEdge, L)];
-                    if (!p.mix_full) x = x - p.u_init[kk - 1] * cos(p.angleEdge[iEdge - 1]) - p.v_init[kk - 1] * sin(p.angleEdge[iEdge - 1]);
-                    um[d + 1] = x;
+#pragma unroll
+            for (int t = 0; t < UNR; ++t) {
+                q_a = q_a + wt[t] * ua[t] * (pv_a + pa[t]);
+                q_b = q_b + wt[t] * ub[t] * (pv_b + pb[t]);
+            }
+        }
+        q_a = (real)0.5 * q_a;
+        q_b = (real)0.5 * q_b;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const int k0 = ka + 32 * h, k = k0 + 1;  // k0: 0-based level
+            const real q = h ? q_b : q_a;
+            const size_t ie = (size_t)eoff + k0;
+            real tu = -p.rdzw[k0] * (wz[k + 1] - wz[k]);
+            const real ue = sc[x_u + k0], rho_e = sc[x_rho + k0];
+            tu = tu + rho_e * (q - (sc[x_ke2 + k0] - sc[x_ke1 + k0]) * idc) - ue * (real)0.5 * (sc[x_hd1 + k0] + sc[x_hd2 + k0]);
+            real te = sc[x_te + k0];
+            if (RK1) {
+                bool changed = false;
+                if (del4) {
+                    const real u_diffusion = rho_e * ((sc[x_dd2 + k0] - sc[x_dd1 + k0]) * r_dc - (sc[x_dv2 + k0] - sc[x_dv1 + k0]) * r_dv);
+                    te = te - u_diffusion;
+                    changed = true;
                 }
-                const real z1 = (real)0.5 * (p.zgrid[IX2(k - 1, cell1, L1)] + p.zgrid[IX2(k - 1, cell2, L1)]);
-                const real z2 = (real)0.5 * (p.zgrid[IX2(k, cell1, L1)] + p.zgrid[IX2(k, cell2, L1)]);
-                const real z3 = (real)0.5 * (p.zgrid[IX2(k + 1, cell1, L1)] + p.zgrid[IX2(k + 1, cell2, L1)]);
-                const real z4 = (real)0.5 * (p.zgrid[IX2(k + 2, cell1, L1)] + p.zgrid[IX2(k + 2, cell2, L1)]);
-                const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
-                te = te + rho_e * p.v_mom_eddy_visc2 * ((um[2] - um[1]) / (zp - z0) - (um[1] - um[0]) / (z0 - zm)) / ((real)0.5 * (zp - zm));
-                changed = true;
+                if (VMIX && k >= 2 && k <= L - 1) {  // TI:4949-5006
+                    te = te + u_vmix_term(p, k, iEdge, cell1, cell2, rho_e);
+                    changed = true;
+                }
+                if (changed) p.tend_u_euler[ie] = te;
             }
-            if (changed) p.tend_u_euler[ie] = te;
+            if (p.rayleigh_damp_u && k >= L - p.n_rayleigh_levels + 1) {  // TI:5015-5028
+                const real coef = (real)(k - (L - p.n_rayleigh_levels)) * p.rayleigh_coef_inverse;
+                tu = tu - rho_e * ue * coef;
+            }
+            p.tend_u[ie] = tu + te + (p.tend_ru_physics ? p.tend_ru_physics[ie] : (real)0.0);
         }
-        if (p.rayleigh_damp_u && k >= L - p.n_rayleigh_levels + 1) {  // TI:5015-5028
-            const real coef = (real)(k - (L - p.n_rayleigh_levels)) * p.rayleigh_coef_inverse;
-            tu = tu - rho_e * ue * coef;
-        }
-        p.tend_u[ie] = tu + te + (p.tend_ru_physics ? p.tend_ru_physics[ie] : (real)0.0);
     }
 }
 
@@ -437,6 +546,8 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
     p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.edgeSolveStart = edgeSolveStart; p.edgeSolveEnd = edgeSolveEnd;
     p.nEdgesSolveLoop = edgeSolveEnd - edgeSolveStart + 1; p.vertexStart = vertexStart; p.nVerticesLoop = vertexEnd - vertexStart + 1;
+    static const int pf_mode = tune("dt_pf", 0);
+    p.pf = pf_mode;
     p.mixing = config_horiz_mixing; p.mix_full = config_mix_full; p.rayleigh_damp_u = config_rayleigh_damp_u;
     p.n_rayleigh_levels = config_number_rayleigh_damp_u_levels;
     p.c_s = c_s; p.len_disp = config_len_disp; p.invDt = (real)1.0 / dt; p.cam_coef = config_mpas_cam_coef;
@@ -497,8 +608,13 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     if (!ft || !fw || !ft2) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace");
     WLAUNCH(dt_edge_flux_kernel, p.nEdgesLoop, 0, p, ft, fw, ft2);
     KCHECK("dt_edge_flux_kernel");
-    WLAUNCH(dt_edge_kernel, p.nEdgesSolveLoop, (size_t)WPB * (L + 2) * sizeof(real), p);
-    KCHECK("dt_edge_kernel");
+    {
+        const size_t shm = (size_t)WPB * (rk_step == 1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * tma_slot(L + 1) * sizeof(real);
+        if (rk_step != 1) WLAUNCH((dt_edge_kernel<5, false, false>), p.nEdgesSolveLoop, shm, p);
+        else if (p.v_mom_eddy_visc2 > (real)0.0) WLAUNCH((dt_edge_kernel<5, true, true>), p.nEdgesSolveLoop, shm, p);
+        else WLAUNCH((dt_edge_kernel<5, true, false>), p.nEdgesSolveLoop, shm, p);
+        KCHECK("dt_edge_kernel");
+    }
     WLAUNCH(dt_cell_kernel, p.nCellsSolveLoop, (size_t)WPB * 2 * (L + 2) * sizeof(real), p, ft, fw, ft2);
     KCHECK("dt_cell_kernel");
     return 0;

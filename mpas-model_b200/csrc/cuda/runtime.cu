@@ -13,6 +13,8 @@
 
 #include "common.cuh"
 
+#include <cstdlib>
+
 namespace mpas {
 extern std::string g_last_error;  // host_api.cpp
 }
@@ -68,7 +70,7 @@ real* workspace(int slot, size_t count) {
             cudaStreamSynchronize(stream());
             cudaFree(w.p);
         }
-        if (cudaMalloc(&w.p, count * sizeof(real)) != cudaSuccess) {
+        if (cudaMalloc(&w.p, count * sizeof(real) + 64) != cudaSuccess) {
             w.p = nullptr;
             w.count = 0;
             return nullptr;
@@ -110,6 +112,26 @@ void kflush() {
     g_krecs.clear();
 }
 }  // namespace
+bool ensure_dyn_smem(const void* kernel, size_t bytes) {
+    if (bytes <= 48 * 1024) return true;
+    if (bytes > 227 * 1024) return false;
+    static std::map<const void*, size_t> have;
+    auto it = have.find(kernel);
+    if (it != have.end() && it->second >= bytes) return true;
+    if (cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    have[kernel] = bytes;
+    return true;
+}
+
+int tune(const char* name, int def) {
+    std::string key = std::string("MPAS_B200_TUNE_") + name;
+    const char* v = getenv(key.c_str());
+    return v ? atoi(v) : def;
+}
+
 void ktime_begin(const char* name) {
     if (!g_ktime) return;
     cudaStreamCaptureStatus st;
@@ -169,7 +191,7 @@ int mpas_b200_register_field(const void* host, size_t bytes) {
     }
     Mirror m;
     m.bytes = bytes;
-    cudaError_t e = cudaMalloc(&m.dev, bytes ? bytes : 8);
+    cudaError_t e = cudaMalloc(&m.dev, bytes + 64);  // +64: bulk column copies read a 16-byte aligned window around a column
     if (e != cudaSuccess) return fail("mpas_b200_register_field", e);
     g_reg[a] = m;
     return 0;
@@ -243,7 +265,10 @@ int mpas_b200_ktime_report(char* buf, int cap) {
     std::string out;
     for (auto& kv : g_ktot) {
         char line[256];
-        snprintf(line, sizeof(line), "%s %.6f %ld\n", kv.first.c_str(), kv.second.first, kv.second.second);
+        std::string nm;  // "(kernel<5, false>)" -> "kernel<5,false>": one token per line for the parser
+        for (char c : kv.first)
+            if (c != ' ' && c != '(' && c != ')') nm += c;
+        snprintf(line, sizeof(line), "%s %.6f %ld\n", nm.c_str(), kv.second.first, kv.second.second);
         out += line;
     }
     if ((int)out.size() + 1 > cap) return (int)out.size() + 1;
