@@ -193,40 +193,104 @@ __global__ void __launch_bounds__(256) dt_cell_mix_kernel(DtP p) {  // rk_step =
 //   ft2(k,e) = dvEdge * (ru_save - ru) * 0.5 * (theta_m_save(c2) + theta_m_save(c1))   (rk_step > 1, TI:5256-5269)
 // +- is Fortran sign(1, flux); a + (+-1)*b == a +- b bit for bit, and multiplying by edgesOnCell_sign = +-1 later is
 // exact, so the cell kernels reproduce the reference's sums exactly.
+// One edge per warp; each lane owns levels (lane, lane + 32) of a 64-level chunk so that one address computation
+// serves two gathers.  The stencil is staged once per warp as element offsets plus the two coefficient tables
+// (c + c3, c - c3), padded with zero coefficients to a multiple of FUNR (flux + 0*x == flux exactly, flux is never -0);
+// each lane selects its table by the sign of its own ru once per level.
+#define FUNR 5
+template <bool RK1>
 __global__ void __launch_bounds__(WPB * 32) dt_edge_flux_kernel(DtP p, real* __restrict__ ft, real* __restrict__ fw, real* __restrict__ ft2) {
-    __shared__ int s_cell[WPB][16];
-    __shared__ real s_cp[WPB][16], s_cm[WPB][16];
+    __shared__ unsigned s_ot[WPB][20], s_ow[WPB][20];
+    __shared__ real s_cp[WPB][20], s_cm[WPB][20];
     const int L = p.L, L1 = L + 1;
     WARP_ENTITY(p.edgeStart, p.nEdgesLoop);
     const int iEdge = ent;
     const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
     if (!(cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve)) return;
     const int n = p.nAdvCellsForEdge[iEdge - 1];
-    if (lane < n) {
-        s_cell[warp][lane] = p.advCellsForEdge[IX2(lane + 1, iEdge, 15)];
-        const real c = p.adv_coefs[IX2(lane + 1, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(lane + 1, iEdge, 15)];
-        s_cp[warp][lane] = c + c3;
-        s_cm[warp][lane] = c - c3;
+    const int npad = (n + FUNR - 1) / FUNR * FUNR;
+    if (lane < npad) {
+        const bool in = lane < n;
+        const int c = in ? p.advCellsForEdge[IX2(lane + 1, iEdge, 15)] : cell1;
+        const real a = in ? p.adv_coefs[IX2(lane + 1, iEdge, 15)] : (real)0.0, a3 = in ? p.adv_coefs_3rd[IX2(lane + 1, iEdge, 15)] : (real)0.0;
+        s_ot[warp][lane] = (unsigned)(c - 1) * (unsigned)L;
+        s_ow[warp][lane] = (unsigned)(c - 1) * (unsigned)L1;
+        s_cp[warp][lane] = a + a3;
+        s_cm[warp][lane] = a - a3;
     }
     __syncwarp();
     const real dv = p.dvEdge[iEdge - 1];
-    for (int k = lane + 1; k <= L; k += 32) {
-        const size_t ie = IX2(k, iEdge, L);
-        const real rue = p.ru[ie];
+    const unsigned eoff = (unsigned)(iEdge - 1) * (unsigned)L;
+    const unsigned c1off = (unsigned)(cell1 - 1) * (unsigned)L, c2off = (unsigned)(cell2 - 1) * (unsigned)L;
+    for (int ka = lane; ka < L; ka += 64) {  // 0-based levels ka and ka + 32
+        const bool vb = ka + 32 < L;
+        const int bo = vb ? 32 : 0;  // lanes without a second level recompute the first one
+        const real* __restrict__ rup = elem_ptr(p.ru + ka, eoff);
+        const real rue_a = rup[0], rue_b = rup[bo];
+        const int mo = ka > 0 ? -1 : 0;  // level below (k = 1 has no w flux; keeps the load in bounds)
+        const real rum_a = rup[mo], rum_b = rup[bo - 1 + (vb ? 0 : 1 + mo)];
+        real rs_a = 0, rs_b = 0, t1_a = 0, t1_b = 0, t2_a = 0, t2_b = 0;
+        if (!RK1) {  // operands of ft2, loaded ahead of the two gathers
+            const real* __restrict__ rs = elem_ptr(p.ru_save + ka, eoff);
+            const real* __restrict__ t1 = elem_ptr(p.theta_m_save + ka, c1off);
+            const real* __restrict__ t2 = elem_ptr(p.theta_m_save + ka, c2off);
+            rs_a = rs[0]; rs_b = rs[bo];
+            t1_a = t1[0]; t1_b = t1[bo];
+            t2_a = t2[0]; t2_b = t2[bo];
+        }
         {
-            const real* tab = signbit(rue) ? s_cm[warp] : s_cp[warp];
-            real flux = 0.0;
-            for (int j = 0; j < n; ++j) flux = flux + tab[j] * p.theta_m[IX2(k, s_cell[warp][j], L)];
-            ft[ie] = rue * flux;
+            const real* tab_a = signbit(rue_a) ? s_cm[warp] : s_cp[warp];
+            const real* tab_b = signbit(rue_b) ? s_cm[warp] : s_cp[warp];
+            const real* __restrict__ th = p.theta_m + ka;
+            real f_a = 0.0, f_b = 0.0;
+            for (int j = 0; j < npad; j += FUNR) {
+                real xa[FUNR], xb[FUNR];
+#pragma unroll
+                for (int t = 0; t < FUNR; ++t) {
+                    const real* __restrict__ q = elem_ptr(th, s_ot[warp][j + t]);
+                    xa[t] = q[0];
+                    xb[t] = q[bo];
+                }
+#pragma unroll
+                for (int t = 0; t < FUNR; ++t) {
+                    f_a = f_a + tab_a[j + t] * xa[t];
+                    f_b = f_b + tab_b[j + t] * xb[t];
+                }
+            }
+            real* o = ft + (size_t)eoff + ka;
+            o[0] = rue_a * f_a;
+            if (vb) o[32] = rue_b * f_b;
         }
-        if (k >= 2) {
-            const real ru_edge_w = p.fzm[k - 1] * rue + p.fzp[k - 1] * p.ru[ie - 1];
-            const real* tab = signbit(ru_edge_w) ? s_cm[warp] : s_cp[warp];
-            real flux = 0.0;
-            for (int j = 0; j < n; ++j) flux = flux + tab[j] * p.w[IX2(k, s_cell[warp][j], L1)];
-            fw[ie] = ru_edge_w * flux;
+        {
+            const real ruw_a = p.fzm[ka] * rue_a + p.fzp[ka] * rum_a;
+            const real ruw_b = p.fzm[ka + bo] * rue_b + p.fzp[ka + bo] * rum_b;
+            const real* tab_a = signbit(ruw_a) ? s_cm[warp] : s_cp[warp];
+            const real* tab_b = signbit(ruw_b) ? s_cm[warp] : s_cp[warp];
+            const real* __restrict__ wp = p.w + ka;
+            real f_a = 0.0, f_b = 0.0;
+            for (int j = 0; j < npad; j += FUNR) {
+                real xa[FUNR], xb[FUNR];
+#pragma unroll
+                for (int t = 0; t < FUNR; ++t) {
+                    const real* __restrict__ q = elem_ptr(wp, s_ow[warp][j + t]);
+                    xa[t] = q[0];
+                    xb[t] = q[bo];
+                }
+#pragma unroll
+                for (int t = 0; t < FUNR; ++t) {
+                    f_a = f_a + tab_a[j + t] * xa[t];
+                    f_b = f_b + tab_b[j + t] * xb[t];
+                }
+            }
+            real* o = fw + (size_t)eoff + ka;
+            if (ka > 0) o[0] = ruw_a * f_a;
+            if (vb) o[32] = ruw_b * f_b;
         }
-        if (p.rk_step > 1) ft2[ie] = dv * (p.ru_save[ie] - rue) * (real)0.5 * (p.theta_m_save[IX2(k, cell2, L)] + p.theta_m_save[IX2(k, cell1, L)]);
+        if (!RK1) {
+            real* o = ft2 + (size_t)eoff + ka;
+            o[0] = dv * (rs_a - rue_a) * (real)0.5 * (t2_a + t1_a);
+            if (vb) o[32] = dv * (rs_b - rue_b) * (real)0.5 * (t2_b + t1_b);
+        }
     }
 }
 
@@ -422,114 +486,238 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) 
     }
 }
 
-__device__ __forceinline__ real wdwz_at(const DtP& p, int kk, int iCell) {
-    const int L = p.L, L1 = L + 1;
-    if (kk == 1 || kk == L1) return (real)0.0;
-    const real rwk = p.rw[IX2(kk, iCell, L1)], rwkm = p.rw[IX2(kk - 1, iCell, L1)];
-    const real wk = p.w[IX2(kk, iCell, L1)], wkm = p.w[IX2(kk - 1, iCell, L1)];
-    if (kk == 2 || kk == L) return (real)0.25 * (rwk + rwkm) * (wk + wkm);
-    return flux3(p.w[IX2(kk - 2, iCell, L1)], wkm, wk, p.w[IX2(kk + 1, iCell, L1)], (real)0.5 * (rwk + rwkm), (real)1.0);
+// acc -= sum_t sg[t] * col_t(level), two levels per lane, all 2*NE loads issued before the first dependent subtract
+// (the sum keeps the list order; one memory round trip per call instead of one per edge)
+template <int NE>
+__device__ __forceinline__ void gather_sub(const real* __restrict__ base_ka, const unsigned* eo, const real* sg, int bo, real& acc_a, real& acc_b) {
+    real xa[NE], xb[NE];
+#pragma unroll
+    for (int t = 0; t < NE; ++t) {
+        const real* __restrict__ q = elem_ptr(base_ka, eo[t]);
+        xa[t] = q[0];
+        xb[t] = q[bo];
+    }
+#pragma unroll
+    for (int t = 0; t < NE; ++t) {
+        const real s = sg[t];
+        acc_a = acc_a - s * xa[t];
+        acc_b = acc_b - s * xb[t];
+    }
+}
+// acc -= sum_t coef[t] * (col2_t(level) - col1_t(level))
+template <int NE>
+__device__ __forceinline__ void gather_sub_diff(const real* __restrict__ base_ka, const unsigned* o2, const unsigned* o1, const real* coef, int bo, real& acc_a,
+                                                real& acc_b) {
+    real ya[NE], yb[NE], za[NE], zb[NE];
+#pragma unroll
+    for (int t = 0; t < NE; ++t) {
+        const real* __restrict__ q2 = elem_ptr(base_ka, o2[t]);
+        const real* __restrict__ q1 = elem_ptr(base_ka, o1[t]);
+        ya[t] = q2[0];
+        yb[t] = q2[bo];
+        za[t] = q1[0];
+        zb[t] = q1[bo];
+    }
+#pragma unroll
+    for (int t = 0; t < NE; ++t) {
+        const real e = coef[t];
+        acc_a = acc_a - e * (ya[t] - za[t]);
+        acc_b = acc_b - e * (yb[t] - zb[t]);
+    }
 }
 
-__device__ __forceinline__ real wdtz_at(const DtP& p, int kk, int iCell) {
-    const int L = p.L, L1 = L + 1;
-    if (kk == 1 || kk == L1) return (real)0.0;
-    const real fm = p.fzm[kk - 1], fp = p.fzp[kk - 1];
-    const real th_k = p.theta_m[IX2(kk, iCell, L)], th_km = p.theta_m[IX2(kk - 1, iCell, L)];
-    if (kk == L) return p.rw_save[IX2(kk, iCell, L1)] * (fm * th_k + fp * th_km);
-    const real rwk = p.rw[IX2(kk, iCell, L1)];
-    real f;
-    if (kk == 2) f = rwk * (fm * th_k + fp * th_km);
-    else f = flux3(p.theta_m[IX2(kk - 2, iCell, L)], th_km, th_k, p.theta_m[IX2(kk + 1, iCell, L)], rwk, p.coef_3rd_order);
-    return f + (p.rw_save[IX2(kk, iCell, L1)] - rwk) * (fm * p.theta_m_save[IX2(kk, iCell, L)] + fp * p.theta_m_save[IX2(kk - 1, iCell, L)]);
-}
+// Shared-memory column slots of one warp of dt_cell_kernel (tma_slot(L + 1) reals each)
+enum { CC_W, CC_RW, CC_TH, CC_RWS, CC_THS, CC_TWE, CC_TTE, CC_RHO, CC_WDW, CC_WDT, CC_NCOL_RK23, CC_CQW = CC_NCOL_RK23, CC_PP, CC_DPDZ, CC_NCOL_RK1 };
 
-// w and theta_m tendencies of one owned cell per warp.  dynamic shared memory: WPB * 2 * (L + 2) reals.
-__global__ void __launch_bounds__(WPB * 32) dt_cell_kernel(DtP p, const real* __restrict__ ft, const real* __restrict__ fw, const real* __restrict__ ft2) {
-    extern __shared__ real s_dyn[];
-    __shared__ int s_edge[WPB][8], s_c1[WPB][8], s_c2[WPB][8];
+// w and theta_m tendencies of one owned cell per warp (w: flux divergence TI:5046-5074, rk1 del4 TI:5134-5154, vertical
+// advection, pgf + buoyancy, final sum TI:5167-5223; theta_m: TI:5231-5269, 5304-5325, 5331-5414).
+// The cell's own columns (w, rw, theta_m, rw_save, theta_m_save, tend_w_euler, tend_theta_euler, rho_zz [, cqw, pp, dpdz])
+// are staged into shared memory by one bulk (TMA) copy each, issued by lane 0 before the stencil metadata is even
+// read, so every vertical stencil and every single-use operand costs a shared-memory read and the warp waits for
+// memory once.  The edge gathers (fw, ft, ft2, delsq_*) are direct loads: each lane owns levels (lane, lane + 32), the
+// edge list is staged as element offsets with signs (and the rk1 del4 coefficients), padded with zero entries to 6 or 8
+// (x - 0*y == x exactly, the sums are never -0), and all loads of a sum are issued before its first subtract.
+// dynamic shared memory: WPB * ncol * tma_slot(L + 1) reals.
+template <bool RK1, int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) dt_cell_kernel(DtP p, const real* __restrict__ ft, const real* __restrict__ fw, const real* __restrict__ ft2) {
+    extern __shared__ __align__(16) real s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar[WPB];
+    __shared__ unsigned s_eo[WPB][8], s_c1[WPB][8], s_c2[WPB][8];
     __shared__ real s_sign[WPB][8], s_esw[WPB][8], s_est[WPB][8];
-    const int L = p.L, L1 = L + 1, mE = p.mE;
+    const int L = p.L, L1 = L + 1, mE = p.mE, LS = tma_slot(L1);
     WARP_ENTITY(p.cellSolveStart, p.nCellsSolveLoop);
     const int iCell = ent;
-    real* wdw = s_dyn + (size_t)warp * 2 * (L + 2);
-    real* wdt = wdw + (L + 2);
+    real* sc = s_dyn + (size_t)warp * (RK1 ? CC_NCOL_RK1 : CC_NCOL_RK23) * LS;
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+    const unsigned coff = (unsigned)(iCell - 1) * (unsigned)L, woff = (unsigned)(iCell - 1) * (unsigned)L1;
+    const real *g_w = p.w + woff, *g_rw = p.rw + woff, *g_th = p.theta_m + coff, *g_rws = p.rw_save + woff, *g_ths = p.theta_m_save + coff;
+    const real *g_twe = p.tend_w_euler + woff, *g_tte = p.tend_theta_euler + coff, *g_rho = p.rho_zz + coff;
+    const real *g_cqw = p.cqw + coff, *g_pp = p.pp + coff, *g_dpdz = p.dpdz + coff;
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
+        unsigned total = 0;
+        tma_issue_col(s0 + CC_W * cs, g_w, L1, mbar, total);
+        tma_issue_col(s0 + CC_RW * cs, g_rw, L1, mbar, total);
+        tma_issue_col(s0 + CC_TH * cs, g_th, L, mbar, total);
+        tma_issue_col(s0 + CC_RWS * cs, g_rws, L1, mbar, total);
+        tma_issue_col(s0 + CC_THS * cs, g_ths, L, mbar, total);
+        tma_issue_col(s0 + CC_TWE * cs, g_twe, L1, mbar, total);
+        tma_issue_col(s0 + CC_TTE * cs, g_tte, L, mbar, total);
+        tma_issue_col(s0 + CC_RHO * cs, g_rho, L, mbar, total);
+        if (RK1) {
+            tma_issue_col(s0 + CC_CQW * cs, g_cqw, L, mbar, total);
+            tma_issue_col(s0 + CC_PP * cs, g_pp, L, mbar, total);
+            tma_issue_col(s0 + CC_DPDZ * cs, g_dpdz, L, mbar, total);
+        }
+        mbar_arrive_expect_tx(mbar, total);
+    }
+    // 1-based views of the staged columns: s_w[k] = w(k, iCell), ...
+    const real* s_w = sc + CC_W * LS + tma_shift(g_w) - 1;
+    const real* s_rw = sc + CC_RW * LS + tma_shift(g_rw) - 1;
+    const real* s_th = sc + CC_TH * LS + tma_shift(g_th) - 1;
+    const real* s_rws = sc + CC_RWS * LS + tma_shift(g_rws) - 1;
+    const real* s_ths = sc + CC_THS * LS + tma_shift(g_ths) - 1;
+    const real* s_twe = sc + CC_TWE * LS + tma_shift(g_twe) - 1;
+    const real* s_tte = sc + CC_TTE * LS + tma_shift(g_tte) - 1;
+    const real* s_rho = sc + CC_RHO * LS + tma_shift(g_rho) - 1;
+    const real* s_cqw = sc + CC_CQW * LS + tma_shift(g_cqw) - 1;
+    const real* s_pp = sc + CC_PP * LS + tma_shift(g_pp) - 1;
+    const real* s_dpdz = sc + CC_DPDZ * LS + tma_shift(g_dpdz) - 1;
+    real* wdw = sc + CC_WDW * LS - 1;
+    real* wdt = sc + CC_WDT * LS - 1;
+
     const int ne = p.nEdgesOnCell[iCell - 1];
+    const int npad = ne <= 6 ? 6 : 8;  // padded edge count (zero signs / coefficients beyond ne)
     const real invArea = p.invAreaCell[iCell - 1];
-    const bool del4w = (p.rk_step == 1 && p.h_mom_eddy_visc4 > (real)0.0);
-    const bool del4t = (p.rk_step == 1 && p.h_theta_eddy_visc4 > (real)0.0);
-    if (lane < ne) {
-        const int iEdge = p.edgesOnCell[IX2(lane + 1, iCell, mE)];
-        const real sgn = p.edgesOnCell_sign[IX2(lane + 1, iCell, mE)];
-        s_edge[warp][lane] = iEdge;
+    const bool del4w = (RK1 && p.h_mom_eddy_visc4 > (real)0.0);
+    const bool del4t = (RK1 && p.h_theta_eddy_visc4 > (real)0.0);
+    if (lane < npad) {
+        const bool in = lane < ne;
+        const int iEdge = p.edgesOnCell[IX2(in ? lane + 1 : 1, iCell, mE)];
+        const real sgn = in ? p.edgesOnCell_sign[IX2(lane + 1, iCell, mE)] : (real)0.0;
+        s_eo[warp][lane] = (unsigned)(iEdge - 1) * (unsigned)L;
         s_sign[warp][lane] = sgn;
         if (del4w || del4t) {
-            s_c1[warp][lane] = p.cellsOnEdge[IX2(1, iEdge, 2)];
-            s_c2[warp][lane] = p.cellsOnEdge[IX2(2, iEdge, 2)];
+            s_c1[warp][lane] = (unsigned)(p.cellsOnEdge[IX2(1, iEdge, 2)] - 1) * (unsigned)L;
+            s_c2[warp][lane] = (unsigned)(p.cellsOnEdge[IX2(2, iEdge, 2)] - 1) * (unsigned)L;
             const real ms4 = p.meshScalingDel4[iEdge - 1], dv = p.dvEdge[iEdge - 1], idc = p.invDcEdge[iEdge - 1];
             s_esw[warp][lane] = ms4 * (p.h_mom_eddy_visc4 * invArea) * dv * sgn * idc;                    // TI:5141-5146
             s_est[warp][lane] = ms4 * (p.h_theta_eddy_visc4 * p.prandtl_inv * invArea) * dv * sgn * idc;  // TI:5309-5315
         }
     }
-    for (int k = lane + 1; k <= L1; k += 32) {
-        wdw[k] = wdwz_at(p, k, iCell);
-        wdt[k] = wdtz_at(p, k, iCell);
+    __syncwarp();
+    mbar_wait(mbar, 0);
+    // ---- vertical fluxes at the interfaces (TI:5167-5185, 5331-5353), branch-free: stencil levels are clamped into the
+    // column, both the 3rd-order and the 2nd-order (boundary) forms are evaluated and one is selected
+    for (int kk = lane + 1; kk <= L1; kk += 32) {
+        const int k = min(max(kk, 2), L);  // evaluation level (results for kk = 1, L+1 are discarded)
+        const int km2 = max(k - 2, 1), kp1 = min(k + 1, L);
+        const real rwk = s_rw[k], rwkm = s_rw[k - 1];
+        const real wk = s_w[k], wkm = s_w[k - 1];
+        const bool bnd = (k == 2 || k == L), ends = (kk == 1 || kk == L1);
+        {
+            const real f2 = (real)0.25 * (rwk + rwkm) * (wk + wkm);
+            const real f3 = flux3(s_w[km2], wkm, wk, s_w[kp1], (real)0.5 * (rwk + rwkm), (real)1.0);
+            wdw[kk] = ends ? (real)0.0 : (bnd ? f2 : f3);
+        }
+        {
+            const real fm = p.fzm[k - 1], fp = p.fzp[k - 1];
+            const real th_k = s_th[k], th_km = s_th[k - 1];
+            const real rws = s_rws[k];
+            const real c2 = fm * th_k + fp * th_km;
+            const real f3 = flux3(s_th[km2], th_km, th_k, s_th[kp1], rwk, p.coef_3rd_order);
+            const real corr = (rws - rwk) * (fm * s_ths[k] + fp * s_ths[k - 1]);
+            const real inner = ((k == 2) ? rwk * c2 : f3) + corr;
+            wdt[kk] = ends ? (real)0.0 : ((k == L) ? rws * c2 : inner);
+        }
     }
     __syncwarp();
-    // ---- w, TI:5046-5074, 5134-5154, 5167-5223
-    for (int k = lane + 1; k <= L1; k += 32) {
-        const size_t iw = IX2(k, iCell, L1);
-        if (k == 1 || k == L1) {
-            p.tend_w[iw] = 0.0;
-            continue;
-        }
-        real tw = 0.0;
-        real twe = p.tend_w_euler[iw];
-        for (int i = 0; i < ne; ++i) {
-            tw = tw - s_sign[warp][i] * fw[IX2(k, s_edge[warp][i], L)];
-            if (del4w) twe = twe - s_esw[warp][i] * (p.delsq_w[IX2(k, s_c2[warp][i], L)] - p.delsq_w[IX2(k, s_c1[warp][i], L)]);
-        }
-        tw = tw * invArea - p.rdzu[k - 1] * (wdw[k + 1] - wdw[k]);
-        if (p.rk_step == 1) {
-            const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L);
-            twe = twe - p.cqw[ic] * (p.rdzu[k - 1] * (p.pp[ic] - p.pp[icm]) - (p.fzm[k - 1] * p.dpdz[ic] + p.fzp[k - 1] * p.dpdz[icm]));
-            if (p.v_mom_eddy_visc2 > (real)0.0) {
-                const real wk = p.w[iw];
-                twe = twe + p.v_mom_eddy_visc2 * (real)0.5 * (p.rho_zz[ic] + p.rho_zz[icm]) *
-                                ((p.w[IX2(k + 1, iCell, L1)] - wk) * p.rdzw[k - 1] - (wk - p.w[IX2(k - 1, iCell, L1)]) * p.rdzw[k - 2]) * p.rdzu[k - 1];
+    // ---- w, TI:5046-5074, 5134-5154, 5167-5223: levels k = ka + 1 and ka + 33 of (1..L+1)
+    for (int ka = lane; ka < L1; ka += 64) {
+        const bool vb = ka + 32 < L1;
+        const int bo = vb ? 32 : 0;
+        real tw_a = 0.0, tw_b = 0.0;
+        real twe_a = s_twe[ka + 1], twe_b = s_twe[ka + 1 + bo];
+        {
+            const real* __restrict__ fwp = fw + ka;  // fw(k, e): element (e-1)*L + k-1
+            gather_sub<6>(fwp, s_eo[warp], s_sign[warp], bo, tw_a, tw_b);
+            if (npad > 6) gather_sub<2>(fwp, s_eo[warp] + 6, s_sign[warp] + 6, bo, tw_a, tw_b);
+            if (del4w) {
+                const real* __restrict__ dsw = p.delsq_w + ka;
+                gather_sub_diff<6>(dsw, s_c2[warp], s_c1[warp], s_esw[warp], bo, twe_a, twe_b);
+                if (npad > 6) gather_sub_diff<2>(dsw, s_c2[warp] + 6, s_c1[warp] + 6, s_esw[warp] + 6, bo, twe_a, twe_b);
             }
-            p.tend_w_euler[iw] = twe;
         }
-        p.tend_w[iw] = tw + twe;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const int k = ka + 1 + 32 * h;
+            const size_t iw = (size_t)woff + (k - 1);
+            if (k == 1 || k == L1) {
+                p.tend_w[iw] = 0.0;
+                continue;
+            }
+            real tw = h ? tw_b : tw_a, twe = h ? twe_b : twe_a;
+            tw = tw * invArea - p.rdzu[k - 1] * (wdw[k + 1] - wdw[k]);
+            if (RK1) {
+                twe = twe - s_cqw[k] * (p.rdzu[k - 1] * (s_pp[k] - s_pp[k - 1]) - (p.fzm[k - 1] * s_dpdz[k] + p.fzp[k - 1] * s_dpdz[k - 1]));
+                if (p.v_mom_eddy_visc2 > (real)0.0) {
+                    const real wk = s_w[k];
+                    twe = twe + p.v_mom_eddy_visc2 * (real)0.5 * (s_rho[k] + s_rho[k - 1]) *
+                                    ((s_w[k + 1] - wk) * p.rdzw[k - 1] - (wk - s_w[k - 1]) * p.rdzw[k - 2]) * p.rdzu[k - 1];
+                }
+                p.tend_w_euler[iw] = twe;
+            }
+            p.tend_w[iw] = tw + twe;
+        }
     }
     // ---- theta_m, TI:5231-5269, 5304-5325, 5331-5414
-    for (int k = lane + 1; k <= L; k += 32) {
-        const size_t ic = IX2(k, iCell, L);
-        real tt = 0.0;
-        real tte = p.tend_theta_euler[ic];
-        for (int i = 0; i < ne; ++i) tt = tt - s_sign[warp][i] * ft[IX2(k, s_edge[warp][i], L)];
-        if (p.rk_step > 1)
-            for (int i = 0; i < ne; ++i) tt = tt - s_sign[warp][i] * ft2[IX2(k, s_edge[warp][i], L)];
-        if (del4t)
-            for (int i = 0; i < ne; ++i) tte = tte - s_est[warp][i] * (p.delsq_theta[IX2(k, s_c2[warp][i], L)] - p.delsq_theta[IX2(k, s_c1[warp][i], L)]);
-        tt = tt * invArea - p.rdzw[k - 1] * (wdt[k + 1] - wdt[k]);
-        const real rho = p.rho_zz[ic];
-        if (p.tend_rtheta_adv) p.tend_rtheta_adv[ic] = tt;
-        if (p.rthdynten) p.rthdynten[ic] = tt / rho;
-        tt = tt + rho * (p.rt_diabatic_tend ? p.rt_diabatic_tend[ic] : (real)0.0);
-        if (p.rk_step == 1 && p.v_theta_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:5360-5406
-            const real z1 = p.zgrid[IX2(k - 1, iCell, L1)], z2 = p.zgrid[IX2(k, iCell, L1)], z3 = p.zgrid[IX2(k + 1, iCell, L1)], z4 = p.zgrid[IX2(k + 2, iCell, L1)];
-            const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
-            real a = p.theta_m[IX2(k + 1, iCell, L)], b = p.theta_m[ic], c = p.theta_m[IX2(k - 1, iCell, L)];
-            if (p.mix_full) {
-                tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * ((a - b) / (zp - z0) - (b - c) / (z0 - zm)) / ((real)0.5 * (zp - zm));
-            } else {
-                const real ta = p.t_init[IX2(k + 1, iCell, L)], tb = p.t_init[ic], tc = p.t_init[IX2(k - 1, iCell, L)];
-                tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * (((a - ta) - (b - tb)) / (zp - z0) - ((b - tb) - (c - tc)) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+    for (int ka = lane; ka < L; ka += 64) {
+        const bool vb = ka + 32 < L;
+        const int bo = vb ? 32 : 0;
+        real tt_a = 0.0, tt_b = 0.0;
+        real tte_a = s_tte[ka + 1], tte_b = s_tte[ka + 1 + bo];
+        {
+            const real* __restrict__ ftp = ft + ka;
+            gather_sub<6>(ftp, s_eo[warp], s_sign[warp], bo, tt_a, tt_b);
+            if (npad > 6) gather_sub<2>(ftp, s_eo[warp] + 6, s_sign[warp] + 6, bo, tt_a, tt_b);
+            if (!RK1) {
+                const real* __restrict__ f2p = ft2 + ka;
+                gather_sub<6>(f2p, s_eo[warp], s_sign[warp], bo, tt_a, tt_b);
+                if (npad > 6) gather_sub<2>(f2p, s_eo[warp] + 6, s_sign[warp] + 6, bo, tt_a, tt_b);
+            }
+            if (del4t) {
+                const real* __restrict__ dst = p.delsq_theta + ka;
+                gather_sub_diff<6>(dst, s_c2[warp], s_c1[warp], s_est[warp], bo, tte_a, tte_b);
+                if (npad > 6) gather_sub_diff<2>(dst, s_c2[warp] + 6, s_c1[warp] + 6, s_est[warp] + 6, bo, tte_a, tte_b);
             }
         }
-        if (p.rk_step == 1 && (del4t || p.v_theta_eddy_visc2 > (real)0.0)) p.tend_theta_euler[ic] = tte;
-        p.tend_theta[ic] = tt + tte + (p.tend_rtheta_physics ? p.tend_rtheta_physics[ic] : (real)0.0);
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const int k = ka + 1 + 32 * h;
+            const size_t ic = (size_t)coff + (k - 1);
+            real tt = h ? tt_b : tt_a, tte = h ? tte_b : tte_a;
+            tt = tt * invArea - p.rdzw[k - 1] * (wdt[k + 1] - wdt[k]);
+            const real rho = s_rho[k];
+            if (p.tend_rtheta_adv) p.tend_rtheta_adv[ic] = tt;
+            if (p.rthdynten) p.rthdynten[ic] = tt / rho;
+            tt = tt + rho * (p.rt_diabatic_tend ? p.rt_diabatic_tend[ic] : (real)0.0);
+            if (RK1 && p.v_theta_eddy_visc2 > (real)0.0 && k >= 2 && k <= L - 1) {  // TI:5360-5406
+                const real z1 = p.zgrid[IX2(k - 1, iCell, L1)], z2 = p.zgrid[IX2(k, iCell, L1)], z3 = p.zgrid[IX2(k + 1, iCell, L1)], z4 = p.zgrid[IX2(k + 2, iCell, L1)];
+                const real zm = (real)0.5 * (z1 + z2), z0 = (real)0.5 * (z2 + z3), zp = (real)0.5 * (z3 + z4);
+                real a = s_th[k + 1], b = s_th[k], c = s_th[k - 1];
+                if (p.mix_full) {
+                    tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * ((a - b) / (zp - z0) - (b - c) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+                } else {
+                    const real ta = p.t_init[ic + 1], tb = p.t_init[ic], tc = p.t_init[ic - 1];
+                    tte = tte + p.v_theta_eddy_visc2 * p.prandtl_inv * rho * (((a - ta) - (b - tb)) / (zp - z0) - ((b - tb) - (c - tc)) / (z0 - zm)) / ((real)0.5 * (zp - zm));
+                }
+            }
+            if (RK1 && (del4t || p.v_theta_eddy_visc2 > (real)0.0)) p.tend_theta_euler[ic] = tte;
+            p.tend_theta[ic] = tt + tte + (p.tend_rtheta_physics ? p.tend_rtheta_physics[ic] : (real)0.0);
+        }
     }
 }
 
@@ -606,7 +794,8 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     real* fw = workspace(1, nEL);
     real* ft2 = workspace(2, nEL);
     if (!ft || !fw || !ft2) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace");
-    WLAUNCH(dt_edge_flux_kernel, p.nEdgesLoop, 0, p, ft, fw, ft2);
+    if (rk_step == 1) WLAUNCH(dt_edge_flux_kernel<true>, p.nEdgesLoop, 0, p, ft, fw, ft2);
+    else WLAUNCH(dt_edge_flux_kernel<false>, p.nEdgesLoop, 0, p, ft, fw, ft2);
     KCHECK("dt_edge_flux_kernel");
     {
         const size_t shm = (size_t)WPB * (rk_step == 1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * tma_slot(L + 1) * sizeof(real);
@@ -615,7 +804,21 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
         else WLAUNCH((dt_edge_kernel<5, true, false>), p.nEdgesSolveLoop, shm, p);
         KCHECK("dt_edge_kernel");
     }
-    WLAUNCH(dt_cell_kernel, p.nCellsSolveLoop, (size_t)WPB * 2 * (L + 2) * sizeof(real), p, ft, fw, ft2);
+    {
+        static const int minb = tune("dt_cell_minb", 4);
+        const size_t shm = (size_t)WPB * (rk_step == 1 ? CC_NCOL_RK1 : CC_NCOL_RK23) * tma_slot(L + 1) * sizeof(real);
+        if (rk_step == 1) {
+            if (minb == 3) WLAUNCH((dt_cell_kernel<true, 3>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+            else if (minb == 5) WLAUNCH((dt_cell_kernel<true, 5>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+            else if (minb == 6) WLAUNCH((dt_cell_kernel<true, 6>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+            else WLAUNCH((dt_cell_kernel<true, 4>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+        } else {
+            if (minb == 3) WLAUNCH((dt_cell_kernel<false, 3>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+            else if (minb == 5) WLAUNCH((dt_cell_kernel<false, 5>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+            else if (minb == 6) WLAUNCH((dt_cell_kernel<false, 6>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+            else WLAUNCH((dt_cell_kernel<false, 4>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);
+        }
+    }
     KCHECK("dt_cell_kernel");
     return 0;
 }

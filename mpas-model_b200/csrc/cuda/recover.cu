@@ -98,31 +98,49 @@ struct RecWP {
     real* w;
 };
 
-__global__ void __launch_bounds__(256) recover_w_kernel(RecWP p) {
+// Flat (k, cell) mapping; the edge loop is unrolled to NE slots with the loads of ALL edges issued before the first
+// dependent add (index loads, then ru / zb / zb3 loads, then the sum in the reference's order), so a thread waits for
+// memory twice instead of twice per edge.  Slots beyond nEdgesOnCell repeat edge 1 and are skipped in the sum.
+template <int NE>
+__global__ void __launch_bounds__(256, NE <= 6 ? 3 : 2) recover_w_kernel(RecWP p) {
     const int L = p.L, L1 = L + 1, mE = p.mE;
     FLAT_KC(p.nCellsLoop, L);
     const int iCell = p.cellStart + _c0;
     if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) return;
     const size_t iw = IX2(k, iCell, L1);
-    real wk = p.w[iw];
     const int ne = p.nEdgesOnCell[iCell - 1];
-    if (k == 1) {
-        for (int i = 1; i <= ne; ++i) {
-            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-            const real flux = (p.cf1 * p.ru[IX2(1, iEdge, L)] + p.cf2 * p.ru[IX2(2, iEdge, L)] + p.cf3 * p.ru[IX2(3, iEdge, L)]);
-            wk = wk + p.edgesOnCell_sign[IX2(i, iCell, mE)] * (p.zb_cell[IX3(1, i, iCell, L1, mE)] + fsign((real)1.0, flux) * p.zb3_cell[IX3(1, i, iCell, L1, mE)]) * flux;
-        }
-        wk = wk / (p.cf1 * p.rho_zz[IX2(1, iCell, L)] + p.cf2 * p.rho_zz[IX2(2, iCell, L)] + p.cf3 * p.rho_zz[IX2(3, iCell, L)]);
-    } else {
-        const real fm = p.fzm[k - 1], fp = p.fzp[k - 1];
-        for (int i = 1; i <= ne; ++i) {
-            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-            const real flux = (fm * p.ru[IX2(k, iEdge, L)] + fp * p.ru[IX2(k - 1, iEdge, L)]);
-            wk = wk + p.edgesOnCell_sign[IX2(i, iCell, mE)] * (p.zb_cell[IX3(k, i, iCell, L1, mE)] + fsign((real)1.0, flux) * p.zb3_cell[IX3(k, i, iCell, L1, mE)]) * flux;
-        }
-        wk = wk / (fm * p.rho_zz[IX2(k, iCell, L)] + fp * p.rho_zz[IX2(k - 1, iCell, L)]);
+    const int* eoc = p.edgesOnCell + (size_t)(iCell - 1) * mE;
+    const real* sgn = p.edgesOnCell_sign + (size_t)(iCell - 1) * mE;
+    const real* zb = p.zb_cell + (size_t)(iCell - 1) * mE * L1 + (k - 1);
+    const real* zb3 = p.zb3_cell + (size_t)(iCell - 1) * mE * L1 + (k - 1);
+    int e[NE];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) e[i] = eoc[i < ne ? i : 0];
+    real a[NE], a3[NE], r0[NE], r1[NE];
+    const int km = k >= 2 ? k - 1 : 2;  // second level of the flux (k = 1 uses levels 1, 2, 3)
+#pragma unroll
+    for (int i = 0; i < NE; ++i) {
+        const int j = i < ne ? i : 0;
+        const real* ru = p.ru + (size_t)(e[i] - 1) * L;
+        a[i] = zb[(size_t)j * L1];
+        a3[i] = zb3[(size_t)j * L1];
+        r0[i] = ru[k - 1];
+        r1[i] = ru[km - 1];
     }
-    p.w[iw] = wk;
+    real wk = p.w[iw];
+    // k = 1: flux = cf1 ru(1) + cf2 ru(2) + cf3 ru(3) (TI:3069-3082); k >= 2: flux = fzm(k) ru(k) + fzp(k) ru(k-1) (TI:3085-3095)
+    const bool first = (k == 1);
+    const real c0 = first ? p.cf1 : p.fzm[k - 1], c1 = first ? p.cf2 : p.fzp[k - 1];
+    const real* rho = p.rho_zz + (size_t)(iCell - 1) * L;
+    real den = c0 * rho[k - 1] + c1 * rho[km - 1];
+    if (first) den = den + p.cf3 * rho[2];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) {
+        real flux = c0 * r0[i] + c1 * r1[i];
+        if (first) flux = flux + p.cf3 * p.ru[(size_t)(e[i] - 1) * L + 2];
+        if (i < ne) wk = wk + sgn[i] * (a[i] + fsign((real)1.0, flux) * a3[i]) * flux;
+    }
+    p.w[iw] = wk / den;
 }
 
 struct SmlP {
@@ -133,6 +151,7 @@ struct SmlP {
 };
 
 // TI:2287-2307: omega tendency from the w tendency and the terrain flux of the u tendency
+template <int NE>
 __global__ void __launch_bounds__(256) smlstep_kernel(SmlP p) {
     const int L = p.L, L1 = L + 1, mE = p.mE;
     FLAT_KC(p.nCellsLoop, L);
@@ -140,16 +159,34 @@ __global__ void __launch_bounds__(256) smlstep_kernel(SmlP p) {
     const int iCell = p.cellStart + _c0;
     if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) return;
     const size_t iw = IX2(k, iCell, L1);
-    real wt = p.w_tend[iw];
     const int ne = p.nEdgesOnCell[iCell - 1];
-    const real fm = p.fzm[k - 1], fp = p.fzp[k - 1];
-    for (int i = 1; i <= ne; ++i) {
-        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-        const real ut = p.u_tend[IX2(k, iEdge, L)];
-        const real flux = p.edgesOnCell_sign[IX2(i, iCell, mE)] * (fm * ut + fp * p.u_tend[IX2(k - 1, iEdge, L)]);
-        wt = wt - (p.zb_cell[IX3(k, i, iCell, L1, mE)] + fsign((real)1.0, ut) * p.zb3_cell[IX3(k, i, iCell, L1, mE)]) * flux;
+    const int* eoc = p.edgesOnCell + (size_t)(iCell - 1) * mE;
+    const real* sgn = p.edgesOnCell_sign + (size_t)(iCell - 1) * mE;
+    const real* zb = p.zb_cell + (size_t)(iCell - 1) * mE * L1 + (k - 1);
+    const real* zb3 = p.zb3_cell + (size_t)(iCell - 1) * mE * L1 + (k - 1);
+    int e[NE];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) e[i] = eoc[i < ne ? i : 0];
+    real s[NE], a[NE], a3[NE], u0[NE], u1[NE];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) {  // every load of the edge sum is issued before its first use
+        const int j = i < ne ? i : 0;
+        const real* ut = p.u_tend + (size_t)(e[i] - 1) * L + (k - 1);
+        s[i] = sgn[j];
+        a[i] = zb[(size_t)j * L1];
+        a3[i] = zb3[(size_t)j * L1];
+        u0[i] = ut[0];
+        u1[i] = ut[-1];
     }
-    p.w_tend[iw] = (fm * p.zz[IX2(k, iCell, L)] + fp * p.zz[IX2(k - 1, iCell, L)]) * wt;
+    real wt = p.w_tend[iw];
+    const real fm = p.fzm[k - 1], fp = p.fzp[k - 1];
+    const real zf = fm * p.zz[IX2(k, iCell, L)] + fp * p.zz[IX2(k - 1, iCell, L)];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) {
+        const real flux = s[i] * (fm * u0[i] + fp * u1[i]);
+        if (i < ne) wt = wt - (a[i] + fsign((real)1.0, u0[i]) * a3[i]) * flux;
+    }
+    p.w_tend[iw] = zf * wt;
 }
 
 }  // namespace
@@ -190,7 +227,9 @@ extern "C" int mpas_b200_recover_large_step_variables_work(MPAS_RECOVER_ARGS) {
         p.bdyMaskCell = X(bdyMaskCell); p.nEdgesOnCell = X(nEdgesOnCell); p.edgesOnCell = X(edgesOnCell);
         p.edgesOnCell_sign = X(edgesOnCell_sign); p.zb_cell = X(zb_cell); p.zb3_cell = X(zb3_cell); p.ru = X(ru); p.rho_zz = d_rho_zz;
         p.fzm = X(fzm); p.fzp = X(fzp); p.w = X(w);
-        KLAUNCH(recover_w_kernel, (long long)p.nCellsLoop * L, 256, p);
+        if (p.mE <= 6) KLAUNCH(recover_w_kernel<6>, (long long)p.nCellsLoop * L, 256, p);
+        else if (p.mE <= 8) KLAUNCH(recover_w_kernel<8>, (long long)p.nCellsLoop * L, 256, p);
+        else KLAUNCH(recover_w_kernel<12>, (long long)p.nCellsLoop * L, 256, p);
         KCHECK("recover_w_kernel");
     }
     return 0;
@@ -204,7 +243,9 @@ extern "C" int mpas_b200_set_smlstep_pert_variables_work(MPAS_SMLSTEP_ARGS) {
     p.bdyMaskCell = X(bdyMaskCell); p.nEdgesOnCell = X(nEdgesOnCell); p.edgesOnCell = X(edgesOnCell);
     p.edgesOnCell_sign = X(edgesOnCell_sign); p.zb_cell = X(zb_cell); p.zb3_cell = X(zb3_cell); p.u_tend = X(u_tend); p.zz = X(zz);
     p.fzm = X(fzm); p.fzp = X(fzp); p.w_tend = X(w_tend);
-    KLAUNCH(smlstep_kernel, (long long)p.nCellsLoop * p.L, 256, p);
+    if (p.mE <= 6) KLAUNCH(smlstep_kernel<6>, (long long)p.nCellsLoop * p.L, 256, p);
+    else if (p.mE <= 8) KLAUNCH(smlstep_kernel<8>, (long long)p.nCellsLoop * p.L, 256, p);
+    else KLAUNCH(smlstep_kernel<12>, (long long)p.nCellsLoop * p.L, 256, p);
     KCHECK("smlstep_kernel");
     return 0;
 }

@@ -113,8 +113,8 @@ void kflush() {
 }
 }  // namespace
 bool ensure_dyn_smem(const void* kernel, size_t bytes) {
-    if (bytes <= 48 * 1024) return true;
-    if (bytes > 227 * 1024) return false;
+    if (bytes <= 32 * 1024) return true;  // static shared memory counts against the default 48 KB as well
+    if (bytes > 220 * 1024) return false;
     static std::map<const void*, size_t> have;
     auto it = have.find(kernel);
     if (it != have.end() && it->second >= bytes) return true;
