@@ -58,136 +58,274 @@ struct AcCellP {
     real *rw_p, *rtheta_pp, *rtheta_pp_old, *wwAvg, *rho_pp;
 };
 
-// shared memory per warp: ts[L+1] rs[L+1] rwp[L+2] a[L+1] al[L+1] ga[L+1]  (1-based slots)
-__global__ void __launch_bounds__(256) acoustic_cell_kernel(AcCellP p) {
-    extern __shared__ real smem[];
-    const int L = p.L, L1 = L + 1, mE = p.mE;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    real* ts = smem + (size_t)warp * (6 * (L + 2));
-    real* rs = ts + (L + 2);
-    real* rwp = rs + (L + 2);
-    real* sa = rwp + (L + 2);
-    real* sal = sa + (L + 2);
-    real* sga = sal + (L + 2);
+// Shared-memory column slots of one warp of acoustic_cell_kernel (tma_slot(L + 1) reals each).  The first AC_NTMA_* are
+// filled by bulk (TMA) copies, the rest is scratch.
+enum { AC_ZZ, AC_COFTZ, AC_COFWT, AC_RHOZZ, AC_ATRI, AC_ALTRI, AC_GATRI, AC_NTMA_FIRST, AC_RTPP = AC_NTMA_FIRST, AC_RHOPP, AC_RWPOLD, AC_NTMA, AC_TS = AC_NTMA, AC_RS, AC_RWP, AC_NCOL };
+
+// rs/ts -= flux over NE edges for the two levels of a lane; all 6*NE loads are issued before the first dependent subtract
+template <int NE>
+__device__ __forceinline__ void ac_flux_sub(const real* __restrict__ rup_ka, const real* __restrict__ thp_ka, const unsigned* eo, const unsigned* c1o,
+                                            const unsigned* c2o, const real* coef, real invArea, int bo, real& rs_a, real& rs_b, real& ts_a, real& ts_b) {
+    real ua[NE], ub[NE], t1a[NE], t1b[NE], t2a[NE], t2b[NE];
+#pragma unroll
+    for (int t = 0; t < NE; ++t) {
+        const real* __restrict__ q = elem_ptr(rup_ka, eo[t]);
+        const real* __restrict__ q1 = elem_ptr(thp_ka, c1o[t]);
+        const real* __restrict__ q2 = elem_ptr(thp_ka, c2o[t]);
+        ua[t] = q[0];
+        ub[t] = q[bo];
+        t1a[t] = q1[0];
+        t1b[t] = q1[bo];
+        t2a[t] = q2[0];
+        t2b[t] = q2[bo];
+    }
+#pragma unroll
+    for (int t = 0; t < NE; ++t) {
+        const real c = coef[t];
+        const real fa = c * ua[t] * invArea, fb = c * ub[t] * invArea;
+        rs_a = rs_a - fa;
+        rs_b = rs_b - fb;
+        ts_a = ts_a - fa * (real)0.5 * (t2a[t] + t1a[t]);
+        ts_b = ts_b - fb * (real)0.5 * (t2b[t] + t1b[t]);
+    }
+}
+
+// One column per warp, lanes along k.  Columns with a vertical stencil or several uses (zz, coftz, cofwt, rho_zz, the
+// tridiagonal coefficients, and after the first substep rtheta_pp, rho_pp, rw_p) are staged by one bulk (TMA) copy each,
+// issued before the stencil metadata is read; the flux divergence over edgesOnCell is a direct gather with two levels
+// per lane, the edge list staged as element offsets + the coefficient (sign*dts)*dvEdge (zero beyond nEdgesOnCell).
+// FIRST = small_step 1: rtheta_pp, rho_pp, rw_p, wwAvg start from zero and are not read (TI:2603-2622).
+// dynamic shared memory: WPB * AC_NCOL * tma_slot(L + 1) reals.
+template <bool FIRST>
+__global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
+    extern __shared__ __align__(16) real s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar[WPB];
+    __shared__ unsigned s_eo[WPB][8], s_c1[WPB][8], s_c2[WPB][8];
+    __shared__ real s_coef[WPB][8];
+    const int L = p.L, L1 = L + 1, mE = p.mE, LS = tma_slot(L1);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ int s_tv[WPB][5];  // per warp: active flag and the s_dyn indices of its rwp, a, alpha, gamma columns (level 1)
+    const int iCell0 = p.cellStart + blockIdx.x * WPB + warp;
+    const bool exists = iCell0 <= p.cellEnd;
+    const int iCell = exists ? iCell0 : p.cellEnd;
     const real dts = p.dts, epssm = p.epssm, resm = p.resm;
-    const bool first = p.small_step == 1;
-
-    for (int iCell = p.cellStart + blockIdx.x * wpb + warp; iCell <= p.cellEnd; iCell += gridDim.x * wpb) {
-        // TI:2603-2611 (all cells)
+    const unsigned coff = (unsigned)(iCell - 1) * (unsigned)L, woff = (unsigned)(iCell - 1) * (unsigned)L1;
+    const bool solve = exists && !(iCell > p.cellSolveEnd || iCell < p.cellSolveStart);
+    const bool spec = solve && p.specZoneMaskCell[iCell - 1] != (real)0.0;
+    if (!solve || spec) {  // halo column: TI:2603-2611 copy only; specified zone of a regional run: TI:2710-2719
+        if (lane == 0) s_tv[warp][0] = 0;
+        if (exists)
         for (int k = lane + 1; k <= L; k += 32) {
-            const size_t ic = IX2(k, iCell, L);
-            p.rtheta_pp_old[ic] = first ? (real)0.0 : p.rtheta_pp[ic];
-        }
-        if (iCell > p.cellSolveEnd || iCell < p.cellSolveStart) continue;  // halo column: copy only
-
-        if (p.specZoneMaskCell[iCell - 1] == (real)0.0) {
-            const real invArea = p.invAreaCell[iCell - 1];
-            // stage the old rw_p column and the Thomas coefficients
-            for (int k = lane + 1; k <= L1; k += 32) rwp[k] = first ? (real)0.0 : p.rw_p[IX2(k, iCell, L1)];
-            for (int k = lane + 1; k <= L; k += 32) {
-                const size_t ic = IX2(k, iCell, L);
-                sa[k] = p.a_tri[ic];
-                sal[k] = p.alpha_tri[ic];
-                sga[k] = p.gamma_tri[ic];
-            }
-            __syncwarp();
-            const int ne = p.nEdgesOnCell[iCell - 1];
-            for (int k = lane + 1; k <= L; k += 32) {
-                real tsk = 0.0, rsk = 0.0;
-                for (int i = 1; i <= ne; ++i) {
-                    const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-                    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
-                    const real flux = p.edgesOnCell_sign[IX2(i, iCell, mE)] * dts * p.dvEdge[iEdge - 1] * p.ru_p[IX2(k, iEdge, L)] * invArea;
-                    rsk = rsk - flux;
-                    tsk = tsk - flux * (real)0.5 * (p.theta_m[IX2(k, cell2, L)] + p.theta_m[IX2(k, cell1, L)]);
-                }
-                const size_t ic = IX2(k, iCell, L);
-                const real rho_pp_k = first ? (real)0.0 : p.rho_pp[ic];
-                const real rth_pp_k = first ? (real)0.0 : p.rtheta_pp[ic];
-                rsk = rho_pp_k + dts * p.tend_rho[ic] + rsk - p.cofrz[k - 1] * resm * (rwp[k + 1] - rwp[k]);
-                tsk = rth_pp_k + dts * p.tend_rt[ic] + tsk -
-                      resm * p.rdzw[k - 1] * (p.coftz[IX2(k + 1, iCell, L1)] * rwp[k + 1] - p.coftz[IX2(k, iCell, L1)] * rwp[k]);
-                rs[k] = rsk;
-                ts[k] = tsk;
-            }
-            __syncwarp();
-            // explicit part of rw_p, TI:2659-2670 (reads only rwp[k] of its own level)
-            for (int k = lane + 1; k <= L; k += 32) {
-                if (k < 2) continue;
-                const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L);
-                const real rtpp_k = first ? (real)0.0 : p.rtheta_pp[ic], rtpp_km = first ? (real)0.0 : p.rtheta_pp[icm];
-                const real rpp_k = first ? (real)0.0 : p.rho_pp[ic], rpp_km = first ? (real)0.0 : p.rho_pp[icm];
-                const real zzk = p.zz[ic], zzkm = p.zz[icm];
-                rwp[k] = rwp[k] + dts * p.tend_rw[IX2(k, iCell, L1)] -
-                         p.cofwz[ic] * ((zzk * ts[k] - zzkm * ts[k - 1]) + resm * (zzk * rtpp_k - zzkm * rtpp_km)) -
-                         p.cofwr[ic] * ((rs[k] + rs[k - 1]) + resm * (rpp_k + rpp_km)) + p.cofwt[ic] * (ts[k] + resm * rtpp_k) +
-                         p.cofwt[icm] * (ts[k - 1] + resm * rtpp_km);
-            }
-            // first half of the wwAvg accumulation uses the OLD rw_p (TI:2655-2657): keep it in a register
-            // by recomputing from global below; here we only need ordering, so do it before rwp is overwritten.
-            // (old rw_p is still in global memory: rwp[] in shared memory is the working copy)
-            __syncwarp();
-            if (lane == 0) {  // TI:2675-2682, reference order
-                real prev = rwp[1];
-                for (int k = 2; k <= L; ++k) {
-                    prev = (rwp[k] - sa[k] * prev) * sal[k];
-                    rwp[k] = prev;
-                }
-                real next = rwp[L1];
-                for (int k = L; k >= 1; --k) {
-                    next = rwp[k] - sga[k] * next;
-                    rwp[k] = next;
-                }
-            }
-            __syncwarp();
-            for (int k = lane + 1; k <= L; k += 32) {
-                if (k < 2) continue;
-                const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L), iw = IX2(k, iCell, L1);
-                const real rw_old = first ? (real)0.0 : p.rw_p[iw];
-                real ww = first ? (real)0.0 : p.wwAvg[iw];
-                ww = ww + (real)0.5 * ((real)1.0 - epssm) * rw_old;
-                const real d = p.rw_save[iw] - p.rw[iw];
-                const real dk = p.dss[ic];
-                const real r = (rwp[k] + d -
-                                dts * dk * (p.fzm[k - 1] * p.zz[ic] + p.fzp[k - 1] * p.zz[icm]) *
-                                    (p.fzm[k - 1] * p.rho_zz[ic] + p.fzp[k - 1] * p.rho_zz[icm]) * p.w[iw]) /
-                                   ((real)1.0 + dts * dk) -
-                               d;
-                rwp[k] = r;
-                ww = ww + (real)0.5 * ((real)1.0 + epssm) * r;
-                p.wwAvg[iw] = ww;
-            }
-            __syncwarp();
-            for (int k = lane + 1; k <= L; k += 32) {
-                const size_t ic = IX2(k, iCell, L);
-                p.rw_p[IX2(k, iCell, L1)] = rwp[k];
-                p.rho_pp[ic] = rs[k] - p.cofrz[k - 1] * (rwp[k + 1] - rwp[k]);
-                p.rtheta_pp[ic] = ts[k] - p.rdzw[k - 1] * (p.coftz[IX2(k + 1, iCell, L1)] * rwp[k + 1] - p.coftz[IX2(k, iCell, L1)] * rwp[k]);
-            }
-            if (first) {  // TI:2617-2622: the levels the loops above never write
-                if (lane == 0) {
-                    p.wwAvg[IX2(1, iCell, L1)] = 0.0;
-                    p.wwAvg[IX2(L1, iCell, L1)] = 0.0;
-                    p.rw_p[IX2(L1, iCell, L1)] = 0.0;
-                }
-            }
-            __syncwarp();
-        } else {  // specified zone of a regional run, TI:2710-2719
-            for (int k = lane + 1; k <= L; k += 32) {
-                const size_t ic = IX2(k, iCell, L), iw = IX2(k, iCell, L1);
-                const real rho0 = first ? (real)0.0 : p.rho_pp[ic], rt0 = first ? (real)0.0 : p.rtheta_pp[ic];
-                const real rw0 = first ? (real)0.0 : p.rw_p[iw], ww0 = first ? (real)0.0 : p.wwAvg[iw];
+            const size_t ic = (size_t)coff + (k - 1), iw = (size_t)woff + (k - 1);
+            const real rt0 = FIRST ? (real)0.0 : p.rtheta_pp[ic];
+            p.rtheta_pp_old[ic] = rt0;
+            if (spec) {
+                const real rho0 = FIRST ? (real)0.0 : p.rho_pp[ic];
+                const real rw0 = FIRST ? (real)0.0 : p.rw_p[iw], ww0 = FIRST ? (real)0.0 : p.wwAvg[iw];
                 p.rho_pp[ic] = rho0 + dts * p.tend_rho[ic];
                 p.rtheta_pp[ic] = rt0 + dts * p.tend_rt[ic];
                 const real r = rw0 + dts * p.tend_rw[iw];
                 p.rw_p[iw] = r;
                 p.wwAvg[iw] = ww0 + (real)0.5 * ((real)1.0 + epssm) * r;
             }
-            if (first && lane == 0) {
-                p.wwAvg[IX2(L1, iCell, L1)] = 0.0;
-                p.rw_p[IX2(L1, iCell, L1)] = 0.0;
-            }
         }
+        if (spec && FIRST && lane == 0) {
+            p.wwAvg[IX2(L1, iCell, L1)] = 0.0;
+            p.rw_p[IX2(L1, iCell, L1)] = 0.0;
+        }
+        __syncthreads();  // the two block barriers around the tridiagonal sweep of the other warps
+        __syncthreads();
+        return;
+    }
+    real* sc = s_dyn + (size_t)warp * AC_NCOL * LS;
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+    const real *g_zz = p.zz + coff, *g_coftz = p.coftz + woff, *g_cofwt = p.cofwt + coff, *g_rhozz = p.rho_zz + coff;
+    const real *g_a = p.a_tri + coff, *g_al = p.alpha_tri + coff, *g_ga = p.gamma_tri + coff;
+    const real *g_rtpp = p.rtheta_pp + coff, *g_rhopp = p.rho_pp + coff, *g_rwp = p.rw_p + woff;
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
+        unsigned total = 0;
+        tma_issue_col(s0 + AC_ZZ * cs, g_zz, L, mbar, total);
+        tma_issue_col(s0 + AC_COFTZ * cs, g_coftz, L1, mbar, total);
+        tma_issue_col(s0 + AC_COFWT * cs, g_cofwt, L, mbar, total);
+        tma_issue_col(s0 + AC_RHOZZ * cs, g_rhozz, L, mbar, total);
+        tma_issue_col(s0 + AC_ATRI * cs, g_a, L, mbar, total);
+        tma_issue_col(s0 + AC_ALTRI * cs, g_al, L, mbar, total);
+        tma_issue_col(s0 + AC_GATRI * cs, g_ga, L, mbar, total);
+        if (!FIRST) {
+            tma_issue_col(s0 + AC_RTPP * cs, g_rtpp, L, mbar, total);
+            tma_issue_col(s0 + AC_RHOPP * cs, g_rhopp, L, mbar, total);
+            tma_issue_col(s0 + AC_RWPOLD * cs, g_rwp, L1, mbar, total);
+        }
+        mbar_arrive_expect_tx(mbar, total);
+    }
+    // 1-based views
+    const real* s_zz = sc + AC_ZZ * LS + tma_shift(g_zz) - 1;
+    const real* s_coftz = sc + AC_COFTZ * LS + tma_shift(g_coftz) - 1;
+    const real* s_cofwt = sc + AC_COFWT * LS + tma_shift(g_cofwt) - 1;
+    const real* s_rhozz = sc + AC_RHOZZ * LS + tma_shift(g_rhozz) - 1;
+    const real* sa = sc + AC_ATRI * LS + tma_shift(g_a) - 1;
+    const real* sal = sc + AC_ALTRI * LS + tma_shift(g_al) - 1;
+    const real* sga = sc + AC_GATRI * LS + tma_shift(g_ga) - 1;
+    const real* s_rtpp = sc + AC_RTPP * LS + tma_shift(g_rtpp) - 1;
+    const real* s_rhopp = sc + AC_RHOPP * LS + tma_shift(g_rhopp) - 1;
+    const real* s_rwold = sc + AC_RWPOLD * LS + tma_shift(g_rwp) - 1;
+    real* ts = sc + AC_TS * LS - 1;
+    real* rs = sc + AC_RS * LS - 1;
+    real* rwp = sc + AC_RWP * LS - 1;
+
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const int npad = ne <= 6 ? 6 : 8;
+    const real invArea = p.invAreaCell[iCell - 1];
+    if (lane < npad) {
+        const bool in = lane < ne;
+        const int iEdge = p.edgesOnCell[IX2(in ? lane + 1 : 1, iCell, mE)];
+        s_eo[warp][lane] = (unsigned)(iEdge - 1) * (unsigned)L;
+        s_c1[warp][lane] = (unsigned)(p.cellsOnEdge[IX2(1, iEdge, 2)] - 1) * (unsigned)L;
+        s_c2[warp][lane] = (unsigned)(p.cellsOnEdge[IX2(2, iEdge, 2)] - 1) * (unsigned)L;
+        s_coef[warp][lane] = in ? p.edgesOnCell_sign[IX2(lane + 1, iCell, mE)] * dts * p.dvEdge[iEdge - 1] : (real)0.0;
+    }
+    __syncwarp();
+    // ---- flux divergence, TI:2629-2639 (direct gather; the first chunk overlaps the bulk copies), then TI:2646-2653.
+    // Each lane owns levels k0 + lane + 1 and k0 + lane + 33 of a 64-level chunk.
+    bool staged = false;
+    for (int k0 = 0; k0 < L; k0 += 64) {
+        const int ka = k0 + lane;
+        const bool va = ka < L, vb = ka + 32 < L;
+        const int kl = va ? ka : L - 1;  // lanes past the column recompute its last level (loads stay in bounds)
+        const int bo = vb ? 32 : 0;
+        real rs_a = 0.0, rs_b = 0.0, ts_a = 0.0, ts_b = 0.0;
+        {
+            const real* __restrict__ rup = p.ru_p + kl;
+            const real* __restrict__ thp = p.theta_m + kl;
+            ac_flux_sub<3>(rup, thp, s_eo[warp], s_c1[warp], s_c2[warp], s_coef[warp], invArea, bo, rs_a, rs_b, ts_a, ts_b);
+            ac_flux_sub<3>(rup, thp, s_eo[warp] + 3, s_c1[warp] + 3, s_c2[warp] + 3, s_coef[warp] + 3, invArea, bo, rs_a, rs_b, ts_a, ts_b);
+            if (npad > 6) ac_flux_sub<2>(rup, thp, s_eo[warp] + 6, s_c1[warp] + 6, s_c2[warp] + 6, s_coef[warp] + 6, invArea, bo, rs_a, rs_b, ts_a, ts_b);
+        }
+        // single-use operands of this chunk, loaded now so that they share the round trip of the gather
+        const real trho_a = p.tend_rho[coff + kl], trho_b = p.tend_rho[coff + kl + bo];
+        const real trt_a = p.tend_rt[coff + kl], trt_b = p.tend_rt[coff + kl + bo];
+        if (!staged) {
+            mbar_wait(mbar, 0);
+            // TI:2603-2611 and the working copy of the old rw_p column
+            for (int k = lane + 1; k <= L1; k += 32) rwp[k] = FIRST ? (real)0.0 : s_rwold[k];
+            for (int k = lane + 1; k <= L; k += 32) p.rtheta_pp_old[(size_t)coff + (k - 1)] = FIRST ? (real)0.0 : s_rtpp[k];
+            __syncwarp();
+            staged = true;
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 0 ? !va : !vb) continue;
+            const int k = ka + 1 + 32 * h;
+            real rsk = h ? rs_b : rs_a, tsk = h ? ts_b : ts_a;
+            const real rho_pp_k = FIRST ? (real)0.0 : s_rhopp[k];
+            const real rth_pp_k = FIRST ? (real)0.0 : s_rtpp[k];
+            rsk = rho_pp_k + dts * (h ? trho_b : trho_a) + rsk - p.cofrz[k - 1] * resm * (rwp[k + 1] - rwp[k]);
+            tsk = rth_pp_k + dts * (h ? trt_b : trt_a) + tsk - resm * p.rdzw[k - 1] * (s_coftz[k + 1] * rwp[k + 1] - s_coftz[k] * rwp[k]);
+            rs[k] = rsk;
+            ts[k] = tsk;
+        }
+    }
+    __syncwarp();
+    // explicit part of rw_p, TI:2659-2670 (reads only rwp[k] of its own level)
+    for (int k = lane + 1; k <= L; k += 32) {
+        if (k < 2) continue;
+        const size_t ic = (size_t)coff + (k - 1);
+        const real rtpp_k = FIRST ? (real)0.0 : s_rtpp[k], rtpp_km = FIRST ? (real)0.0 : s_rtpp[k - 1];
+        const real rpp_k = FIRST ? (real)0.0 : s_rhopp[k], rpp_km = FIRST ? (real)0.0 : s_rhopp[k - 1];
+        const real zzk = s_zz[k], zzkm = s_zz[k - 1];
+        rwp[k] = rwp[k] + dts * p.tend_rw[(size_t)woff + (k - 1)] -
+                 p.cofwz[ic] * ((zzk * ts[k] - zzkm * ts[k - 1]) + resm * (zzk * rtpp_k - zzkm * rtpp_km)) -
+                 p.cofwr[ic] * ((rs[k] + rs[k - 1]) + resm * (rpp_k + rpp_km)) + s_cofwt[k] * (ts[k] + resm * rtpp_k) +
+                 s_cofwt[k - 1] * (ts[k - 1] + resm * rtpp_km);
+    }
+    // ---- tridiagonal sweep, TI:2675-2682, in the reference's order.  The recurrence is serial in k, so one LANE sweeps one
+    // column: the block's WPB columns are swept together by the first WPB lanes of warp 0 (1/WPB of the instructions of
+    // a sweep per warp), between two block barriers.
+    if (lane == 0) {
+        s_tv[warp][0] = 1;
+        s_tv[warp][1] = (int)(rwp - s_dyn);
+        s_tv[warp][2] = (int)(sa - s_dyn);
+        s_tv[warp][3] = (int)(sal - s_dyn);
+        s_tv[warp][4] = (int)(sga - s_dyn);
+    }
+    __syncthreads();
+    if (warp == 0 && lane < WPB && s_tv[lane][0]) {
+        real* __restrict__ x = s_dyn + s_tv[lane][1];
+        const real* __restrict__ ca = s_dyn + s_tv[lane][2];
+        const real* __restrict__ cal = s_dyn + s_tv[lane][3];
+        const real* __restrict__ cga = s_dyn + s_tv[lane][4];
+        // operands of four steps are read ahead of the dependent chain (mul, sub, mul per step)
+        real prev = x[1];
+        int k = 2;
+        for (; k + 3 <= L; k += 4) {
+            const real b0 = x[k], b1 = x[k + 1], b2 = x[k + 2], b3 = x[k + 3];
+            const real a0 = ca[k], a1 = ca[k + 1], a2 = ca[k + 2], a3 = ca[k + 3];
+            const real l0 = cal[k], l1 = cal[k + 1], l2 = cal[k + 2], l3 = cal[k + 3];
+            const real y0 = (b0 - a0 * prev) * l0;
+            const real y1 = (b1 - a1 * y0) * l1;
+            const real y2 = (b2 - a2 * y1) * l2;
+            const real y3 = (b3 - a3 * y2) * l3;
+            x[k] = y0;
+            x[k + 1] = y1;
+            x[k + 2] = y2;
+            x[k + 3] = y3;
+            prev = y3;
+        }
+        for (; k <= L; ++k) {
+            prev = (x[k] - ca[k] * prev) * cal[k];
+            x[k] = prev;
+        }
+        real next = x[L1];
+        k = L;
+        for (; k - 3 >= 1; k -= 4) {
+            const real b0 = x[k], b1 = x[k - 1], b2 = x[k - 2], b3 = x[k - 3];
+            const real g0 = cga[k], g1 = cga[k - 1], g2 = cga[k - 2], g3 = cga[k - 3];
+            const real y0 = b0 - g0 * next;
+            const real y1 = b1 - g1 * y0;
+            const real y2 = b2 - g2 * y1;
+            const real y3 = b3 - g3 * y2;
+            x[k] = y0;
+            x[k - 1] = y1;
+            x[k - 2] = y2;
+            x[k - 3] = y3;
+            next = y3;
+        }
+        for (; k >= 1; --k) {
+            next = x[k] - cga[k] * next;
+            x[k] = next;
+        }
+    }
+    __syncthreads();
+    for (int k = lane + 1; k <= L; k += 32) {  // TI:2655-2657, 2687-2699
+        if (k < 2) continue;
+        const size_t ic = (size_t)coff + (k - 1), iw = (size_t)woff + (k - 1);
+        const real rw_old = FIRST ? (real)0.0 : s_rwold[k];
+        real ww = FIRST ? (real)0.0 : p.wwAvg[iw];
+        ww = ww + (real)0.5 * ((real)1.0 - epssm) * rw_old;
+        const real d = p.rw_save[iw] - p.rw[iw];
+        const real dk = p.dss[ic];
+        const real r = (rwp[k] + d -
+                        dts * dk * (p.fzm[k - 1] * s_zz[k] + p.fzp[k - 1] * s_zz[k - 1]) *
+                            (p.fzm[k - 1] * s_rhozz[k] + p.fzp[k - 1] * s_rhozz[k - 1]) * p.w[iw]) /
+                           ((real)1.0 + dts * dk) -
+                       d;
+        rwp[k] = r;
+        ww = ww + (real)0.5 * ((real)1.0 + epssm) * r;
+        p.wwAvg[iw] = ww;
+    }
+    __syncwarp();
+    for (int k = lane + 1; k <= L; k += 32) {  // TI:2701-2708
+        const size_t ic = (size_t)coff + (k - 1);
+        p.rw_p[(size_t)woff + (k - 1)] = rwp[k];
+        p.rho_pp[ic] = rs[k] - p.cofrz[k - 1] * (rwp[k + 1] - rwp[k]);
+        p.rtheta_pp[ic] = ts[k] - p.rdzw[k - 1] * (s_coftz[k + 1] * rwp[k + 1] - s_coftz[k] * rwp[k]);
+    }
+    if (FIRST && lane == 0) {  // TI:2617-2622: the levels the loops above never write
+        p.wwAvg[IX2(1, iCell, L1)] = 0.0;
+        p.wwAvg[IX2(L1, iCell, L1)] = 0.0;
+        p.rw_p[IX2(L1, iCell, L1)] = 0.0;
     }
 }
 
@@ -244,22 +382,10 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
         p.ru_p = X(ru_p);
         p.rw_p = X(rw_p); p.rtheta_pp = X(rtheta_pp); p.rtheta_pp_old = X(rtheta_pp_old); p.wwAvg = X(wwAvg); p.rho_pp = X(rho_pp);
         const int ncols = cellEnd - cellStart + 1;
-        if (ncols > 0) {
-            const int wpb = 8;
-            const size_t shm = (size_t)wpb * 6 * (L + 2) * sizeof(real);
-            static bool attr_set = false;
-            if (!attr_set) {
-                cudaFuncSetAttribute(acoustic_cell_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-                attr_set = true;
-            }
-            if (shm > 200 * 1024) return fail_msg("acoustic_cell_kernel: nVertLevels too large for the shared-memory staging");
-            int nblocks = cdiv(ncols, wpb);
-            ktime_begin("acoustic_cell_kernel");
-            acoustic_cell_kernel<<<nblocks, wpb * 32, shm, stream()>>>(p);
-            ktime_end();
-            count_launch();
-            KCHECK("acoustic_cell_kernel");
-        }
+        const size_t shm = (size_t)WPB * AC_NCOL * tma_slot(L + 1) * sizeof(real);
+        if (small_step == 1) WLAUNCH(acoustic_cell_kernel<true>, ncols, shm, p);
+        else WLAUNCH(acoustic_cell_kernel<false>, ncols, shm, p);
+        KCHECK("acoustic_cell_kernel");
     }
     return 0;
 }

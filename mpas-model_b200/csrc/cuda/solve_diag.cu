@@ -27,30 +27,44 @@ struct SdP {
     real *h_edge, *v, *vorticity, *ke, *pv_edge, *pv_vertex, *pv_cell, *gradPVn, *gradPVt, *divergence, *ke_vertex, *ke_edge;
 };
 
+// sd_vertex and the fixed part of sd_edge are written load-first: the index loads of every stencil slot, then every data load, then the sums
+// in the reference's order.  A thread therefore waits for memory twice instead of twice per stencil entry (the edge /
+// vertex loops have run-time trip counts the compiler will not batch).  Slots beyond the run-time count repeat slot 1
+// and are left out of the sums.
 __global__ void __launch_bounds__(256) sd_vertex_kernel(SdP p) {
-    const int L = p.L, vD = p.vD;
+    const int L = p.L;
     FLAT_KC(p.nVerticesLoop, L);
     const int iVertex = p.vertexStart + _c0;
-    real vort = 0.0;
-    real kev[3];
-    for (int i = 1; i <= vD; ++i) {
-        const int iEdge = p.edgesOnVertex[IX2(i, iVertex, vD)];
-        const real dc = p.dcEdge[iEdge - 1];
-        const real s = p.edgesOnVertex_sign[IX2(i, iVertex, vD)] * dc;
-        const real ue = p.u[IX2(k, iEdge, L)];
-        vort = vort + s * ue;
-        if (i <= 3) {
-            const real efac = dc * p.dvEdge[iEdge - 1];
-            kev[i - 1] = efac * (ue * ue);
-        }
+    const int* eov = p.edgesOnVertex + (size_t)(iVertex - 1) * 3;
+    const real* sg = p.edgesOnVertex_sign + (size_t)(iVertex - 1) * 3;
+    int e[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) e[i] = eov[i];
+    real dc[3], dv[3], ue[3], sv[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        dc[i] = p.dcEdge[e[i] - 1];
+        dv[i] = p.dvEdge[e[i] - 1];
+        sv[i] = sg[i];
+        ue[i] = p.u[IX2(k, e[i], L)];
     }
     const real iat = p.invAreaTriangle[iVertex - 1];
+    const real fv = p.fVertex[iVertex - 1];
+    real vort = 0.0;
+    real kev[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const real s = sv[i] * dc[i];
+        vort = vort + s * ue[i];
+        const real efac = dc[i] * dv[i];
+        kev[i] = efac * (ue[i] * ue[i]);
+    }
     vort = vort * iat;
     const size_t iv = IX2(k, iVertex, L);
     p.vorticity[iv] = vort;
     const real r = (real)0.25 * iat;
     p.ke_vertex[iv] = (kev[0] + kev[1] + kev[2]) * r;
-    p.pv_vertex[iv] = (p.fVertex[iVertex - 1] + vort);
+    p.pv_vertex[iv] = (fv + vort);
 }
 
 __global__ void __launch_bounds__(256) sd_cell_kernel(SdP p) {
@@ -88,20 +102,32 @@ __global__ void __launch_bounds__(256) sd_cell_kernel(SdP p) {
     if (p.apvm > (real)0.0) p.pv_cell[ic] = pvc;
 }
 
+template <bool RECON>
 __global__ void __launch_bounds__(256) sd_edge_kernel(SdP p) {
     const int L = p.L, mE2 = p.mE2;
     FLAT_KC(p.nEdgesLoop, L);
     const int iEdge = p.edgeStart + _c0;
     const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    const int v1 = p.verticesOnEdge[IX2(1, iEdge, 2)], v2 = p.verticesOnEdge[IX2(2, iEdge, 2)];
     const size_t ie = IX2(k, iEdge, L);
-    p.h_edge[ie] = (real)0.5 * (p.h[IX2(k, cell1, L)] + p.h[IX2(k, cell2, L)]);
+    const real h1 = p.h[IX2(k, cell1, L)], h2 = p.h[IX2(k, cell2, L)];
     const real ue = p.u[ie];
+    const real pv1 = p.pv_vertex[IX2(k, v1, L)], pv2 = p.pv_vertex[IX2(k, v2, L)];
+    const bool apvm = p.apvm > (real)0.0;
+    real pc1 = 0, pc2 = 0, idv = 0, idc = 0;
+    if (apvm) {
+        pc1 = p.pv_cell[IX2(k, cell1, L)];
+        pc2 = p.pv_cell[IX2(k, cell2, L)];
+        idv = p.invDvEdge[iEdge - 1];
+        idc = p.invDcEdge[iEdge - 1];
+    }
+    p.h_edge[ie] = (real)0.5 * (h1 + h2);
     if (p.ke_edge) {
         const real efac = p.dcEdge[iEdge - 1] * p.dvEdge[iEdge - 1];
         p.ke_edge[ie] = efac * (ue * ue);
     }
     real ve;
-    if (p.reconstruct_v) {
+    if (RECON) {
         ve = 0.0;
         const int n = p.nEdgesOnEdge[iEdge - 1];
         for (int i = 1; i <= n; ++i) {
@@ -110,16 +136,14 @@ __global__ void __launch_bounds__(256) sd_edge_kernel(SdP p) {
         }
         p.v[ie] = ve;
     } else {
-        ve = p.v[ie];
+        ve = apvm ? p.v[ie] : (real)0.0;
     }
-    const int v1 = p.verticesOnEdge[IX2(1, iEdge, 2)], v2 = p.verticesOnEdge[IX2(2, iEdge, 2)];
-    const real pv1 = p.pv_vertex[IX2(k, v1, L)], pv2 = p.pv_vertex[IX2(k, v2, L)];
     real pve = (real)0.5 * (pv1 + pv2);
-    if (p.apvm > (real)0.0) {
+    if (apvm) {
         const real r = p.apvm * p.dt;
-        const real r1 = (real)1.0 * p.invDvEdge[iEdge - 1], r2 = (real)1.0 * p.invDcEdge[iEdge - 1];
+        const real r1 = (real)1.0 * idv, r2 = (real)1.0 * idc;
         const real gt = (pv2 - pv1) * r1;
-        const real gn = (p.pv_cell[IX2(k, cell2, L)] - p.pv_cell[IX2(k, cell1, L)]) * r2;
+        const real gn = (pc2 - pc1) * r2;
         if (p.gradPVt) p.gradPVt[ie] = gt;
         if (p.gradPVn) p.gradPVn[ie] = gn;
         pve = pve - r * (ve * gt + ue * gn);
@@ -151,7 +175,8 @@ extern "C" int mpas_b200_compute_solve_diagnostics_work(MPAS_SOLVEDIAG_ARGS) {
     KCHECK("sd_vertex_kernel");
     KLAUNCH(sd_cell_kernel, (long long)p.nCellsLoop * p.L, 256, p);
     KCHECK("sd_cell_kernel");
-    KLAUNCH(sd_edge_kernel, (long long)p.nEdgesLoop * p.L, 256, p);
+    if (p.reconstruct_v) KLAUNCH(sd_edge_kernel<true>, (long long)p.nEdgesLoop * p.L, 256, p);
+    else KLAUNCH(sd_edge_kernel<false>, (long long)p.nEdgesLoop * p.L, 256, p);
     KCHECK("sd_edge_kernel");
     return 0;
 }
