@@ -32,73 +32,173 @@ struct AsP {
     real *scalar_new, *horiz_flux_arr;
 };
 
-__global__ void __launch_bounds__(256) as_edge_kernel(AsP p) {
-    const int L = p.L, ns = p.ns;
-    FLAT_KC(p.nEdgesLoop, L * ns);
-    const int iEdge = p.edgeStart + _c0;
+// High-order horizontal flux of every scalar through one edge per warp (TI:3330-3387).  Lanes run over the flattened
+// (scalar, level) index of the edge (num_scalars is the fastest dimension of the scalar arrays), two elements per
+// lane; the stencil is staged once per warp as element offsets plus the two coefficient tables (c + c3, c - c3),
+// padded with zero coefficients to a multiple of 5; each element selects its table by the sign of uhAvg at its level.
+// The reference assigns the first of exactly 10 terms and otherwise adds the terms to zero (TI:3339-3375): kept.
+__global__ void __launch_bounds__(WPB * 32) as_edge_kernel(AsP p) {
+    __shared__ unsigned s_o[WPB][20];
+    __shared__ real s_cp[WPB][20], s_cm[WPB][20];
+    const int L = p.L, ns = p.ns, nel = L * ns;
+    WARP_ENTITY(p.edgeStart, p.nEdgesLoop);
+    const int iEdge = ent;
     if (config_apply_lbcs && !(p.bdyMaskEdge[iEdge - 1] < MPAS_NRELAXZONE - 1)) return;
-    const int kk = (k - 1) / ns + 1, q = (k - 1) % ns + 1;
     const int n = p.nAdvCellsForEdge[iEdge - 1];
-    const real s3 = fsign((real)1.0, p.uhAvg[IX2(kk, iEdge, L)]);
-    real s;
-    if (n == 10) {  // TI:3339-3360: first term assigned, not added to zero
-        s = (p.adv_coefs[IX2(1, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(1, iEdge, 15)]) * p.scalar_new[IX3(q, kk, p.advCellsForEdge[IX2(1, iEdge, 15)], ns, L)];
-        for (int j = 2; j <= 10; ++j)
-            s = s + (p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)]) * p.scalar_new[IX3(q, kk, p.advCellsForEdge[IX2(j, iEdge, 15)], ns, L)];
-    } else {
-        s = 0.0;
-        for (int j = 1; j <= n; ++j) {
-            const real scalar_weight = p.adv_coefs[IX2(j, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(j, iEdge, 15)];
-            s = s + scalar_weight * p.scalar_new[IX3(q, kk, p.advCellsForEdge[IX2(j, iEdge, 15)], ns, L)];
-        }
+    const int npad = n <= 5 ? 5 : ((n + 4) / 5 * 5);
+    if (lane < npad) {
+        const bool in = lane < n;
+        const int c = in ? p.advCellsForEdge[IX2(lane + 1, iEdge, 15)] : p.advCellsForEdge[IX2(1, iEdge, 15)];
+        const real a = in ? p.adv_coefs[IX2(lane + 1, iEdge, 15)] : (real)0.0, a3 = in ? p.adv_coefs_3rd[IX2(lane + 1, iEdge, 15)] : (real)0.0;
+        s_o[warp][lane] = (unsigned)(max(c, 1) - 1) * (unsigned)nel;
+        s_cp[warp][lane] = a + a3;
+        s_cm[warp][lane] = a - a3;
     }
-    p.horiz_flux_arr[IX3(q, kk, iEdge, ns, L)] = s;
+    __syncwarp();
+    const bool assign_first = (n == 10);
+    const real* __restrict__ uh = p.uhAvg + (size_t)(iEdge - 1) * L;
+    real* __restrict__ out = p.horiz_flux_arr + (size_t)(iEdge - 1) * nel;
+    for (int ea = lane; ea < nel; ea += 64) {
+        const bool vb = ea + 32 < nel;
+        const int bo = vb ? 32 : 0;
+        const real* tab_a = signbit(uh[ea / ns]) ? s_cm[warp] : s_cp[warp];
+        const real* tab_b = signbit(uh[(ea + bo) / ns]) ? s_cm[warp] : s_cp[warp];
+        const real* __restrict__ sp = p.scalar_new + ea;
+        real s_a = 0.0, s_b = 0.0;
+        for (int j = 0; j < npad; j += 5) {
+            real xa[5], xb[5];
+#pragma unroll
+            for (int t = 0; t < 5; ++t) {
+                const real* __restrict__ q = elem_ptr(sp, s_o[warp][j + t]);
+                xa[t] = q[0];
+                xb[t] = q[bo];
+            }
+#pragma unroll
+            for (int t = 0; t < 5; ++t) {
+                const real ta = tab_a[j + t] * xa[t], tb = tab_b[j + t] * xb[t];
+                if (t == 0 && j == 0 && assign_first) {
+                    s_a = ta;
+                    s_b = tb;
+                } else {
+                    s_a = s_a + ta;
+                    s_b = s_b + tb;
+                }
+            }
+        }
+        out[ea] = s_a;
+        if (vb) out[ea + 32] = s_b;
+    }
 }
 
-__device__ __forceinline__ real as_wdtn_at(const AsP& p, int q, int kk, int iCell) {
-    const int L = p.L, L1 = L + 1, ns = p.ns;
-    if (kk == 1 || kk == L1) return (real)0.0;
-    const real ww = p.wwAvg[IX2(kk, iCell, L1)];
-    if (kk == 2 || kk == L) return ww * (p.fnm[kk - 1] * p.scalar_new[IX3(q, kk, iCell, ns, L)] + p.fnp[kk - 1] * p.scalar_new[IX3(q, kk - 1, iCell, ns, L)]);
-    return flux3(p.scalar_new[IX3(q, kk - 2, iCell, ns, L)], p.scalar_new[IX3(q, kk - 1, iCell, ns, L)], p.scalar_new[IX3(q, kk, iCell, ns, L)],
-                 p.scalar_new[IX3(q, kk + 1, iCell, ns, L)], ww, p.coef_3rd_order);
-}
+enum { ASC_SCAL, ASC_WW, ASC_NTMA };
 
-// Each thread writes scalar_new(q,k,iCell) while its vertical neighbours read it, and the reference
-// evaluates every flux of a column from the pre-update values (TI:3436-3470 fill wdtn for the whole
-// column before TI:3474-3500 updates).  A block therefore owns AS_COLS whole columns: all results go
-// to shared memory first, the block synchronises, then they are stored.
-#define AS_COLS 8
-__global__ void __launch_bounds__(256) as_cell_kernel(AsP p) {
-    extern __shared__ real as_hold[];
-    const int L = p.L, mE = p.mE, ns = p.ns;
-    const int n = L * ns;
-    const int col0 = blockIdx.x * AS_COLS;
-    const int ncols = min(AS_COLS, p.nCellsSolveLoop - col0);
-    for (int t = threadIdx.x; t < ncols * n; t += blockDim.x) {
-        const int c = t / n, r = t - c * n;
-        const int kk = r / ns + 1, q = r - (kk - 1) * ns + 1;
-        const int iCell = p.cellSolveStart + col0 + c;
-        if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) continue;
-        const int ne = p.nEdgesOnCell[iCell - 1];
-        real col = 0.0;
-        for (int i = 1; i <= ne; ++i) {
-            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-            col = col - p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.uhAvg[IX2(kk, iEdge, L)] * p.horiz_flux_arr[IX3(q, kk, iEdge, ns, L)];
-        }
-        col = col * p.invAreaCell[iCell - 1] + p.scalar_tend_save[IX3(q, kk, iCell, ns, L)];
-        const real flo = as_wdtn_at(p, q, kk, iCell), fhi = as_wdtn_at(p, q, kk + 1, iCell);
-        const real rho_old = p.rho_zz_old[IX2(kk, iCell, L)];
-        const real rho_zz_new_inv = (real)1.0 / (p.weight_time_old * rho_old + p.weight_time_new * p.rho_zz_new[IX2(kk, iCell, L)]);
-        as_hold[t] = (p.scalar_old[IX3(q, kk, iCell, ns, L)] * rho_old + p.dt * (col - p.rdnw[kk - 1] * (fhi - flo))) * rho_zz_new_inv;
+// Flux divergence, vertical 3rd-order flux and update of every scalar of one owned cell per warp (TI:3400-3500).
+// The cell's scalar_new block (num_scalars x nVertLevels, contiguous) and its wwAvg column are staged by bulk (TMA)
+// copies, so the update can be stored in place: every read of the pre-update column comes from shared memory (the
+// reference fills wdtn for the whole column before it updates, TI:3436-3500).  The vertical fluxes are evaluated once
+// per (scalar, interface) into shared memory; the edge sum is a direct gather, two elements per lane, the edge list
+// staged as offsets and signs padded to 6 or 8 with zero signs (x - 0*y == x).
+// dynamic shared memory per warp: tma_slot(ns*L) + tma_slot(L+1) + ns*(L+1) reals.
+__global__ void __launch_bounds__(WPB * 32, 4) as_cell_kernel(AsP p) {
+    extern __shared__ __align__(16) real s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar[WPB];
+    __shared__ unsigned s_eL[WPB][8], s_eF[WPB][8];
+    __shared__ real s_sign[WPB][8];
+    const int L = p.L, L1 = L + 1, mE = p.mE, ns = p.ns, nel = L * ns;
+    const int slotS = tma_slot(nel), slotW = tma_slot(L1), per_warp = slotS + slotW + ((ns * L1 + 1) & ~1);  // multiple of 16 bytes
+    WARP_ENTITY(p.cellSolveStart, p.nCellsSolveLoop);
+    const int iCell = ent;
+    if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) return;
+    real* sc = s_dyn + (size_t)warp * per_warp;
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+    const real* g_scal = p.scalar_new + (size_t)(iCell - 1) * nel;
+    const real* g_ww = p.wwAvg + (size_t)(iCell - 1) * L1;
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc);
+        unsigned total = 0;
+        tma_issue_col(s0, g_scal, nel, mbar, total);
+        tma_issue_col(s0 + (unsigned)(slotS * sizeof(real)), g_ww, L1, mbar, total);
+        mbar_arrive_expect_tx(mbar, total);
     }
-    __syncthreads();
-    for (int t = threadIdx.x; t < ncols * n; t += blockDim.x) {
-        const int c = t / n, r = t - c * n;
-        const int kk = r / ns + 1, q = r - (kk - 1) * ns + 1;
-        const int iCell = p.cellSolveStart + col0 + c;
-        if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) continue;
-        p.scalar_new[IX3(q, kk, iCell, ns, L)] = as_hold[t];
+    const real* s_scal = sc + tma_shift(g_scal);          // s_scal[(kk-1)*ns + q-1]
+    const real* s_ww = sc + slotS + tma_shift(g_ww) - 1;  // s_ww[kk]
+    real* wd = sc + slotS + slotW;                        // wd[(kk-1)*ns + q-1], kk = 1..L+1
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const int npad = ne <= 6 ? 6 : 8;
+    if (lane < npad) {
+        const bool in = lane < ne;
+        const int iEdge = p.edgesOnCell[IX2(in ? lane + 1 : 1, iCell, mE)];
+        s_eL[warp][lane] = (unsigned)(iEdge - 1) * (unsigned)L;
+        s_eF[warp][lane] = (unsigned)(iEdge - 1) * (unsigned)nel;
+        s_sign[warp][lane] = in ? p.edgesOnCell_sign[IX2(lane + 1, iCell, mE)] : (real)0.0;
+    }
+    const real invArea = p.invAreaCell[iCell - 1];
+    __syncwarp();
+    mbar_wait(mbar, 0);
+    // ---- vertical flux at every (scalar, interface), TI:3436-3470, branch-free
+    for (int t = lane; t < ns * L1; t += 32) {
+        const int kk = t / ns + 1, q0 = t - (kk - 1) * ns;  // interface kk, scalar q0 (0-based)
+        const int k = min(max(kk, 2), L);
+        const int km2 = max(k - 2, 1), kp1 = min(k + 1, L);
+        const real ww = s_ww[k];
+        const real x_m2 = s_scal[(km2 - 1) * ns + q0], x_m1 = s_scal[(k - 2) * ns + q0], x_c = s_scal[(k - 1) * ns + q0], x_p1 = s_scal[(kp1 - 1) * ns + q0];
+        const real f3 = flux3(x_m2, x_m1, x_c, x_p1, ww, p.coef_3rd_order);
+        const real f2 = ww * (p.fnm[k - 1] * x_c + p.fnp[k - 1] * x_m1);
+        wd[t] = (kk == 1 || kk == L1) ? (real)0.0 : ((k == 2 || k == L) ? f2 : f3);
+    }
+    __syncwarp();
+    // ---- flux divergence and update, TI:3400-3432, 3474-3500
+    const real* __restrict__ rho_old_col = p.rho_zz_old + (size_t)(iCell - 1) * L;
+    const real* __restrict__ rho_new_col = p.rho_zz_new + (size_t)(iCell - 1) * L;
+    const real* __restrict__ tend_col = p.scalar_tend_save + (size_t)(iCell - 1) * nel;
+    const real* __restrict__ old_col = p.scalar_old + (size_t)(iCell - 1) * nel;
+    real* __restrict__ new_col = p.scalar_new + (size_t)(iCell - 1) * nel;
+    for (int ea = lane; ea < nel; ea += 64) {
+        const bool vb = ea + 32 < nel;
+        const int bo = vb ? 32 : 0;
+        const int ka = ea / ns, kb = (ea + bo) / ns;  // 0-based levels
+        real col_a = 0.0, col_b = 0.0;
+        {
+            const real* __restrict__ hf = p.horiz_flux_arr + ea;
+            const real* __restrict__ uha = p.uhAvg + ka;
+            const real* __restrict__ uhb = p.uhAvg + kb;
+            real fa[8], fb[8], ua[8], ub[8];
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const real* __restrict__ q = elem_ptr(hf, s_eF[warp][i]);
+                fa[i] = q[0];
+                fb[i] = q[bo];
+                ua[i] = *elem_ptr(uha, s_eL[warp][i]);
+                ub[i] = *elem_ptr(uhb, s_eL[warp][i]);
+            }
+#pragma unroll
+            for (int i = 0; i < 6; ++i) {
+                const real s = s_sign[warp][i];
+                col_a = col_a - s * ua[i] * fa[i];
+                col_b = col_b - s * ub[i] * fb[i];
+            }
+            if (npad > 6) {
+#pragma unroll
+                for (int i = 6; i < 8; ++i) {
+                    const real* __restrict__ q = elem_ptr(hf, s_eF[warp][i]);
+                    const real s = s_sign[warp][i];
+                    col_a = col_a - s * *elem_ptr(uha, s_eL[warp][i]) * q[0];
+                    col_b = col_b - s * *elem_ptr(uhb, s_eL[warp][i]) * q[bo];
+                }
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const int e = ea + 32 * h, k0 = h ? kb : ka;
+            real col = h ? col_b : col_a;
+            col = col * invArea + tend_col[e];
+            const real flo = wd[e], fhi = wd[e + ns];
+            const real rho_old = rho_old_col[k0];
+            const real rho_zz_new_inv = (real)1.0 / (p.weight_time_old * rho_old + p.weight_time_new * rho_new_col[k0]);
+            new_col[e] = (old_col[e] * rho_old + p.dt * (col - p.rdnw[k0] * (fhi - flo))) * rho_zz_new_inv;
+        }
     }
 }
 
@@ -370,15 +470,12 @@ extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
     p.adv_coefs = X(adv_coefs); p.adv_coefs_3rd = X(adv_coefs_3rd); p.edgesOnCell = X(edgesOnCell); p.nEdgesOnCell = X(nEdgesOnCell);
     p.bdyMaskCell = X(bdyMaskCell); p.bdyMaskEdge = X(bdyMaskEdge); p.nAdvCellsForEdge = X(nAdvCellsForEdge); p.advCellsForEdge = X(advCellsForEdge);
     p.scalar_tend_save = X(scalar_tend_save); p.scalar_new = X(scalar_new); p.horiz_flux_arr = X(horiz_flux_arr);
-    KLAUNCH(as_edge_kernel, (long long)p.nEdgesLoop * p.L * p.ns, 256, p);
+    WLAUNCH(as_edge_kernel, p.nEdgesLoop, 0, p);
     KCHECK("as_edge_kernel");
     if (p.nCellsSolveLoop > 0) {
-        const size_t shm = (size_t)AS_COLS * p.L * p.ns * sizeof(real);
-        if (shm > 48 * 1024) return fail_msg("mpas_b200_advance_scalars_work: nVertLevels*num_scalars too large for the column staging");
-        ktime_begin("as_cell_kernel");
-        as_cell_kernel<<<cdiv(p.nCellsSolveLoop, AS_COLS), 256, shm, stream()>>>(p);
-        ktime_end();
-        count_launch();
+        if (p.mE > 8) return fail_msg("mpas_b200_advance_scalars_work: maxEdges > 8 not supported");
+        const size_t shm = (size_t)WPB * (tma_slot(p.L * p.ns) + tma_slot(p.L + 1) + ((p.ns * (p.L + 1) + 1) & ~1)) * sizeof(real);
+        WLAUNCH(as_cell_kernel, p.nCellsSolveLoop, shm, p);
         KCHECK("as_cell_kernel");
     }
     return 0;
