@@ -297,50 +297,100 @@ __global__ void __launch_bounds__(256) mono_bounds_kernel(MonoP p) {
     p.s_min[ic] = smin;
 }
 
-__global__ void __launch_bounds__(256) mono_edge_flux_kernel(MonoP p) {
+// High-order and upwind horizontal fluxes of the current scalar through one edge per warp (TI:3916-3961, 4007-4022).
+// Two levels per lane; for the usual 10-cell stencil the offsets and the two pre-combined coefficient tables are staged
+// once per warp and every level selects its table by uhAvg > 0 (TI:3925-3945); other stencil sizes take the reference's
+// general form (TI:3947-3957) in a plain loop.
+__global__ void __launch_bounds__(WPB * 32) mono_edge_flux_kernel(MonoP p) {
+    __shared__ unsigned s_o[WPB][10];
+    __shared__ real s_cp[WPB][10], s_cm[WPB][10];
     const int L = p.L;
-    FLAT_KC(p.nEdgesLoop, L);
-    const int iEdge = p.edgeStart + _c0;
+    WARP_ENTITY(p.edgeStart, p.nEdgesLoop);
+    const int iEdge = ent;
     const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
-    const size_t ie = IX2(k, iEdge, L);
-    const real uh = p.uhAvg[ie];
-    real fa;
-    if (cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve) {
-        const int n = p.nAdvCellsForEdge[iEdge - 1];
-        if (n == 10) {  // TI:3925-3945: weights pre-combined, merge(1,2,uhAvg>0)
-            const bool pos = uh > 0;
-            real s;
-            {
-                const real c = p.adv_coefs[IX2(1, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(1, iEdge, 15)];
-                s = (pos ? (c + c3) : (c - c3)) * p.scalar_new[IX2(k, p.advCellsForEdge[IX2(1, iEdge, 15)], L)];
+    const bool owned = (cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve);
+    const int n = owned ? p.nAdvCellsForEdge[iEdge - 1] : 0;
+    if (n == 10 && lane < 10) {
+        const real c = p.adv_coefs[IX2(lane + 1, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(lane + 1, iEdge, 15)];
+        s_o[warp][lane] = (unsigned)(p.advCellsForEdge[IX2(lane + 1, iEdge, 15)] - 1) * (unsigned)L;
+        s_cp[warp][lane] = c + c3;
+        s_cm[warp][lane] = c - c3;
+    }
+    __syncwarp();
+    const real dvdt = p.dvEdge[iEdge - 1] * p.dt;
+    const int bm = p.bdyMaskEdge[iEdge - 1];
+    const bool zero_corr = (config_apply_lbcs && (bm == MPAS_NRELAXZONE)) || (bm == MPAS_NRELAXZONE - 1);
+    const unsigned eoff = (unsigned)(iEdge - 1) * (unsigned)L, c1off = (unsigned)(cell1 - 1) * (unsigned)L, c2off = (unsigned)(cell2 - 1) * (unsigned)L;
+    for (int ka = lane; ka < L; ka += 64) {
+        const bool vb = ka + 32 < L;
+        const int bo = vb ? 32 : 0;
+        const real* __restrict__ uhp = elem_ptr(p.uhAvg + ka, eoff);
+        const real uh_a = uhp[0], uh_b = uhp[bo];
+        const real* __restrict__ o1 = elem_ptr(p.scalar_old + ka, c1off);
+        const real* __restrict__ o2 = elem_ptr(p.scalar_old + ka, c2off);
+        const real so1_a = o1[0], so1_b = o1[bo], so2_a = o2[0], so2_b = o2[bo];
+        real fa_a = 0.0, fa_b = 0.0;
+        if (n == 10) {
+            const real* tab_a = (uh_a > 0) ? s_cp[warp] : s_cm[warp];
+            const real* tab_b = (uh_b > 0) ? s_cp[warp] : s_cm[warp];
+            const real* __restrict__ sp = p.scalar_new + ka;
+            real s_a = 0.0, s_b = 0.0;
+#pragma unroll
+            for (int j = 0; j < 10; j += 5) {
+                real xa[5], xb[5];
+#pragma unroll
+                for (int t = 0; t < 5; ++t) {
+                    const real* __restrict__ q = elem_ptr(sp, s_o[warp][j + t]);
+                    xa[t] = q[0];
+                    xb[t] = q[bo];
+                }
+#pragma unroll
+                for (int t = 0; t < 5; ++t) {
+                    const real ta = tab_a[j + t] * xa[t], tb = tab_b[j + t] * xb[t];
+                    if (j == 0 && t == 0) {  // the first term is assigned (TI:3928), not added to zero
+                        s_a = ta;
+                        s_b = tb;
+                    } else {
+                        s_a = s_a + ta;
+                        s_b = s_b + tb;
+                    }
+                }
             }
-            for (int jj = 2; jj <= 10; ++jj) {
-                const real c = p.adv_coefs[IX2(jj, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(jj, iEdge, 15)];
-                s = s + (pos ? (c + c3) : (c - c3)) * p.scalar_new[IX2(k, p.advCellsForEdge[IX2(jj, iEdge, 15)], L)];
-            }
-            fa = uh * s;
-        } else {
-            fa = 0.0;
-            const real s3 = fsign((real)1.0, uh);
-            for (int i = 1; i <= n; ++i) {
-                const real scalar_weight = uh * (p.adv_coefs[IX2(i, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(i, iEdge, 15)]);
-                fa = fa + scalar_weight * p.scalar_new[IX2(k, p.advCellsForEdge[IX2(i, iEdge, 15)], L)];
+            fa_a = uh_a * s_a;
+            fa_b = uh_b * s_b;
+        } else if (n > 0) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int k = ka + 1 + (h ? bo : 0);
+                const real uh = h ? uh_b : uh_a;
+                const real s3 = fsign((real)1.0, uh);
+                real fa = 0.0;
+                for (int i = 1; i <= n; ++i) {
+                    const real scalar_weight = uh * (p.adv_coefs[IX2(i, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(i, iEdge, 15)]);
+                    fa = fa + scalar_weight * p.scalar_new[IX2(k, p.advCellsForEdge[IX2(i, iEdge, 15)], L)];
+                }
+                if (h) fa_b = fa;
+                else fa_a = fa;
             }
         }
-    } else {
-        fa = 0.0;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const real uh = h ? uh_b : uh_a;
+            real fa = h ? fa_b : fa_a;
+            // TI:4007-4022 (all edges)
+            const real fup = dvdt * (fmax((real)0.0, uh) * (h ? so1_b : so1_a) + fmin((real)0.0, uh) * (h ? so2_b : so2_a));
+            real ft = p.dt * fa - fup;
+            if (zero_corr) {
+                ft = 0.;
+                fa = fup;
+            }
+            const size_t ie = (size_t)eoff + ka + 32 * h;
+            p.flux_arr[ie] = fa;
+            p.flux_upwind_tmp[ie] = fup;
+            p.flux_tmp[ie] = ft;
+        }
     }
-    // TI:4007-4022 (all edges)
-    const real fup = p.dvEdge[iEdge - 1] * p.dt * (fmax((real)0.0, uh) * p.scalar_old[IX2(k, cell1, L)] + fmin((real)0.0, uh) * p.scalar_old[IX2(k, cell2, L)]);
-    real ft = p.dt * fa - fup;
-    const int bm = p.bdyMaskEdge[iEdge - 1];
-    if ((config_apply_lbcs && (bm == MPAS_NRELAXZONE)) || (bm == MPAS_NRELAXZONE - 1)) {
-        ft = 0.;
-        fa = fup;
-    }
-    p.flux_arr[ie] = fa;
-    p.flux_upwind_tmp[ie] = fup;
-    p.flux_tmp[ie] = ft;
 }
 
 __device__ __forceinline__ real mono_upwind_at(const MonoP& p, int kk, int iCell) {  // flux_upwind_arr(kk), kk in 2..L
@@ -514,7 +564,7 @@ extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
         KCHECK("mono_copy_kernel");
         KLAUNCH(mono_bounds_kernel, (long long)p.nCellsSolveLoop * (L + 1), 256, p);
         KCHECK("mono_bounds_kernel");
-        KLAUNCH(mono_edge_flux_kernel, (long long)p.nEdgesLoop * L, 256, p);
+        WLAUNCH(mono_edge_flux_kernel, p.nEdgesLoop, 0, p);
         KCHECK("mono_edge_flux_kernel");
         KLAUNCH(mono_limiter_kernel, (long long)p.nCellsSolveLoop * L, 256, p);
         KCHECK("mono_limiter_kernel");
