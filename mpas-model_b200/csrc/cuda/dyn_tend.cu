@@ -47,24 +47,53 @@ struct DtP {
     real *tend_rtheta_adv, *rthdynten, *delsq_theta, *delsq_w, *delsq_divergence, *delsq_u, *delsq_vorticity, *dpdz;
 };
 
-__global__ void __launch_bounds__(256) dt_cell_pre_kernel(DtP p) {
+// Load-first flat kernels: the index loads of all stencil slots, then the data loads (in batches that fit the register
+// budget), then the sums in the reference's order.  Slots beyond nEdgesOnCell repeat slot 1 and are left out of the sums.
+template <int NE, bool SMAG>
+__global__ void __launch_bounds__(256, SMAG ? 3 : 4) dt_cell_pre_kernel(DtP p) {
     const int L = p.L, L1 = L + 1, mE = p.mE;
     FLAT_KC(p.nCellsLoop, L);
     const int iCell = p.cellStart + _c0;
     const size_t ic = IX2(k, iCell, L);
     const int ne = p.nEdgesOnCell[iCell - 1];
+    const int* eoc = p.edgesOnCell + (size_t)(iCell - 1) * mE;
+    const real* sg = p.edgesOnCell_sign + (size_t)(iCell - 1) * mE;
+    int e[NE];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) e[i] = eoc[i < ne ? i : 0];
     real hdiv = 0.0, d_diag = 0.0, d_off_diag = 0.0;
-    const bool smag = (p.rk_step == 1 && p.mixing == 1);
-    for (int i = 1; i <= ne; ++i) {
-        const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-        const size_t ie = IX2(k, iEdge, L);
-        const real edge_sign = p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.dvEdge[iEdge - 1];
-        hdiv = hdiv + edge_sign * p.ru[ie];
-        if (smag) {
-            const real a = p.defc_a[IX2(i, iCell, mE)], b = p.defc_b[IX2(i, iCell, mE)];
-            const real ue = p.u[ie], ve = p.v[ie];
-            d_diag = d_diag + a * ue - b * ve;
-            d_off_diag = d_off_diag + b * ue + a * ve;
+    {
+        real dv[NE], rue[NE], sv[NE];
+#pragma unroll
+        for (int i = 0; i < NE; ++i) {
+            dv[i] = p.dvEdge[e[i] - 1];
+            rue[i] = p.ru[IX2(k, e[i], L)];
+            sv[i] = sg[i < ne ? i : 0];
+        }
+#pragma unroll
+        for (int i = 0; i < NE; ++i) {
+            const real edge_sign = sv[i] * dv[i];
+            if (i < ne) hdiv = hdiv + edge_sign * rue[i];
+        }
+    }
+    if (SMAG) {  // TI:4677-4693
+        const real* da = p.defc_a + (size_t)(iCell - 1) * mE;
+        const real* db = p.defc_b + (size_t)(iCell - 1) * mE;
+        real a[NE], b[NE], ue[NE], ve[NE];
+#pragma unroll
+        for (int i = 0; i < NE; ++i) {
+            const int j = i < ne ? i : 0;
+            a[i] = da[j];
+            b[i] = db[j];
+            ue[i] = p.u[IX2(k, e[i], L)];
+            ve[i] = p.v[IX2(k, e[i], L)];
+        }
+#pragma unroll
+        for (int i = 0; i < NE; ++i) {
+            if (i < ne) {
+                d_diag = d_diag + a[i] * ue[i] - b[i] * ve[i];
+                d_off_diag = d_off_diag + b[i] * ue[i] + a[i] * ve[i];
+            }
         }
     }
     hdiv = hdiv * p.invAreaCell[iCell - 1];
@@ -776,7 +805,18 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     if (!p.mix_full && (p.v_mom_eddy_visc2 > 0 || p.v_theta_eddy_visc2 > 0) && (!u_init || !v_init || !angleEdge || !t_init))
         return fail_msg("mpas_b200_compute_dyn_tend_work: config_mix_full=false needs u_init, v_init, angleEdge, t_init");
     const int L = p.L;
-    KLAUNCH(dt_cell_pre_kernel, (long long)p.nCellsLoop * L, 256, p);
+    if (maxEdges > 8) return fail_msg("mpas_b200_compute_dyn_tend_work: maxEdges > 8 or maxEdges2 > 16 not supported");
+    {
+        const bool smag = (rk_step == 1 && config_horiz_mixing == 1);
+        const long long nt = (long long)p.nCellsLoop * L;
+        if (maxEdges <= 6) {
+            if (smag) KLAUNCH((dt_cell_pre_kernel<6, true>), nt, 256, p);
+            else KLAUNCH((dt_cell_pre_kernel<6, false>), nt, 256, p);
+        } else {
+            if (smag) KLAUNCH((dt_cell_pre_kernel<8, true>), nt, 256, p);
+            else KLAUNCH((dt_cell_pre_kernel<8, false>), nt, 256, p);
+        }
+    }
     KCHECK("dt_cell_pre_kernel");
     if (rk_step == 1) {
         KLAUNCH(dt_edge_mix_kernel, (long long)p.nEdgesLoop * L, 256, p);
