@@ -446,25 +446,42 @@ int dycore_step(Dycore& m) {
     // (both allocate, which a capture forbids).
     const bool graphable = m.use_graph && !m.timing && m.blocks.size() == 1 && m.steps_done >= 2;
     if (graphable) {
-        cudaGraphExec_t& ge = m.graph_exec[m.parity];
-        if (!ge) {
+        auto capture = [&](int par) -> int {
             cudaGraph_t g;
             const long long before = launches();
             const long xbefore = m.nExchanges;
             cudaError_t e = cudaStreamBeginCapture(stream(), cudaStreamCaptureModeThreadLocal);
             if (e != cudaSuccess) return fail("cudaStreamBeginCapture", e);
-            rc = srk3_body(m);
+            const int r = srk3_body(m);
             e = cudaStreamEndCapture(stream(), &g);
-            m.graph_nodes[m.parity] = launches() - before;  // kernels / copies recorded, not yet executed
-            m.graph_exchanges[m.parity] = m.nExchanges - xbefore;
-            count_launch(-(int)m.graph_nodes[m.parity]);
+            m.graph_nodes[par] = launches() - before;  // kernels / copies recorded, not yet executed
+            m.graph_exchanges[par] = m.nExchanges - xbefore;
+            count_launch(-(int)m.graph_nodes[par]);
             m.nExchanges = xbefore;
-            if (rc) return rc;
+            if (r) return r;
             if (e != cudaSuccess) return fail("cudaStreamEndCapture", e);
-            e = cudaGraphInstantiate(&ge, g, 0);
+            e = cudaGraphInstantiate(&m.graph_exec[par], g, 0);
             cudaGraphDestroy(g);
             if (e != cudaSuccess) return fail("cudaGraphInstantiate", e);
+            return 0;
+        };
+        auto swap_all = [&]() {
+            for (auto& b : m.blocks)
+                for (const char* n : {"u", "w", "theta_m", "rho_zz", "scalars"}) b.swap_levels(n);
+            m.parity ^= 1;
+        };
+        if (!m.graph_exec[m.parity]) {
+            // both graphs are built on the first graphable step (the third): capture records without executing, so the
+            // other parity is captured with the time levels swapped and swapped back
+            if ((rc = capture(m.parity))) return rc;
+            if (!m.graph_exec[m.parity ^ 1]) {
+                swap_all();
+                rc = capture(m.parity);
+                swap_all();
+                if (rc) return rc;
+            }
         }
+        cudaGraphExec_t& ge = m.graph_exec[m.parity];
         cudaError_t e = cudaGraphLaunch(ge, stream());
         if (e != cudaSuccess) return fail("cudaGraphLaunch", e);
         count_launch((int)m.graph_nodes[m.parity]);
