@@ -342,7 +342,9 @@ __device__ __noinline__ real u_vmix_term(const DtP& p, int k, int iEdge, int cel
 }
 
 // Shared-memory column slots of one warp of dt_edge_kernel (tma_slot(L + 1) reals each), filled by tma_stage_col.
-enum { EC_RW1, EC_RW2, EC_U, EC_PV, EC_RHO, EC_TE, EC_KE1, EC_KE2, EC_HD1, EC_HD2, EC_WZ, EC_NCOL_RK23, EC_DD1 = EC_NCOL_RK23, EC_DD2, EC_DV1, EC_DV2, EC_NCOL_RK1 };
+// (rk 1: the delsq_vorticity columns reuse the rw slots in a second copy phase once the vertical flux is done, which keeps
+// the block at 13 slots = 4 blocks per SM)
+enum { EC_RW1, EC_RW2, EC_U, EC_PV, EC_RHO, EC_TE, EC_KE1, EC_KE2, EC_HD1, EC_HD2, EC_WZ, EC_NCOL_RK23, EC_DD1 = EC_NCOL_RK23, EC_DD2, EC_NCOL_RK1, EC_DV1 = EC_RW1, EC_DV2 = EC_RW2 };
 
 // One owned edge per warp.  Every column the edge reads exactly once per level (its own u, pv_edge, rho_edge,
 // tend_u_euler; rw, ke, h_divergence [, delsq_divergence] of its two cells [, delsq_vorticity of its two vertices]) is
@@ -409,8 +411,6 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) 
         if (del4) {
             tma_issue_col(s0 + EC_DD1 * cs, g_dd1, L, mbar, total);
             tma_issue_col(s0 + EC_DD2 * cs, g_dd2, L, mbar, total);
-            tma_issue_col(s0 + EC_DV1 * cs, g_dv1, L, mbar, total);
-            tma_issue_col(s0 + EC_DV2 * cs, g_dv2, L, mbar, total);
         }
         mbar_arrive_expect_tx(mbar, total);
     }
@@ -453,6 +453,15 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) 
         wz[kk] = f;
     }
     __syncwarp();
+    if (del4 && lane == 0) {  // second copy phase into the rw slots (their last read is above)
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
+        unsigned total = 0;
+        tma_issue_col(s0 + EC_DV1 * cs, g_dv1, L, mbar, total);
+        tma_issue_col(s0 + EC_DV2 * cs, g_dv2, L, mbar, total);
+        mbar_arrive_expect_tx(mbar, total);
+    }
+    bool dv_ready = !del4;
     for (int ka = lane; ka < L; ka += 64) {  // 0-based levels ka and ka + 32
         const bool vb = ka + 32 < L;
         const int bo = vb ? 32 : 0;  // lanes without a second level recompute the first one (no predicated loads)
@@ -483,6 +492,10 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) 
         }
         q_a = (real)0.5 * q_a;
         q_b = (real)0.5 * q_b;
+        if (!dv_ready) {
+            mbar_wait(mbar, 1);
+            dv_ready = true;
+        }
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
             if (h == 1 && !vb) break;
