@@ -69,79 +69,128 @@ __global__ void cofrz_kernel(VicP p) {  // TI:2070-2072
     if (k <= p.L) p.cofrz[k - 1] = p.dtseps * p.rdzw[k - 1];
 }
 
-// one warp per column; lanes along k for the coefficient arrays, lane 0 runs the recurrence
-// alpha(k) = 1/(b(k) - a(k)*gamma(k-1)), gamma(k) = c(k)*alpha(k) (TI:2124-2127) in the reference's order.
-// shared memory per warp: b_tri[L+2] c_tri[L+2] a[L+2] al[L+2] ga[L+2]
-__global__ void __launch_bounds__(256) vert_imp_kernel(VicP p) {
+// One warp per column, lanes along k (two levels per lane and pass so that the 9 input columns of a 64-level chunk arrive
+// in one round trip); the coefficients stay in shared memory between the passes.  The recurrence
+// alpha(k) = 1/(b(k) - a(k)*gamma(k-1)), gamma(k) = c(k)*alpha(k) (TI:2124-2127) is serial in k, so one LANE runs it for one
+// column: the block's WPB columns are swept together by the first WPB lanes of warp 0 between two block barriers, in the
+// reference's order.  shared memory per warp: VI_NCOL columns of L + 2 reals.
+enum { VI_ZZ, VI_P, VI_T, VI_CQW, VI_WT, VI_WR, VI_TZ, VI_C, VI_NCOL, VI_WZ = VI_CQW, VI_A = VI_P, VI_B = VI_T };
+__global__ void __launch_bounds__(WPB * 32) vert_imp_kernel(VicP p) {
     extern __shared__ real smem[];
-    const int L = p.L, L1 = L + 1;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    real* b_tri = smem + (size_t)warp * 5 * (L + 2);
-    real* c_tri = b_tri + (L + 2);
-    real* sa = c_tri + (L + 2);
-    real* sal = sa + (L + 2);
-    real* sga = sal + (L + 2);
+    const int L = p.L, L1 = L + 1, LS = L + 2;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    real* sw = smem + (size_t)warp * VI_NCOL * LS;
+    real *s_zz = sw + VI_ZZ * LS, *s_p = sw + VI_P * LS, *s_t = sw + VI_T * LS, *s_cqw = sw + VI_CQW * LS, *s_wt = sw + VI_WT * LS;
+    real *s_wr = sw + VI_WR * LS, *s_tz = sw + VI_TZ * LS, *s_c = sw + VI_C * LS;
     const real dtseps = p.dtseps, rcv = p.rcv, c2 = p.c2;
-    for (int iCell = p.cellSolveStart + blockIdx.x * wpb + warp; iCell < p.cellSolveStart + p.nCellsLoop; iCell += gridDim.x * wpb) {
-        // pass 1: cofwr, cofwz, coftz, cofwt
+    const int iCell = p.cellSolveStart + blockIdx.x * WPB + warp;
+    const bool exists = iCell < p.cellSolveStart + p.nCellsLoop;
+    if (exists) {
+        const size_t c0 = IX2(1, iCell, L);
+        // pass 1: inputs of levels ka, ka + 32; cofwt (TI:2100-2107)
+        for (int k0 = 0; k0 < L; k0 += 64) {
+            const int ka = k0 + lane + 1, kb = ka + 32;
+            const bool va = ka <= L, vb = kb <= L;
+            const size_t ia = c0 + ((va ? ka : L) - 1), ib = c0 + ((vb ? kb : L) - 1);
+            const real zz_a = p.zz[ia], zz_b = p.zz[ib], p_a = p.p_[ia], p_b = p.p_[ib], t_a = p.t[ia], t_b = p.t[ib];
+            const real cq_a = p.cqw[ia], cq_b = p.cqw[ib], q_a = p.qtot[ia], q_b = p.qtot[ib], rb_a = p.rb[ia], rb_b = p.rb[ib];
+            const real rtb_a = p.rtb[ia], rtb_b = p.rtb[ib], rt_a = p.rt[ia], rt_b = p.rt[ib], pb_a = p.pb[ia], pb_b = p.pb[ib];
+            if (va) {
+                const real wt = (real).5 * dtseps * rcv * zz_a * MPAS_GRAVITY * rb_a / ((real)1. + q_a) * p_a / ((rtb_a + rt_a) * pb_a);
+                p.cofwt[ia] = wt;
+                s_wt[ka] = wt; s_zz[ka] = zz_a; s_p[ka] = p_a; s_t[ka] = t_a; s_cqw[ka] = cq_a;
+            }
+            if (vb) {
+                const real wt = (real).5 * dtseps * rcv * zz_b * MPAS_GRAVITY * rb_b / ((real)1. + q_b) * p_b / ((rtb_b + rt_b) * pb_b);
+                p.cofwt[ib] = wt;
+                s_wt[kb] = wt; s_zz[kb] = zz_b; s_p[kb] = p_b; s_t[kb] = t_b; s_cqw[kb] = cq_b;
+            }
+        }
+        __syncwarp();
+        // pass 2: cofwr, cofwz, coftz (TI:2083-2098)
         for (int k = lane + 1; k <= L1; k += 32) {
             if (k == 1 || k == L1) {
                 p.coftz[IX2(k, iCell, L1)] = 0.0;
-            }
-            if (k >= 2 && k <= L) {
-                const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L);
+                s_tz[k] = 0.0;
+            } else {
+                const size_t ic = c0 + (k - 1);
                 const real fm = p.fzm[k - 1], fp = p.fzp[k - 1];
-                const real zzk = p.zz[ic], zzkm = p.zz[icm];
-                p.cofwr[ic] = (real).5 * dtseps * MPAS_GRAVITY * (fm * zzk + fp * zzkm);
-                p.cofwz[ic] = dtseps * c2 * (fm * zzk + fp * zzkm) * p.rdzu[k - 1] * p.cqw[ic] * (fm * p.p_[ic] + fp * p.p_[icm]);
-                p.coftz[IX2(k, iCell, L1)] = dtseps * (fm * p.t[ic] + fp * p.t[icm]);
-            }
-            if (k <= L) {
-                const size_t ic = IX2(k, iCell, L);
-                const real qtotal = p.qtot[ic];
-                p.cofwt[ic] = (real).5 * dtseps * rcv * p.zz[ic] * MPAS_GRAVITY * p.rb[ic] / ((real)1. + qtotal) * p.p_[ic] / ((p.rtb[ic] + p.rt[ic]) * p.pb[ic]);
+                const real zzk = s_zz[k], zzkm = s_zz[k - 1];
+                const real wr = (real).5 * dtseps * MPAS_GRAVITY * (fm * zzk + fp * zzkm);
+                const real wz = dtseps * c2 * (fm * zzk + fp * zzkm) * p.rdzu[k - 1] * s_cqw[k] * (fm * s_p[k] + fp * s_p[k - 1]);
+                const real tz = dtseps * (fm * s_t[k] + fp * s_t[k - 1]);
+                p.cofwr[ic] = wr;
+                p.cofwz[ic] = wz;
+                p.coftz[IX2(k, iCell, L1)] = tz;
+                s_wr[k] = wr;
+                s_tz[k] = tz;
+                s_cqw[k] = wz;  // VI_WZ: only this lane reads s_cqw[k]
             }
         }
-        __syncwarp();  // the pass below re-reads this warp's own global writes (same thread block: visible after the barrier)
-        __threadfence_block();
+        __syncwarp();
+        // pass 3: a, b, c of the tridiagonal system (TI:2109-2122); a and b replace the p and t columns (no longer read)
         for (int k = lane + 1; k <= L; k += 32) {
+            real a, b, c;
             if (k == 1) {
-                sa[1] = 0.;
-                b_tri[1] = 1.;
-                c_tri[1] = 0.;
+                a = 0.;
+                b = 1.;
+                c = 0.;
             } else {
-                const size_t ic = IX2(k, iCell, L), icm = IX2(k - 1, iCell, L);
-                const real cofwz = p.cofwz[ic], cofwr = p.cofwr[ic], cofwt = p.cofwt[ic], cofwtm = p.cofwt[icm];
-                const real coftz_k = p.coftz[IX2(k, iCell, L1)], coftz_km = p.coftz[IX2(k - 1, iCell, L1)], coftz_kp = p.coftz[IX2(k + 1, iCell, L1)];
-                const real zzk = p.zz[ic], zzkm = p.zz[icm];
+                const real cofwz = s_cqw[k], cofwr = s_wr[k], cofwt = s_wt[k], cofwtm = s_wt[k - 1];
+                const real coftz_k = s_tz[k], coftz_km = s_tz[k - 1], coftz_kp = s_tz[k + 1];
+                const real zzk = s_zz[k], zzkm = s_zz[k - 1];
                 const real rdzw_k = p.rdzw[k - 1], rdzw_km = p.rdzw[k - 2];
                 const real cofrz_k = dtseps * rdzw_k, cofrz_km = dtseps * rdzw_km;
-                sa[k] = -cofwz * coftz_km * rdzw_km * zzkm + cofwr * cofrz_km - cofwtm * coftz_km * rdzw_km;
-                b_tri[k] = (real)1. + cofwz * (coftz_k * rdzw_k * zzk + coftz_k * rdzw_km * zzkm) - coftz_k * (cofwt * rdzw_k - cofwtm * rdzw_km) +
-                           cofwr * (cofrz_k - cofrz_km);
-                c_tri[k] = -cofwz * coftz_kp * rdzw_k * zzk - cofwr * cofrz_k + cofwt * coftz_kp * rdzw_k;
+                a = -cofwz * coftz_km * rdzw_km * zzkm + cofwr * cofrz_km - cofwtm * coftz_km * rdzw_km;
+                b = (real)1. + cofwz * (coftz_k * rdzw_k * zzk + coftz_k * rdzw_km * zzkm) - coftz_k * (cofwt * rdzw_k - cofwtm * rdzw_km) +
+                    cofwr * (cofrz_k - cofrz_km);
+                c = -cofwz * coftz_kp * rdzw_k * zzk - cofwr * cofrz_k + cofwt * coftz_kp * rdzw_k;
             }
+            s_p[k] = a;  // VI_A
+            s_t[k] = b;  // VI_B -> alpha after the sweep
+            s_c[k] = c;  // -> gamma after the sweep
         }
-        __syncwarp();
-        if (lane == 0) {
-            sga[1] = 0.;
-            sal[1] = 0.;
-            real g = 0.;
-            for (int k = 2; k <= L; ++k) {
-                const real al = (real)1. / (b_tri[k] - sa[k] * g);
-                g = c_tri[k] * al;
-                sal[k] = al;
-                sga[k] = g;
-            }
+    }
+    __syncthreads();
+    if (warp == 0 && lane < WPB && p.cellSolveStart + blockIdx.x * WPB + lane < p.cellSolveStart + p.nCellsLoop) {
+        real* __restrict__ xs = smem + (size_t)lane * VI_NCOL * LS;
+        const real* __restrict__ xa = xs + VI_A * LS;
+        real* __restrict__ xb = xs + VI_B * LS;
+        real* __restrict__ xc = xs + VI_C * LS;
+        xb[1] = 0.;
+        xc[1] = 0.;
+        real g = 0.;
+        int k = 2;
+        for (; k + 3 <= L; k += 4) {  // operands of four steps are read ahead of the dependent chain
+            const real a0 = xa[k], a1 = xa[k + 1], a2 = xa[k + 2], a3 = xa[k + 3];
+            const real b0 = xb[k], b1 = xb[k + 1], b2 = xb[k + 2], b3 = xb[k + 3];
+            const real c0 = xc[k], c1 = xc[k + 1], c2_ = xc[k + 2], c3 = xc[k + 3];
+            const real al0 = (real)1. / (b0 - a0 * g);
+            const real g0 = c0 * al0;
+            const real al1 = (real)1. / (b1 - a1 * g0);
+            const real g1 = c1 * al1;
+            const real al2 = (real)1. / (b2 - a2 * g1);
+            const real g2 = c2_ * al2;
+            const real al3 = (real)1. / (b3 - a3 * g2);
+            g = c3 * al3;
+            xb[k] = al0; xb[k + 1] = al1; xb[k + 2] = al2; xb[k + 3] = al3;
+            xc[k] = g0; xc[k + 1] = g1; xc[k + 2] = g2; xc[k + 3] = g;
         }
-        __syncwarp();
+        for (; k <= L; ++k) {
+            const real al = (real)1. / (xb[k] - xa[k] * g);
+            g = xc[k] * al;
+            xb[k] = al;
+            xc[k] = g;
+        }
+    }
+    __syncthreads();
+    if (exists) {
+        const size_t c0 = IX2(1, iCell, L);
         for (int k = lane + 1; k <= L; k += 32) {
-            const size_t ic = IX2(k, iCell, L);
-            p.a_tri[ic] = sa[k];
-            p.alpha_tri[ic] = sal[k];
-            p.gamma_tri[ic] = sga[k];
+            p.a_tri[c0 + (k - 1)] = s_p[k];
+            p.alpha_tri[c0 + (k - 1)] = s_t[k];
+            p.gamma_tri[c0 + (k - 1)] = s_c[k];
         }
-        __syncwarp();
     }
 }
 
@@ -274,8 +323,8 @@ extern "C" int mpas_b200_compute_vert_imp_coefs_work(MPAS_VERTIMP_ARGS) {
     count_launch();
     KCHECK("cofrz_kernel");
     if (v.nCellsLoop > 0) {
-        const int wpb = 8;
-        const size_t shm = (size_t)wpb * 5 * (v.L + 2) * sizeof(real);
+        const int wpb = WPB;
+        const size_t shm = (size_t)wpb * VI_NCOL * (v.L + 2) * sizeof(real);
         static bool attr_set = false;
         if (!attr_set) {
             cudaFuncSetAttribute(vert_imp_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
