@@ -228,18 +228,37 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
         }
     }
     __syncwarp();
-    // explicit part of rw_p, TI:2659-2670 (reads only rwp[k] of its own level)
-    for (int k = lane + 1; k <= L; k += 32) {
-        if (k < 2) continue;
-        const size_t ic = (size_t)coff + (k - 1);
-        const real rtpp_k = FIRST ? (real)0.0 : s_rtpp[k], rtpp_km = FIRST ? (real)0.0 : s_rtpp[k - 1];
-        const real rpp_k = FIRST ? (real)0.0 : s_rhopp[k], rpp_km = FIRST ? (real)0.0 : s_rhopp[k - 1];
-        const real zzk = s_zz[k], zzkm = s_zz[k - 1];
-        rwp[k] = rwp[k] + dts * p.tend_rw[(size_t)woff + (k - 1)] -
-                 p.cofwz[ic] * ((zzk * ts[k] - zzkm * ts[k - 1]) + resm * (zzk * rtpp_k - zzkm * rtpp_km)) -
-                 p.cofwr[ic] * ((rs[k] + rs[k - 1]) + resm * (rpp_k + rpp_km)) + s_cofwt[k] * (ts[k] + resm * rtpp_k) +
-                 s_cofwt[k - 1] * (ts[k - 1] + resm * rtpp_km);
+    // explicit part of rw_p, TI:2659-2670 (reads only rwp[k] of its own level); the single-use operands of a lane's two
+    // levels share one round trip
+    for (int k0 = 0; k0 < L; k0 += 64) {
+        const int ka = k0 + lane + 1, kb = ka + 32;
+        const bool va = ka >= 2 && ka <= L, vb = kb <= L;
+        const int kla = va ? ka : 2, klb = vb ? kb : 2;
+        const real trw_a = p.tend_rw[(size_t)woff + (kla - 1)], trw_b = p.tend_rw[(size_t)woff + (klb - 1)];
+        const real cwz_a = p.cofwz[(size_t)coff + (kla - 1)], cwz_b = p.cofwz[(size_t)coff + (klb - 1)];
+        const real cwr_a = p.cofwr[(size_t)coff + (kla - 1)], cwr_b = p.cofwr[(size_t)coff + (klb - 1)];
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 0 ? !va : !vb) continue;
+            const int k = h ? kb : ka;
+            const real rtpp_k = FIRST ? (real)0.0 : s_rtpp[k], rtpp_km = FIRST ? (real)0.0 : s_rtpp[k - 1];
+            const real rpp_k = FIRST ? (real)0.0 : s_rhopp[k], rpp_km = FIRST ? (real)0.0 : s_rhopp[k - 1];
+            const real zzk = s_zz[k], zzkm = s_zz[k - 1];
+            rwp[k] = rwp[k] + dts * (h ? trw_b : trw_a) -
+                     (h ? cwz_b : cwz_a) * ((zzk * ts[k] - zzkm * ts[k - 1]) + resm * (zzk * rtpp_k - zzkm * rtpp_km)) -
+                     (h ? cwr_b : cwr_a) * ((rs[k] + rs[k - 1]) + resm * (rpp_k + rpp_km)) + s_cofwt[k] * (ts[k] + resm * rtpp_k) +
+                     s_cofwt[k - 1] * (ts[k - 1] + resm * rtpp_km);
+        }
     }
+    // operands of the Rayleigh-damping pass of the first 64 levels, requested before the sweep so that they arrive during it
+    const int pka = lane + 1, pkb = lane + 33;
+    const bool pva = pka >= 2 && pka <= L, pvb = pkb <= L;
+    const int pla = pva ? pka : 2, plb = pvb ? pkb : 2;
+    const real ww_a = FIRST ? (real)0.0 : p.wwAvg[(size_t)woff + (pla - 1)], ww_b = FIRST ? (real)0.0 : p.wwAvg[(size_t)woff + (plb - 1)];
+    const real d_a = p.rw_save[(size_t)woff + (pla - 1)] - p.rw[(size_t)woff + (pla - 1)];
+    const real d_b = p.rw_save[(size_t)woff + (plb - 1)] - p.rw[(size_t)woff + (plb - 1)];
+    const real dk_a = p.dss[(size_t)coff + (pla - 1)], dk_b = p.dss[(size_t)coff + (plb - 1)];
+    const real w_a = p.w[(size_t)woff + (pla - 1)], w_b = p.w[(size_t)woff + (plb - 1)];
     // ---- tridiagonal sweep, TI:2675-2682, in the reference's order.  The recurrence is serial in k, so one LANE sweeps one
     // column: the block's WPB columns are swept together by the first WPB lanes of warp 0 (1/WPB of the instructions of
     // a sweep per warp), between two block barriers.
@@ -301,14 +320,17 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
     for (int k = lane + 1; k <= L; k += 32) {  // TI:2655-2657, 2687-2699
         if (k < 2) continue;
         const size_t ic = (size_t)coff + (k - 1), iw = (size_t)woff + (k - 1);
+        const bool pre = k <= 64;  // preloaded above
+        const bool hb = k > 32;
         const real rw_old = FIRST ? (real)0.0 : s_rwold[k];
-        real ww = FIRST ? (real)0.0 : p.wwAvg[iw];
+        real ww = pre ? (hb ? ww_b : ww_a) : (FIRST ? (real)0.0 : p.wwAvg[iw]);
         ww = ww + (real)0.5 * ((real)1.0 - epssm) * rw_old;
-        const real d = p.rw_save[iw] - p.rw[iw];
-        const real dk = p.dss[ic];
+        const real d = pre ? (hb ? d_b : d_a) : p.rw_save[iw] - p.rw[iw];
+        const real dk = pre ? (hb ? dk_b : dk_a) : p.dss[ic];
+        const real wk = pre ? (hb ? w_b : w_a) : p.w[iw];
         const real r = (rwp[k] + d -
                         dts * dk * (p.fzm[k - 1] * s_zz[k] + p.fzp[k - 1] * s_zz[k - 1]) *
-                            (p.fzm[k - 1] * s_rhozz[k] + p.fzp[k - 1] * s_rhozz[k - 1]) * p.w[iw]) /
+                            (p.fzm[k - 1] * s_rhozz[k] + p.fzp[k - 1] * s_rhozz[k - 1]) * wk) /
                            ((real)1.0 + dts * dk) -
                        d;
         rwp[k] = r;

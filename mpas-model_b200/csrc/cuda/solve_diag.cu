@@ -128,9 +128,27 @@ __global__ void __launch_bounds__(256) sd_edge_kernel(SdP p) {
     }
     real ve;
     if (RECON) {
+        // TI:5641-5650.  The first RN edges: all indices, then all weights and velocities are loaded before the ordered sum
+        // (two round trips instead of two per edge); entries beyond nEdgesOnEdge repeat the first index and are not added.
         ve = 0.0;
         const int n = p.nEdgesOnEdge[iEdge - 1];
-        for (int i = 1; i <= n; ++i) {
+        constexpr int RN = 10;
+        const int* eoep = p.edgesOnEdge + (size_t)(iEdge - 1) * mE2;
+        const real* wp = p.weightsOnEdge + (size_t)(iEdge - 1) * mE2;
+        const int nn = mE2 < RN ? mE2 : RN;
+        int eo[RN];
+#pragma unroll
+        for (int i = 0; i < RN; ++i) eo[i] = eoep[i < n && i < nn ? i : 0];
+        real wv[RN], uv[RN];
+#pragma unroll
+        for (int i = 0; i < RN; ++i) {
+            wv[i] = wp[i < nn ? i : 0];
+            uv[i] = p.u[IX2(k, eo[i], L)];
+        }
+#pragma unroll
+        for (int i = 0; i < RN; ++i)
+            if (i < n && i < nn) ve = ve + wv[i] * uv[i];
+        for (int i = RN + 1; i <= n; ++i) {
             const int eoe = p.edgesOnEdge[IX2(i, iEdge, mE2)];
             ve = ve + p.weightsOnEdge[IX2(i, iEdge, mE2)] * p.u[IX2(k, eoe, L)];
         }
