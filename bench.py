@@ -38,6 +38,7 @@ def words_per_call(ns):
         "atm_rk_dynamics_substep_finish": 30.0,
         "atm_rk_integration_setup": 20.0 + 2 * ns,
         "atm_compute_moist_coefficients": 6.0 + ns,
+        "mpas_reconstruct": 8.0,  # u over the 3 edges per cell + 5 outputs (mpas_vector_reconstruction.F:254-288)
     }
 
 

@@ -234,4 +234,14 @@ typedef int (*mpas_halo_fn)(void *ctx, int which, mpas_real *array);
         mpas_real *exner, mpas_real *exner_base, const mpas_real *fzm, const mpas_real *fzp,       \
         const mpas_real *zb_cell, const mpas_real *zb3_cell
 
+/* mpas_reconstruct_2d, operators/mpas_vector_reconstruction.F:195-305 (called once per dt at TI:1594 with u time level 2;
+ * pool arrays resolved as at :229-243).  nCellsLoop = nCellsSolve, or nCells when includeHalos is given.  coeffs_reconstruct
+ * (3, maxEdges, nCells+1) comes from mpas_init_reconstruct (:51-176). */
+#define MPAS_RECONSTRUCT_ARGS                                                                      \
+    int nVertLevels, int maxEdges, int nCells, int nEdges, int nCellsLoop, int on_a_sphere,        \
+        const mpas_real *u, const mpas_real *coeffs_reconstruct, const int *nEdgesOnCell,          \
+        const int *edgesOnCell, const mpas_real *latCell, const mpas_real *lonCell,                \
+        mpas_real *uReconstructX, mpas_real *uReconstructY, mpas_real *uReconstructZ,              \
+        mpas_real *uReconstructZonal, mpas_real *uReconstructMeridional
+
 #endif

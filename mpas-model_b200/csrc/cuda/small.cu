@@ -381,6 +381,82 @@ extern "C" int mpas_b200_rk_dynamics_substep_finish(MPAS_SUBSTEPFINISH_ARGS) {
     return 0;
 }
 
+// ---- mpas_reconstruct_2d (operators/mpas_vector_reconstruction.F:195-305)
+namespace {
+struct RecP {
+    int L, mE, nCellsLoop, on_a_sphere;
+    const real *u, *coeffs, *latCell, *lonCell;
+    const int *nEdgesOnCell, *edgesOnCell;
+    real *ux, *uy, *uz, *uzonal, *umerid;
+};
+// one thread per (k, cell); the NE edge indices, then all coefficients and velocities are loaded before the ordered sums
+// (:254-269).  The rotation (:275-288) evaluates cos/sin of the cell's latitude and longitude on the device (<= 2 ulp from
+// the host's libm, the only non-bit-exact part of this routine).
+template <int NE>
+__global__ void __launch_bounds__(256) reconstruct_kernel(RecP p) {
+    const int L = p.L, mE = p.mE;
+    FLAT_KC(p.nCellsLoop, L);
+    const int iCell = 1 + _c0;
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const int* eoc = p.edgesOnCell + (size_t)(iCell - 1) * mE;
+    const real* cf = p.coeffs + (size_t)(iCell - 1) * mE * 3;
+    int e[NE];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) e[i] = eoc[i < ne ? i : 0];
+    real c1[NE], c2[NE], c3[NE], ue[NE];
+#pragma unroll
+    for (int i = 0; i < NE; ++i) {
+        const int j = i < ne ? i : 0;
+        c1[i] = cf[3 * j];
+        c2[i] = cf[3 * j + 1];
+        c3[i] = cf[3 * j + 2];
+        ue[i] = p.u[IX2(k, e[i], L)];
+    }
+    real x = 0.0, y = 0.0, z = 0.0;
+#pragma unroll
+    for (int i = 0; i < NE; ++i)
+        if (i < ne) {
+            x = x + c1[i] * ue[i];
+            y = y + c2[i] * ue[i];
+            z = z + c3[i] * ue[i];
+        }
+    for (int i = NE + 1; i <= ne; ++i) {
+        const real uu = p.u[IX2(k, eoc[i - 1], L)];
+        x = x + cf[3 * (i - 1)] * uu;
+        y = y + cf[3 * (i - 1) + 1] * uu;
+        z = z + cf[3 * (i - 1) + 2] * uu;
+    }
+    const size_t ic = IX2(k, iCell, L);
+    p.ux[ic] = x;
+    p.uy[ic] = y;
+    p.uz[ic] = z;
+    if (p.on_a_sphere) {
+        real slat, clat, slon, clon;
+        sincos(p.latCell[iCell - 1], &slat, &clat);
+        sincos(p.lonCell[iCell - 1], &slon, &clon);
+        p.uzonal[ic] = -x * slon + y * clon;
+        p.umerid[ic] = -(x * clon + y * slon) * slat + z * clat;
+    } else {
+        p.uzonal[ic] = x;
+        p.umerid[ic] = y;
+    }
+}
+}  // namespace
+
+extern "C" int mpas_b200_reconstruct_2d(MPAS_RECONSTRUCT_ARGS) {
+    (void)nCells; (void)nEdges;
+    RecP p;
+    p.L = nVertLevels; p.mE = maxEdges; p.nCellsLoop = nCellsLoop; p.on_a_sphere = on_a_sphere;
+    p.u = X(u); p.coeffs = X(coeffs_reconstruct); p.latCell = X(latCell); p.lonCell = X(lonCell);
+    p.nEdgesOnCell = X(nEdgesOnCell); p.edgesOnCell = X(edgesOnCell);
+    p.ux = X(uReconstructX); p.uy = X(uReconstructY); p.uz = X(uReconstructZ); p.uzonal = X(uReconstructZonal); p.umerid = X(uReconstructMeridional);
+    if (p.nCellsLoop <= 0) return 0;
+    if (maxEdges <= 6) KLAUNCH((reconstruct_kernel<6>), (long long)p.nCellsLoop * p.L, 256, p);
+    else KLAUNCH((reconstruct_kernel<8>), (long long)p.nCellsLoop * p.L, 256, p);
+    KCHECK("reconstruct_kernel");
+    return 0;
+}
+
 extern "C" int mpas_b200_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS) {
     (void)nCells; (void)nEdges; (void)vertexStart; (void)vertexEnd; (void)cellSolveStart; (void)cellSolveEnd; (void)vertexSolveStart; (void)vertexSolveEnd;
     (void)edgeSolveStart; (void)edgeSolveEnd;

@@ -220,6 +220,15 @@ int call_init_coupled(DBlock& b) {
                                               b.R("exner_base"), b.R("fzm"), b.R("fzp"), b.R("zb_cell"), b.R("zb3_cell"));
 }
 
+// mpas_reconstruct at the end of atm_srk3 (TI:1594): u time level 2, owned cells
+int call_reconstruct(DBlock& b) {
+    if (!b.f.count("coeffs_reconstruct") || !b.f.count("uReconstructX")) return 0;
+    Dims d = dims(b);
+    return mpas_b200_reconstruct_2d(d.L, d.mE, d.nC, d.nE, d.nCS, (int)b.c("on_a_sphere", 1), b.R("u@2"), b.R("coeffs_reconstruct"), b.I("nEdgesOnCell"),
+                                    b.I("edgesOnCell"), b.R("latCell"), b.R("lonCell"), b.R("uReconstructX"), b.R("uReconstructY"), b.R("uReconstructZ"),
+                                    b.R("uReconstructZonal"), b.R("uReconstructMeridional"));
+}
+
 // ---- mono: the two embedded exchanges (TI:3757, 4098) need every block of the process at the same point
 struct MonoCtx {
     Dycore* m;
@@ -428,6 +437,10 @@ static int srk3_body(Dycore& m) {
             if (rk_step < 3) CK(xchg(m, {{"scalars@2", 0}}));  // TI:1569-1572
         }
     }
+    {
+        Phase ph(m, "mpas_reconstruct");
+        for (auto& b : m.blocks) CK(call_reconstruct(b));  // TI:1594
+    }
     // DO_PHYSICS (default build, src/core_atmosphere/Makefile:3): negative mixing ratios reset, TI:1646-1647
     for (auto& b : m.blocks) {
         Dims d = dims(b);
@@ -519,6 +532,7 @@ int dycore_call(Dycore& m, const std::string& rt, const double* q, int nq) {
         else if (rt == "moist") CK(call_moist(b));
         else if (rt == "substep_finish") { need(2); CK(call_substep_finish(b, (int)q[0], (int)q[1])); }
         else if (rt == "init_coupled") CK(call_init_coupled(b));
+        else if (rt == "reconstruct") CK(call_reconstruct(b));
         else return fail_msg("dycore_call: unknown routine " + rt);
     }
     return 0;

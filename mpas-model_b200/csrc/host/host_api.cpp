@@ -122,6 +122,7 @@ int mpas_host_case_build_block(void* h, int iBlock, int nVertLevels, int init_ca
     init_advection_and_deformation(blk->mesh, p);
     init_case_jw(blk->mesh, hc->cfg, p);
     core_init_derived(blk->mesh, hc->cfg, p);
+    init_reconstruct(blk->mesh, p);
     allocate_dycore_fields(blk->mesh, hc->cfg, p, full_fields != 0);
     p.cfg["config_coef_3rd_order"] = hc->cfg.coef_3rd_order;
     hc->blocks[iBlock] = std::move(blk);

@@ -46,6 +46,10 @@ void init_case_jw(const Mesh& m, const InitConfig& cfg, Pool& p);
 // core-init derived arrays (mpas_atm_core.F:311-360, 456-463, 927-1288)
 void core_init_derived(const Mesh& m, const InitConfig& cfg, Pool& p);
 
+// mpas_initialize_vectors + mpas_init_reconstruct (mpas_vector_operations.F:653, mpas_vector_reconstruction.F:51):
+// edgeNormalVectors, cellTangentPlane, localVerticalUnitVectors, coeffs_reconstruct
+void init_reconstruct(const Mesh& m, Pool& p);
+
 // allocate the remaining state/diag/tend fields the dycore uses (zero filled)
 void allocate_dycore_fields(const Mesh& m, const InitConfig& cfg, Pool& p, bool full);
 

@@ -494,6 +494,51 @@ int oracle_compute_solve_diagnostics_work(MPAS_SOLVEDIAG_ARGS) {
     return 0;
 }
 
+// ------------------------------------------------------------------ operators/mpas_vector_reconstruction.F:195-305
+// mpas_reconstruct_2d: cell-centre velocity vector from the edge-normal components with the precomputed
+// radial-basis-function coefficients (:254-269), then the zonal / meridional rotation (:275-288).
+int oracle_reconstruct_2d(MPAS_RECONSTRUCT_ARGS) {
+    (void)nCells; (void)nEdges;
+    const int L = nVertLevels, mE = maxEdges;
+#pragma omp parallel for schedule(static)
+    for (int iCell = 1; iCell <= nCellsLoop; ++iCell) {
+        for (int k = 1; k <= L; ++k) {
+            uReconstructX[IX2(k, iCell, L)] = 0.0;
+            uReconstructY[IX2(k, iCell, L)] = 0.0;
+            uReconstructZ[IX2(k, iCell, L)] = 0.0;
+        }
+        for (int i = 1; i <= nEdgesOnCell[iCell - 1]; ++i) {
+            const int iEdge = edgesOnCell[IX2(i, iCell, mE)];
+            const real c1 = coeffs_reconstruct[IX3(1, i, iCell, 3, mE)], c2 = coeffs_reconstruct[IX3(2, i, iCell, 3, mE)],
+                       c3 = coeffs_reconstruct[IX3(3, i, iCell, 3, mE)];
+            for (int k = 1; k <= L; ++k) {
+                uReconstructX[IX2(k, iCell, L)] = uReconstructX[IX2(k, iCell, L)] + c1 * u[IX2(k, iEdge, L)];
+                uReconstructY[IX2(k, iCell, L)] = uReconstructY[IX2(k, iCell, L)] + c2 * u[IX2(k, iEdge, L)];
+                uReconstructZ[IX2(k, iCell, L)] = uReconstructZ[IX2(k, iCell, L)] + c3 * u[IX2(k, iEdge, L)];
+            }
+        }
+    }
+    if (on_a_sphere) {
+#pragma omp parallel for schedule(static)
+        for (int iCell = 1; iCell <= nCellsLoop; ++iCell) {
+            const real clat = std::cos(latCell[iCell - 1]), slat = std::sin(latCell[iCell - 1]);
+            const real clon = std::cos(lonCell[iCell - 1]), slon = std::sin(lonCell[iCell - 1]);
+            for (int k = 1; k <= L; ++k) {
+                const real x = uReconstructX[IX2(k, iCell, L)], y = uReconstructY[IX2(k, iCell, L)], z = uReconstructZ[IX2(k, iCell, L)];
+                uReconstructZonal[IX2(k, iCell, L)] = -x * slon + y * clon;
+                uReconstructMeridional[IX2(k, iCell, L)] = -(x * clon + y * slon) * slat + z * clat;
+            }
+        }
+    } else {
+        for (int iCell = 1; iCell <= nCellsLoop; ++iCell)
+            for (int k = 1; k <= L; ++k) {
+                uReconstructZonal[IX2(k, iCell, L)] = uReconstructX[IX2(k, iCell, L)];
+                uReconstructMeridional[IX2(k, iCell, L)] = uReconstructY[IX2(k, iCell, L)];
+            }
+    }
+    return 0;
+}
+
 // ------------------------------------------------------------------ TI:5825-5990
 int oracle_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS) {
     const int L = nVertLevels, L1 = L + 1, mE = maxEdges, ns = num_scalars;

@@ -30,6 +30,7 @@ int oracle_divergence_damping_3d(MPAS_DIVDAMP_ARGS);
 int oracle_recover_large_step_variables_work(MPAS_RECOVER_ARGS);
 int oracle_compute_solve_diagnostics_work(MPAS_SOLVEDIAG_ARGS);
 int oracle_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS);
+int oracle_reconstruct_2d(MPAS_RECONSTRUCT_ARGS);
 int oracle_rk_dynamics_substep_finish(MPAS_SUBSTEPFINISH_ARGS);
 int oracle_compute_dyn_tend_work(MPAS_DYNTEND_ARGS);
 int oracle_advance_scalars_work(MPAS_ADVSCALARS_ARGS);
@@ -306,6 +307,15 @@ void model_init(OModel& m) {
 }
 
 // atm_srk3, TI:142-1796 (config_apply_lbcs = false, physics off, IAU off)
+// mpas_reconstruct at the end of atm_srk3 (TI:1594): u time level 2, owned cells
+void call_reconstruct(OBlock& b) {
+    if (!b.f.count("coeffs_reconstruct") || !b.f.count("uReconstructX")) return;
+    Dims d = dims(b);
+    oracle_reconstruct_2d(d.L, d.mE, d.nC, d.nE, d.nCS, (int)b.c("on_a_sphere", 1), b.R("u@2"), b.R("coeffs_reconstruct"), b.I("nEdgesOnCell"), b.I("edgesOnCell"),
+                          b.R("latCell"), b.R("lonCell"), b.R("uReconstructX"), b.R("uReconstructY"), b.R("uReconstructZ"), b.R("uReconstructZonal"),
+                          b.R("uReconstructMeridional"));
+}
+
 void srk3_step(OModel& m) {
     OBlock& b0 = m.blocks[0];
     const real dt = (real)b0.c("config_dt");
@@ -420,6 +430,7 @@ void srk3_step(OModel& m) {
         for (size_t i = 0; i < n; ++i)
             if (s2[i] < 0.0) s2[i] = 0.0;
     }
+    for (auto& b : m.blocks) call_reconstruct(b);  // TI:1594
     // mpas_pool_shift_time_levels(state), mpas_atm_core.F:671
     for (auto& b : m.blocks)
         for (const char* n : {"u", "w", "theta_m", "rho_zz", "scalars"}) b.swap_levels(n);
@@ -522,6 +533,7 @@ int oracle_model_call(void* h, const char* routine, const double* q, int nq) {
                                                   b.R("ruAvg_split"), b.R("wwAvg"), b.R("wwAvg_split"), b.R("u@1"), b.R("u@2"), b.R("w@1"), b.R("w@2"),
                                                   b.R("theta_m@1"), b.R("theta_m@2"), b.R("rho_zz@1"), b.R("rho_zz@2"));
             }
+            else if (rt == "reconstruct") call_reconstruct(b);
             else if (rt == "init_coupled") {
                 oracle_init_coupled_diagnostics(d.L, d.mE, d.ns, (int)b.c("index_qv", 1), d.nC, d.nE, RANGES, b.I("cellsOnEdge"), b.I("nEdgesOnCell"), b.I("edgesOnCell"),
                                                 b.R("edgesOnCell_sign"), b.R("theta_m@1"), b.R("theta"), b.R("rho_zz@1"), b.R("rho"), b.R("rho_p"), b.R("rho_base"),

@@ -9,7 +9,8 @@ pytestmark = pytest.mark.gpu
 
 STATE = ["u@1", "w@1", "theta_m@1", "rho_zz@1", "scalars@1"]
 DIAG = ["ru", "rw", "rho_p", "rtheta_p", "exner", "pressure_p", "rho_edge", "pv_edge", "v", "ke", "divergence", "vorticity",
-        "tend_u", "tend_w", "tend_theta", "tend_rho", "ruAvg", "wwAvg", "kdiff", "h_divergence"]
+        "tend_u", "tend_w", "tend_theta", "tend_rho", "ruAvg", "wwAvg", "kdiff", "h_divergence", "uReconstructX", "uReconstructY", "uReconstructZ",
+        "uReconstructZonal", "uReconstructMeridional"]
 TOL = 1e-12
 # Against the oracle with libm pow (the reference's arithmetic) every kernel is bit-exact except exner = x**rcv:
 # glibc's pow is not correctly rounded in ~1e-3 of the cases, the GPU's pow_rcv is.  u, theta_m, rho_zz, scalars

@@ -94,6 +94,24 @@ def test_routine_bit_exact(state, routine, params):
     _check(blocks, gpu, ora)
 
 
+def test_reconstruct_vector_exact_rotation_within_1e12(state):
+    """mpas_reconstruct_2d: the cell-centre 3-vector is an ordered sum (bit-exact); the zonal/meridional rotation uses the
+    device's sin/cos (<= 2 ulp from libm), tolerance 1e-12 relative L2."""
+    blocks, cfg, gpu, ora = state
+    gpu.call("reconstruct")
+    ora.call("reconstruct")
+    for ib in range(len(blocks)):
+        for n in ("uReconstructX", "uReconstructY", "uReconstructZ"):
+            g, o = gpu.field(ib, n), ora.field(ib, n)
+            assert np.abs(o).max() > 1.0
+            assert np.array_equal(g, o), n
+        for n in ("uReconstructZonal", "uReconstructMeridional"):
+            g, o = gpu.field(ib, n), ora.field(ib, n)
+            assert common.rel_l2(g, o) <= 1e-12, (n, common.rel_l2(g, o))
+            gpu.set_field(ib, n, o)  # later tests compare every field bit for bit
+    _check(blocks, gpu, ora)
+
+
 def test_recover_rk3_pow_within_last_place(state):
     blocks, cfg, gpu, ora = state
     gpu.call("recover", cfg["config_dt"] / 3, 2, 3)
