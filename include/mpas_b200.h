@@ -84,6 +84,9 @@ int mpas_b200_dycore_timer_count(void* h);
 int mpas_b200_dycore_timer_get(void* h, int idx, char* name, int cap, double* ms, long* calls);
 int mpas_b200_dycore_timer_reset(void* h);
 double mpas_b200_dycore_global_max_abs(void* h, const char* name); /* summarize_timestep analogue, TI:6675 */
+/* global min / max over owned elements of every stride-th element from offset (one scalar of scalars(:,k,iCell)): the
+ * reductions summarize_timestep prints for w, u and the scalars, TI:6758-7010 (mpas_dmpar_min_real / max_real) */
+int mpas_b200_dycore_global_minmax(void* h, const char* name, long long offset, long long stride, double* min_out, double* max_out);
 
 /* ---- Layer 0: host harness (mesh, partition, JW initial state) ---- */
 void* mpas_host_case_create(int level, int lloyd_iters, int sfc);

@@ -183,6 +183,7 @@ void mpas_b200_dycore_destroy(void* h) {
         if (m->graph_exec[i]) cudaGraphExecDestroy(m->graph_exec[i]);
     for (auto e : m->event_pool) cudaEventDestroy(e);
     if (m->d_reduce) cudaFree(m->d_reduce);
+    if (m->d_minmax) cudaFree(m->d_minmax);
     m->nccl.destroy();
     delete m;
 }

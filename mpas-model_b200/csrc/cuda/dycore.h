@@ -71,6 +71,7 @@ struct Dycore {
     long steps_done = 0;
     int parity = 0;  // number of steps taken mod 2 (time levels swap every step)
     real* d_reduce = nullptr;
+    real* d_minmax = nullptr;
 };
 
 struct XField {

@@ -574,7 +574,96 @@ double dycore_global_max_abs(Dycore& m, const std::string& name) {
     return result;
 }
 
+// global min and max over the owned elements of a field (every stride-th element from offset: one scalar of the
+// (num_scalars, nVertLevels, nCells) array), the reductions summarize_timestep prints (TI:6758-6790 w, :6815-6850 u, :6985-7010 scalars)
+namespace {
+__global__ void minmax_kernel(const real* a, long long n, long long offset, long long stride, real* out, int nout) {
+    __shared__ real smin[256], smax[256];
+    real lo = INFINITY, hi = -INFINITY;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        const real v = a[offset + t * stride];
+        lo = fmin(lo, v);
+        hi = fmax(hi, v);
+    }
+    smin[threadIdx.x] = lo;
+    smax[threadIdx.x] = hi;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) {
+            smin[threadIdx.x] = fmin(smin[threadIdx.x], smin[threadIdx.x + s]);
+            smax[threadIdx.x] = fmax(smax[threadIdx.x], smax[threadIdx.x + s]);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {  // out[2b] = max, out[2b + 1] = -min: both reduce with max
+        out[2 * blockIdx.x] = smax[0];
+        out[2 * blockIdx.x + 1] = -smin[0];
+    }
+    (void)nout;
+}
+__global__ void minmax_final_kernel(const real* part, int nb, real* out) {
+    __shared__ real sa[256], sb[256];
+    real a = -INFINITY, b = -INFINITY;
+    for (int i = threadIdx.x; i < nb; i += blockDim.x) {
+        a = fmax(a, part[2 * i]);
+        b = fmax(b, part[2 * i + 1]);
+    }
+    sa[threadIdx.x] = a;
+    sb[threadIdx.x] = b;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) {
+            sa[threadIdx.x] = fmax(sa[threadIdx.x], sa[threadIdx.x + s]);
+            sb[threadIdx.x] = fmax(sb[threadIdx.x], sb[threadIdx.x + s]);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        out[0] = sa[0];
+        out[1] = sb[0];
+    }
+}
+}  // namespace
+
+int dycore_global_minmax(Dycore& m, const std::string& name, long long offset, long long stride, double* mn, double* mx) {
+    const int NB = 256;
+    if (stride < 1 || offset < 0 || offset >= stride) return fail_msg("mpas_b200_dycore_global_minmax: need 0 <= offset < stride");
+    if (!m.d_minmax) {
+        cudaError_t e = cudaMalloc(&m.d_minmax, (2 * NB + 2) * sizeof(real));
+        if (e != cudaSuccess) return fail("cudaMalloc minmax", e);
+    }
+    double lo = INFINITY, hi = -INFINITY;
+    for (auto& b : m.blocks) {
+        auto it = b.f.find(name);
+        if (it == b.f.end()) return fail_msg("mpas_b200_dycore_global_minmax: no field " + name);
+        const DField& f = it->second;
+        if (f.kind != 0) return fail_msg("mpas_b200_dycore_global_minmax: " + name + " is not a real field");
+        const long long nOwned = f.loc == 1 ? (long long)b.c("nCellsSolve") : f.loc == 2 ? (long long)b.c("nEdgesSolve") : (long long)b.c("nVerticesSolve");
+        if ((nOwned * f.inner) % stride) return fail_msg("mpas_b200_dycore_global_minmax: stride does not divide the field");
+        const long long n = nOwned * f.inner / stride;
+        minmax_kernel<<<NB, 256, 0, stream()>>>((const real*)f.dev, n, offset, stride, m.d_minmax, NB);
+        minmax_final_kernel<<<1, 256, 0, stream()>>>(m.d_minmax, NB, m.d_minmax + 2 * NB);
+        count_launch(2);
+        if (m.nranks > 1 && m.have_comm) m.nccl.allreduce_max(m.d_minmax + 2 * NB, m.d_minmax + 2 * NB, 2, stream());
+        real v[2] = {0, 0};
+        cudaMemcpyAsync(v, m.d_minmax + 2 * NB, 2 * sizeof(real), cudaMemcpyDeviceToHost, stream());
+        cudaError_t e = cudaStreamSynchronize(stream());
+        if (e != cudaSuccess) return fail("mpas_b200_dycore_global_minmax", e);
+        hi = std::max(hi, (double)v[0]);
+        lo = std::min(lo, -(double)v[1]);
+    }
+    *mn = lo;
+    *mx = hi;
+    return 0;
+}
+
 }  // namespace mpasb200
+
+extern "C" int mpas_b200_dycore_global_minmax(void* h, const char* name, long long offset, long long stride, double* mn, double* mx) {
+    try {
+        return mpasb200::dycore_global_minmax(*(mpasb200::Dycore*)h, name, offset, stride, mn, mx);
+    } catch (const std::exception& e) { return mpasb200::fail_msg(e.what()); }
+}
 
 extern "C" double mpas_b200_dycore_global_max_abs(void* h, const char* name) {
     try {

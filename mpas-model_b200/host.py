@@ -78,6 +78,7 @@ def lib():
         _lib.mpas_b200_dycore_timer_reset.argtypes = [C.c_void_p]
         _lib.mpas_b200_dycore_global_max_abs.restype = C.c_double
         _lib.mpas_b200_dycore_global_max_abs.argtypes = [C.c_void_p, C.c_char_p]
+        _lib.mpas_b200_dycore_global_minmax.argtypes = [C.c_void_p, C.c_char_p, C.c_longlong, C.c_longlong, C.POINTER(C.c_double), C.POINTER(C.c_double)]
     return _lib
 
 
@@ -267,6 +268,12 @@ class Dycore:
 
     def max_abs(self, name):
         return lib().mpas_b200_dycore_global_max_abs(self.h, name.encode())
+
+    def minmax(self, name, offset=0, stride=1):
+        """global (all ranks) min and max over the owned elements, the reductions of summarize_timestep (TI:6675)"""
+        lo, hi = C.c_double(), C.c_double()
+        self._chk(lib().mpas_b200_dycore_global_minmax(self.h, name.encode(), offset, stride, C.byref(lo), C.byref(hi)))
+        return lo.value, hi.value
 
     def timers(self):
         L = lib()

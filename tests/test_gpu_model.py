@@ -134,3 +134,20 @@ def test_graph_replay_matches_eager():
     a.step(4); b.step(4)
     for n in STATE:
         assert np.array_equal(a.field(0, n), b.field(0, n)), n
+
+
+def test_global_minmax_matches_numpy_over_owned_elements():
+    """summarize_timestep reductions (TI:6758-7010): min / max of w, u and one scalar over the owned elements of all blocks"""
+    case, blocks = common.make_case(4, 2, nVertLevels=26, num_scalars=3)
+    _tracers(blocks, 3)
+    gpu = common.GpuModel(blocks, common.level_config(4))
+    gpu.init()
+    gpu.step(2)
+    for name, key, off, stride in (("w@1", "nCellsSolve", 0, 1), ("u@1", "nEdgesSolve", 0, 1), ("scalars@1", "nCellsSolve", 1, 3)):
+        lo, hi = np.inf, -np.inf
+        for ib, b in enumerate(blocks):
+            a = gpu.field(ib, name)[:int(b.cfg()[key])]
+            a = a[..., off] if stride > 1 else a
+            lo, hi = min(lo, float(a.min())), max(hi, float(a.max()))
+        assert gpu.minmax(name, off, stride) == (lo, hi), name
+    assert gpu.max_abs("u@1") == max(abs(v) for v in gpu.minmax("u@1"))
