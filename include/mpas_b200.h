@@ -106,6 +106,29 @@ int mpas_host_block_nexch(void* b, int kind, int which);
 int mpas_host_block_exch_info(void* b, int kind, int which, int idx, int* endPoint, int* haloLayer, int* nlist);
 int mpas_host_block_exch_lists(void* b, int kind, int which, int idx, int* srcList, int* destList);
 
+/* ---- on-disk files: MPAS grid / restart files in the netCDF classic formats (CDF-1/2/5), the formats
+ * of the reference's streams (Registry.xml:397-1125, mpas_bootstrapping.F:79-423); no netCDF library is used ---- */
+int mpas_host_case_write_grid(void* h, const char* path, int version);
+void* mpas_host_case_create_from_grid(const char* path, int sfc);
+int mpas_host_case_create_restart(void* h, int iBlock, const char* path, int version, const char* names_csv, const char* xtime);
+int mpas_host_block_write_restart(void* b, const char* path, const char* names_csv);
+int mpas_host_block_read_restart(void* b, const char* path);
+void* mpas_nc_open(const char* path);
+void* mpas_nc_create(const char* path, int version);
+int mpas_nc_close(void* h);
+int mpas_nc_inq(void* h, int* version, int* ndims, int* nvars, int* ngatts, long long* numrecs);
+int mpas_nc_dim_info(void* h, int idx, char* name, int name_cap, long long* len);
+int mpas_nc_var_info(void* h, int idx, char* name, int name_cap, int* type, int* ndims, int* dimids, long long* count);
+int mpas_nc_gatt_text(void* h, const char* name, char* out, int cap);
+int mpas_nc_get_double(void* h, const char* name, double* out);
+int mpas_nc_get_int(void* h, const char* name, int* out);
+int mpas_nc_def_dim(void* h, const char* name, long long len);
+int mpas_nc_def_var(void* h, const char* name, int type, int ndims, const int* dimids);
+int mpas_nc_put_gatt_text(void* h, const char* name, const char* value);
+int mpas_nc_enddef(void* h, long long numrecs);
+int mpas_nc_put_double(void* h, int varid, long long rec, long long start, long long count, const double* data);
+int mpas_nc_put_int(void* h, int varid, long long rec, long long start, long long count, const int* data);
+
 #ifdef __cplusplus
 }
 #endif

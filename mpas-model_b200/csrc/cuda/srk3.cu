@@ -320,7 +320,7 @@ int dycore_init(Dycore& m) {
     }
     CK(dycore_exchange(m, {{"u@1", 0}}));  // :145
     for (auto& b : m.blocks) {
-        CK(call_init_coupled(b));
+        if (b.c("config_do_restart", 0) == 0) CK(call_init_coupled(b));  // mpas_atm_core.F:389
         CK(call_solve_diagnostics(b, 1, (real)b.c("config_dt"), -1));
     }
     CK(dycore_exchange(m, {{"pv_edge", 0}, {"ru", 0}, {"rw", 0}}));  // :180-186

@@ -8,6 +8,8 @@
 #include "decomp.h"
 #include "init_atm.h"
 #include "mesh.h"
+#include "mpas_io.h"
+#include "nc_classic.h"
 #include "pool.h"
 
 using namespace mpas;
@@ -192,4 +194,172 @@ int mpas_host_block_exch_lists(void* b, int kind, int which, int idx, int* srcLi
     return 0;
 }
 
+
+// ---- on-disk files: grid.nc, restart, generic classic-netCDF access -------------------------
+
+static std::vector<std::string> split_csv(const char* s) {
+    std::vector<std::string> out;
+    std::string cur;
+    for (const char* p = s; *p; ++p) {
+        if (*p == ',') { if (!cur.empty()) out.push_back(cur); cur.clear(); }
+        else cur.push_back(*p);
+    }
+    if (!cur.empty()) out.push_back(cur);
+    return out;
+}
+
+// the global mesh of the case as an MPAS grid file (version 1, 2 or 5 = CDF-1 / CDF-2 / CDF-5)
+int mpas_host_case_write_grid(void* h, const char* path, int version) {
+    API_TRY
+    write_grid_nc(((HostCase*)h)->global, path, version);
+    return 0;
+    API_CATCH(1)
+}
+
+// a case from an MPAS grid file instead of the mesh generator; a unit-sphere file is scaled to the Earth radius as
+// init_atm_case_jw does (mpas_init_atm_cases.F:497-510)
+void* mpas_host_case_create_from_grid(const char* path, int sfc) {
+    API_TRY
+    auto* hc = new HostCase();
+    Mesh in;
+    read_grid_nc(path, in);
+    if (sfc) {
+        sfc_reorder(in, hc->global, hc->perm);
+        hc->has_perm = true;
+    } else {
+        hc->global = in;
+    }
+    if (hc->global.sphere_radius == 1.0) scale_mesh_to_sphere(hc->global, Constants::a);
+    return hc;
+    API_CATCH(nullptr)
+}
+
+// restart file: header from the global dimensions and the fields of block iBlock (names: comma-separated pool names)
+int mpas_host_case_create_restart(void* h, int iBlock, const char* path, int version, const char* names_csv, const char* xtime) {
+    API_TRY
+    auto* hc = (HostCase*)h;
+    if (iBlock < 0 || iBlock >= (int)hc->blocks.size() || !hc->blocks[iBlock]) throw std::runtime_error("create_restart: block not built");
+    create_restart_nc(path, version, hc->global, *hc->blocks[iBlock], split_csv(names_csv), xtime ? xtime : "");
+    return 0;
+    API_CATCH(1)
+}
+int mpas_host_block_write_restart(void* b, const char* path, const char* names_csv) {
+    API_TRY
+    write_restart_block(path, *(Block*)b, split_csv(names_csv));
+    return 0;
+    API_CATCH(1)
+}
+int mpas_host_block_read_restart(void* b, const char* path) {  // number of pool fields filled, -1 on error
+    API_TRY
+    return read_restart_block(path, *(Block*)b);
+    API_CATCH(-1)
+}
+
+void* mpas_nc_open(const char* path) {
+    API_TRY
+    auto* f = new nc::File();
+    try { f->open(path); } catch (...) { delete f; throw; }
+    return f;
+    API_CATCH(nullptr)
+}
+void* mpas_nc_create(const char* path, int version) {
+    API_TRY
+    auto* f = new nc::File();
+    try { f->create(path, version); } catch (...) { delete f; throw; }
+    return f;
+    API_CATCH(nullptr)
+}
+int mpas_nc_close(void* h) {
+    API_TRY
+    auto* f = (nc::File*)h;
+    try { f->close(); } catch (...) { delete f; throw; }
+    delete f;
+    return 0;
+    API_CATCH(1)
+}
+int mpas_nc_inq(void* h, int* version, int* ndims, int* nvars, int* ngatts, long long* numrecs) {
+    auto* f = (nc::File*)h;
+    *version = f->version; *ndims = (int)f->dims.size(); *nvars = (int)f->vars.size(); *ngatts = (int)f->gatts.size(); *numrecs = f->numrecs;
+    return 0;
+}
+int mpas_nc_dim_info(void* h, int idx, char* name, int name_cap, long long* len) {
+    auto* f = (nc::File*)h;
+    if (idx < 0 || idx >= (int)f->dims.size()) return 1;
+    std::strncpy(name, f->dims[idx].name.c_str(), name_cap - 1);
+    name[name_cap - 1] = 0;
+    *len = f->dims[idx].len;
+    return 0;
+}
+int mpas_nc_var_info(void* h, int idx, char* name, int name_cap, int* type, int* ndims, int* dimids, long long* count) {
+    auto* f = (nc::File*)h;
+    if (idx < 0 || idx >= (int)f->vars.size()) return 1;
+    const nc::Var& v = f->vars[idx];
+    std::strncpy(name, v.name.c_str(), name_cap - 1);
+    name[name_cap - 1] = 0;
+    *type = v.type; *ndims = (int)v.dimids.size();
+    for (size_t i = 0; i < v.dimids.size() && i < 8; ++i) dimids[i] = v.dimids[i];
+    *count = f->var_count(idx);
+    return 0;
+}
+int mpas_nc_gatt_text(void* h, const char* name, char* out, int cap) {
+    auto* f = (nc::File*)h;
+    const nc::Att* a = f->find_gatt(name);
+    if (!a) return 1;
+    std::string t = a->type == nc::NC_CHAR ? a->text() : std::to_string(a->number());
+    std::strncpy(out, t.c_str(), cap - 1);
+    out[cap - 1] = 0;
+    return 0;
+}
+int mpas_nc_get_double(void* h, const char* name, double* out) {
+    API_TRY
+    auto* f = (nc::File*)h;
+    const int id = f->find_var(name);
+    if (id < 0) throw std::runtime_error(std::string("no variable ") + name);
+    f->get_double(id, out);
+    return 0;
+    API_CATCH(1)
+}
+int mpas_nc_get_int(void* h, const char* name, int* out) {
+    API_TRY
+    auto* f = (nc::File*)h;
+    const int id = f->find_var(name);
+    if (id < 0) throw std::runtime_error(std::string("no variable ") + name);
+    f->get_int(id, out);
+    return 0;
+    API_CATCH(1)
+}
+int mpas_nc_def_dim(void* h, const char* name, long long len) {
+    API_TRY
+    return ((nc::File*)h)->def_dim(name, len);
+    API_CATCH(-1)
+}
+int mpas_nc_def_var(void* h, const char* name, int type, int ndims, const int* dimids) {
+    API_TRY
+    return ((nc::File*)h)->def_var(name, type, std::vector<int>(dimids, dimids + ndims));
+    API_CATCH(-1)
+}
+int mpas_nc_put_gatt_text(void* h, const char* name, const char* value) {
+    API_TRY
+    ((nc::File*)h)->put_gatt_text(name, value);
+    return 0;
+    API_CATCH(1)
+}
+int mpas_nc_enddef(void* h, long long numrecs) {
+    API_TRY
+    ((nc::File*)h)->enddef(numrecs);
+    return 0;
+    API_CATCH(1)
+}
+int mpas_nc_put_double(void* h, int varid, long long rec, long long start, long long count, const double* data) {
+    API_TRY
+    ((nc::File*)h)->put_double(varid, rec, start, count, data);
+    return 0;
+    API_CATCH(1)
+}
+int mpas_nc_put_int(void* h, int varid, long long rec, long long start, long long count, const int* data) {
+    API_TRY
+    ((nc::File*)h)->put_int(varid, rec, start, count, data);
+    return 0;
+    API_CATCH(1)
+}
 }  // extern "C"

@@ -43,6 +43,31 @@ def lib():
         _lib.mpas_host_block_nexch.argtypes = [C.c_void_p, C.c_int, C.c_int]
         _lib.mpas_host_block_exch_info.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int] + [C.POINTER(C.c_int)] * 3
         _lib.mpas_host_block_exch_lists.argtypes = [C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
+        # on-disk files (grid / restart / classic netCDF)
+        _lib.mpas_host_case_write_grid.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+        _lib.mpas_host_case_create_from_grid.restype = C.c_void_p
+        _lib.mpas_host_case_create_from_grid.argtypes = [C.c_char_p, C.c_int]
+        _lib.mpas_host_case_create_restart.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.c_char_p, C.c_char_p]
+        _lib.mpas_host_block_write_restart.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        _lib.mpas_host_block_read_restart.argtypes = [C.c_void_p, C.c_char_p]
+        _lib.mpas_nc_open.restype = C.c_void_p
+        _lib.mpas_nc_open.argtypes = [C.c_char_p]
+        _lib.mpas_nc_create.restype = C.c_void_p
+        _lib.mpas_nc_create.argtypes = [C.c_char_p, C.c_int]
+        _lib.mpas_nc_close.argtypes = [C.c_void_p]
+        _lib.mpas_nc_inq.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 4 + [C.POINTER(C.c_longlong)]
+        _lib.mpas_nc_dim_info.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_longlong)]
+        _lib.mpas_nc_var_info.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.c_void_p,
+                                          C.POINTER(C.c_longlong)]
+        _lib.mpas_nc_gatt_text.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p, C.c_int]
+        _lib.mpas_nc_get_double.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
+        _lib.mpas_nc_get_int.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p]
+        _lib.mpas_nc_def_dim.argtypes = [C.c_void_p, C.c_char_p, C.c_longlong]
+        _lib.mpas_nc_def_var.argtypes = [C.c_void_p, C.c_char_p, C.c_int, C.c_int, C.c_void_p]
+        _lib.mpas_nc_put_gatt_text.argtypes = [C.c_void_p, C.c_char_p, C.c_char_p]
+        _lib.mpas_nc_enddef.argtypes = [C.c_void_p, C.c_longlong]
+        _lib.mpas_nc_put_double.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_longlong, C.c_void_p]
+        _lib.mpas_nc_put_int.argtypes = [C.c_void_p, C.c_int, C.c_longlong, C.c_longlong, C.c_longlong, C.c_void_p]
         # device-resident dycore (include/mpas_b200.h, layer 2) and registry (layer 1 lifecycle)
         _lib.mpas_b200_set_device.argtypes = [C.c_int]
         _lib.mpas_b200_register_field.argtypes = [C.c_void_p, C.c_size_t]
@@ -125,6 +150,18 @@ class Block:
         arr = np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ct)), shape=(n,))
         return arr.reshape(tuple(reversed(dims)))
 
+    def write_restart(self, path, names):
+        """this block's OWNED columns of the named fields into a file made by HostCase.create_restart"""
+        if lib().mpas_host_block_write_restart(self.h, str(path).encode(), ",".join(names).encode()):
+            raise RuntimeError(last_error())
+
+    def read_restart(self, path):
+        """every variable of the file that names a pool field (time level 1), owned and halo columns; returns the count"""
+        n = lib().mpas_host_block_read_restart(self.h, str(path).encode())
+        if n < 0:
+            raise RuntimeError(last_error())
+        return n
+
     def cfg(self):
         L = lib()
         out = {}
@@ -154,8 +191,12 @@ class Block:
 class HostCase:
     """Global icosahedral mesh + partition + per-block JW initial state."""
 
-    def __init__(self, level, lloyd_iters=0, sfc=True):
-        self.h = lib().mpas_host_case_create(level, lloyd_iters, 1 if sfc else 0)
+    def __init__(self, level, lloyd_iters=0, sfc=True, grid_file=None):
+        """level: icosahedral subdivision level of the built-in mesh generator; grid_file: read an MPAS grid.nc instead"""
+        if grid_file is not None:
+            self.h = lib().mpas_host_case_create_from_grid(str(grid_file).encode(), 1 if sfc else 0)
+        else:
+            self.h = lib().mpas_host_case_create(level, lloyd_iters, 1 if sfc else 0)
         if not self.h:
             raise RuntimeError(last_error())
         d = [C.c_int() for _ in range(5)]
@@ -171,6 +212,16 @@ class HostCase:
                 self.h = None
         except Exception:
             pass
+
+    def write_grid(self, path, version=2):
+        """the global mesh as an MPAS grid file (netCDF classic: 1 = CDF-1, 2 = CDF-2 / 64-bit offset, 5 = CDF-5)"""
+        if lib().mpas_host_case_write_grid(self.h, str(path).encode(), version):
+            raise RuntimeError(last_error())
+
+    def create_restart(self, path, names, iblock=0, version=2, xtime="0000-01-01_00:00:00"):
+        """header of a restart file for the global mesh; every block then adds its owned columns with Block.write_restart"""
+        if lib().mpas_host_case_create_restart(self.h, iblock, str(path).encode(), version, ",".join(names).encode(), xtime.encode()):
+            raise RuntimeError(last_error())
 
     def permutation(self, kind):
         n = {"cell": self.nCells, "edge": self.nEdges, "vertex": self.nVertices}[kind]
@@ -306,3 +357,99 @@ def nccl_unique_id():
     if rc:
         raise RuntimeError(last_error())
     return buf.raw
+
+
+class NcFile:
+    """Classic netCDF (CDF-1/2/5) through the library's own reader / writer (csrc/host/nc_classic.cpp)."""
+    TYPES = {1: np.int8, 2: "S1", 3: np.int16, 4: np.int32, 5: np.float32, 6: np.float64}
+
+    def __init__(self, path, mode="r", version=2):
+        self.h = lib().mpas_nc_open(str(path).encode()) if mode == "r" else lib().mpas_nc_create(str(path).encode(), version)
+        if not self.h:
+            raise RuntimeError(last_error())
+        self.mode = mode
+        if mode == "r":
+            self._inq()
+
+    def _inq(self):
+        L = lib()
+        v, nd, nv, ng = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+        nr = C.c_longlong()
+        L.mpas_nc_inq(self.h, C.byref(v), C.byref(nd), C.byref(nv), C.byref(ng), C.byref(nr))
+        self.version, self.numrecs = v.value, nr.value
+        name = C.create_string_buffer(256)
+        ln = C.c_longlong()
+        self.dims = []
+        for i in range(nd.value):
+            L.mpas_nc_dim_info(self.h, i, name, 256, C.byref(ln))
+            self.dims.append((name.value.decode(), ln.value))
+        self.vars = {}
+        t, n = C.c_int(), C.c_int()
+        ids = (C.c_int * 8)()
+        cnt = C.c_longlong()
+        for i in range(nv.value):
+            L.mpas_nc_var_info(self.h, i, name, 256, C.byref(t), C.byref(n), ids, C.byref(cnt))
+            shape = tuple(self.numrecs if self.dims[ids[k]][1] == 0 else self.dims[ids[k]][1] for k in range(n.value))
+            self.vars[name.value.decode()] = (t.value, tuple(self.dims[ids[k]][0] for k in range(n.value)), shape, cnt.value)
+
+    def gatt(self, name):
+        out = C.create_string_buffer(1024)
+        if lib().mpas_nc_gatt_text(self.h, name.encode(), out, 1024):
+            raise KeyError(name)
+        return out.value.decode()
+
+    def get(self, name):
+        t, dimnames, shape, cnt = self.vars[name]
+        if t in (5, 6):
+            out = np.empty(cnt, dtype=np.float64)
+            rc = lib().mpas_nc_get_double(self.h, name.encode(), out.ctypes.data)
+        else:
+            out = np.empty(cnt, dtype=np.int32)
+            rc = lib().mpas_nc_get_int(self.h, name.encode(), out.ctypes.data)
+        if rc:
+            raise RuntimeError(last_error())
+        return out.reshape(shape)
+
+    # ---- writing
+    def def_dim(self, name, length):
+        i = lib().mpas_nc_def_dim(self.h, name.encode(), 0 if length is None else int(length))
+        if i < 0:
+            raise RuntimeError(last_error())
+        return i
+
+    def def_var(self, name, nctype, dimids):
+        a = (C.c_int * max(1, len(dimids)))(*dimids)
+        i = lib().mpas_nc_def_var(self.h, name.encode(), nctype, len(dimids), a)
+        if i < 0:
+            raise RuntimeError(last_error())
+        return i
+
+    def put_gatt(self, name, text):
+        if lib().mpas_nc_put_gatt_text(self.h, name.encode(), text.encode()):
+            raise RuntimeError(last_error())
+
+    def enddef(self, numrecs=0):
+        if lib().mpas_nc_enddef(self.h, numrecs):
+            raise RuntimeError(last_error())
+
+    def put(self, varid, data, rec=0, start=0):
+        data = np.ascontiguousarray(data)
+        if data.dtype == np.float64:
+            rc = lib().mpas_nc_put_double(self.h, varid, rec, start, data.size, data.ctypes.data)
+        else:
+            data = np.ascontiguousarray(data, dtype=np.int32)
+            rc = lib().mpas_nc_put_int(self.h, varid, rec, start, data.size, data.ctypes.data)
+        if rc:
+            raise RuntimeError(last_error())
+
+    def close(self):
+        if self.h:
+            h, self.h = self.h, None
+            if lib().mpas_nc_close(h):
+                raise RuntimeError(last_error())
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -294,6 +294,7 @@ void model_init(OModel& m) {
     for (auto& b : m.blocks) {
         Dims d = dims(b);
         Ranges r = ranges(b);
+        if (b.c("config_do_restart", 0) == 0)  // mpas_atm_core.F:389: a restart file already holds the coupled diagnostics
         oracle_init_coupled_diagnostics(d.L, d.mE, d.ns, (int)b.c("index_qv", 1), d.nC, d.nE, RANGES, b.I("cellsOnEdge"), b.I("nEdgesOnCell"), b.I("edgesOnCell"),
                                         b.R("edgesOnCell_sign"), b.R("theta_m@1"), b.R("theta"), b.R("rho_zz@1"), b.R("rho"), b.R("rho_p"), b.R("rho_base"),
                                         b.R("rtheta_base"), b.R("theta_base"), b.R("rtheta_p"), b.R("zz"), b.R("scalars@1"), b.R("ru"), b.R("rw"), b.R("u@1"),
