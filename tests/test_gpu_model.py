@@ -151,3 +151,16 @@ def test_global_minmax_matches_numpy_over_owned_elements():
             lo, hi = min(lo, float(a.min())), max(hi, float(a.max()))
         assert gpu.minmax(name, off, stride) == (lo, hi), name
     assert gpu.max_abs("u@1") == max(abs(v) for v in gpu.minmax("u@1"))
+
+
+@pytest.mark.parametrize("L,max_edges", [(70, 6), (5, 6), (26, 8)])
+def test_odd_shapes_levels_beyond_one_chunk_minimum_levels_wide_strides(L, max_edges, cr_pow, monkeypatch):
+    """nVertLevels > 64 (second 64-level chunk of the warp-per-column kernels), the minimum the stencils allow, and
+    maxEdges = 8 / maxEdges2 = 16 array strides (the NE = 8 instantiations): all fields 1e-12 after 1 and 3 steps"""
+    monkeypatch.setenv("MPAS_B200_MAXEDGES", str(max_edges))
+    case, blocks, gpu, ora = _pair(3, 1, L, 2)
+    assert int(blocks[0].cfg()["maxEdges"]) == max_edges
+    gpu.step(1); ora.step(1)
+    _compare(gpu, ora, blocks, STATE + DIAG, TOL)
+    gpu.step(2); ora.step(2)
+    _compare(gpu, ora, blocks, STATE + DIAG, TOL)

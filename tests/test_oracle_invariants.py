@@ -152,3 +152,31 @@ def test_libm_pow_noise_floor_of_the_reference_arithmetic():
     print("libm vs correctly rounded pow after 10 steps: u %.2e  w %.2e  theta_m %.2e" % (eu, ew, et))
     assert eu < 1e-13 and et < 1e-14
     assert 0 < ew < 1e-9
+
+
+def test_wider_maxEdges_strides_do_not_change_results(monkeypatch):
+    """maxEdges = 8 / maxEdges2 = 16 (the strides of real variable-resolution meshes) on the same icosahedral mesh: only the
+    array layout changes, every result is identical"""
+    out = []
+    for me in (6, 8):
+        monkeypatch.setenv("MPAS_B200_MAXEDGES", str(me))
+        case, blocks = common.make_case(3, 1, nVertLevels=8, num_scalars=2)
+        assert int(blocks[0].cfg()["maxEdges"]) == me and blocks[0].field("edgesOnEdge").shape[1] == 2 * me
+        m = common.OracleModel(blocks, common.level_config(3))
+        m.init()
+        m.step(2)
+        out.append({n: m.field(0, n).copy() for n in ("u@1", "w@1", "theta_m@1", "rho_zz@1", "scalars@1", "uReconstructZonal")})
+    for n in out[0]:
+        assert np.array_equal(out[0][n], out[1][n]), n
+
+
+@pytest.mark.parametrize("L", [5, 70])
+def test_few_and_many_levels_stay_finite_and_conserve_mass(L):
+    case, blocks = common.make_case(3, 1, nVertLevels=L, num_scalars=1)
+    m = common.OracleModel(blocks, common.level_config(3))
+    m.init()
+    m0 = _mass(blocks[0], m, 0)
+    m.step(2)
+    assert abs(_mass(blocks[0], m, 0) - m0) / m0 < 1e-13
+    for n in ("u@1", "w@1", "theta_m@1", "rho_zz@1"):
+        assert np.isfinite(m.field(0, n)).all()
