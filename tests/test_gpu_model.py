@@ -164,3 +164,42 @@ def test_odd_shapes_levels_beyond_one_chunk_minimum_levels_wide_strides(L, max_e
     _compare(gpu, ora, blocks, STATE + DIAG, TOL)
     gpu.step(2); ora.step(2)
     _compare(gpu, ora, blocks, STATE + DIAG, TOL)
+
+
+def _doctor_connectivity(b):
+    """Give every fifth hexagon a seventh edge slot (a copy of its second) and every seventh edge twelve edgesOnEdge entries
+    (copies of its first two).  Geometrically meaningless, but to the kernels it is connectivity like any other: it drives the
+    code paths of 7-sided cells (padded width 8) and of long edgesOnEdge lists that no icosahedral mesh reaches."""
+    ne = b.field("nEdgesOnCell")
+    sel = np.arange(0, ne.shape[0] - 1, 5)
+    sel = sel[ne[sel] == 6]
+    for name in ("edgesOnCell", "cellsOnCell", "verticesOnCell", "edgesOnCell_sign", "kiteForCell", "defc_a", "defc_b", "zb_cell", "zb3_cell",
+                 "coeffs_reconstruct"):
+        a = b.field(name)  # (cell, maxEdges[, x])
+        a[sel, 6] = a[sel, 1]
+    ne[sel] = 7
+    nee = b.field("nEdgesOnEdge")
+    es = np.arange(0, nee.shape[0] - 1, 7)
+    es = es[nee[es] == 10]
+    for name in ("edgesOnEdge", "weightsOnEdge"):
+        a = b.field(name)
+        a[es, 10] = a[es, 0]
+        a[es, 11] = a[es, 1]
+    nee[es] = 12
+    return len(sel), len(es)
+
+
+def test_seven_sided_cells_and_long_edge_lists(cr_pow, monkeypatch):
+    monkeypatch.setenv("MPAS_B200_MAXEDGES", "8")
+    case, blocks = common.make_case(3, 1, nVertLevels=26, num_scalars=3)
+    _tracers(blocks, 3)
+    n7, n12 = _doctor_connectivity(blocks[0])
+    assert n7 > 100 and n12 > 200
+    cfg = common.level_config(3)
+    gpu = common.GpuModel(blocks, cfg)
+    ora = common.OracleModel(blocks, cfg)
+    gpu.init(); ora.init()
+    _compare(gpu, ora, blocks, STATE + DIAG[:12], TOL)
+    for _ in range(2):
+        gpu.step(1); ora.step(1)
+        _compare(gpu, ora, blocks, STATE + DIAG, TOL)
