@@ -192,6 +192,10 @@ void count_launch(int n = 1);
 // phase, TI:592-626; here it lives for the life of the process).  Grows on demand; never call inside stream capture
 // before the first eager step has sized it.
 real* workspace(int slot, size_t count);
+// Per-block persistent workspace keyed by an address that identifies the block; nullptr if it cannot be granted
+// (out of memory, or a first call inside a stream capture): callers then take their workspace-free path.
+real* keyed_workspace(const void* key, size_t count);
+void release_keyed_workspace(const void* key);
 
 // Translate a pointer handed over the C ABI: a registered host address (anywhere inside a
 // registered range) maps to its device mirror; anything else is taken to be a device pointer.

@@ -134,7 +134,7 @@ int add_field(DBlock& blk, const std::string& name, const void* host, int kind, 
         cudaMemset(df.dev, 0, df.bytes);
     }
     auto it = blk.f.find(name);
-    if (it != blk.f.end()) cudaFree(it->second.dev);
+    if (it != blk.f.end() && it->second.owned) cudaFree(it->second.dev);
     blk.f[name] = df;
     return 0;
 }
@@ -176,7 +176,10 @@ void mpas_b200_dycore_destroy(void* h) {
     if (!m) return;
     cudaStreamSynchronize(stream());
     for (auto& b : m->blocks) {
-        for (auto& kv : b.f) cudaFree(kv.second.dev);
+        auto sa = b.f.find("scale_arr");
+        if (sa != b.f.end()) release_keyed_workspace(sa->second.dev);  // the all-scalars mono workspace of this block
+        for (auto& kv : b.f)
+            if (kv.second.owned) cudaFree(kv.second.dev);
         for (auto& kv : b.halo.plans) halo_free_plan(kv.second);
     }
     for (int i = 0; i < 2; ++i)

@@ -17,6 +17,7 @@ struct DField {
     int kind = 0;   // 0 real, 1 int
     int loc = 0;    // 0 none, 1 cell, 2 edge, 3 vertex
     int inner = 1;  // product of all dims but the last
+    bool owned = true;  // false: a view of library workspace (not freed with the block)
     std::vector<long long> dims;
 };
 

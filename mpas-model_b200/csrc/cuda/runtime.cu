@@ -80,6 +80,44 @@ real* workspace(int slot, size_t count) {
     return w.p;
 }
 
+// Per-block workspace (keyed by an address that identifies the block, e.g. its scale_arr): the all-scalars monotonic
+// transport needs num_scalars-wide scratch the reference argument list has no room for, and several blocks of one
+// process run the routine concurrently (one host thread per block), so the slots above cannot be shared.
+namespace {
+std::mutex g_kws_mu;
+std::map<const void*, Ws> g_kws;
+}  // namespace
+real* keyed_workspace(const void* key, size_t count) {
+    std::lock_guard<std::mutex> lk(g_kws_mu);
+    Ws& w = g_kws[key];
+    if (w.count < count) {
+        cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(stream(), &st) == cudaSuccess && st != cudaStreamCaptureStatusNone) return nullptr;  // never allocate inside a capture
+        if (w.p) {
+            cudaStreamSynchronize(stream());
+            cudaFree(w.p);
+            w.p = nullptr;
+            w.count = 0;
+        }
+        if (cudaMalloc(&w.p, count * sizeof(real) + 64) != cudaSuccess) {
+            cudaGetLastError();  // clear the sticky-free allocation error: the caller falls back to the per-scalar path
+            w.p = nullptr;
+            w.count = 0;
+            return nullptr;
+        }
+        cudaMemsetAsync(w.p, 0, count * sizeof(real) + 64, stream());
+        w.count = count;
+    }
+    return w.p;
+}
+void release_keyed_workspace(const void* key) {
+    std::lock_guard<std::mutex> lk(g_kws_mu);
+    auto it = g_kws.find(key);
+    if (it == g_kws.end()) return;
+    if (it->second.p) cudaFree(it->second.p);
+    g_kws.erase(it);
+}
+
 namespace {
 bool g_ktime = false;
 struct KRec {
@@ -284,6 +322,12 @@ int mpas_b200_finalize() {
         if (w.p) cudaFree(w.p);
         w.p = nullptr;
         w.count = 0;
+    }
+    {
+        std::lock_guard<std::mutex> lk2(g_kws_mu);
+        for (auto& kv : g_kws)
+            if (kv.second.p) cudaFree(kv.second.p);
+        g_kws.clear();
     }
     return 0;
 }

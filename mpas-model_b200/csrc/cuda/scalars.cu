@@ -497,6 +497,333 @@ __global__ void __launch_bounds__(256) mono_update_kernel(MonoP p) {
     if (p.bdyMaskCell[iCell - 1] <= MPAS_NSPECZONE) p.scalars_new[IX3(p.iScalar, k, iCell, ns, L)] = fmax((real)0.0, sn);
 }
 
+// ---------------------------------------------------------------------------------------------
+// All scalars in one pass (the default path of mpas_b200_advance_scalars_mono_work).  The reference loops over the
+// scalars (TI:3798-4212) with 2-D working copies; nothing in that loop couples two scalars, so the same arithmetic is
+// done here on the 3-D (num_scalars, nVertLevels, .) layout with the flattened (scalar, level) index e = (k-1)*ns + q-1
+// along the lanes: no working copies, one read of the stencil metadata for all scalars, 4 launches and ONE scale_arr
+// exchange instead of 7 and 1 per scalar.  Scratch lives in the library's per-block workspace:
+//   w_fa, w_fup (ns*L, nEdges+1)   high-order / upwind horizontal flux        (flux_arr, flux_upwind_tmp; flux_tmp is recomputed)
+//   w_wdtn      (ns*(L+1), nCells+1)  dt*wdtn - flux_upwind_arr               (wdtn after TI:3990-3993)
+//   w_snew      (ns*L, nCells+1)   upwind-updated scalar_new                  (TI:3969-4039)
+//   w_scale     (2*ns*L, nCells+1) [scale_in | scale_out] per cell            (scale_arr)
+// s_max / s_min stay in registers.  Every expression and every summation order is the reference's.
+struct MonoNP {
+    int L, mE, ns, nCells;
+    int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, nCellsSolve;
+    real dt, coef_3rd_order;
+    const real *uhAvg, *wwAvg, *rho_zz_old, *rho_lim, *invAreaCell, *dvEdge, *edgesOnCell_sign, *fnm, *fnp, *rdnw, *adv_coefs, *adv_coefs_3rd;
+    const int *cellsOnEdge, *cellsOnCell, *edgesOnCell, *nEdgesOnCell, *nAdvCellsForEdge, *advCellsForEdge, *bdyMaskCell, *bdyMaskEdge;
+    const real* scalars_old;
+    real *scalars_new, *w_fa, *w_fup, *w_wdtn, *w_snew, *w_scale;
+};
+
+__device__ __forceinline__ bool mono_zero_corr(int bm) { return (config_apply_lbcs && (bm == MPAS_NRELAXZONE)) || (bm == MPAS_NRELAXZONE - 1); }
+
+// TI:3916-3961 + 4007-4022 for every scalar of one edge per warp: w_fa = high-order flux (0 off the owned edges),
+// w_fup = upwind flux (all edges).  Two (scalar, level) elements per lane, 10-cell stencil staged as in mono_edge_flux_kernel.
+__global__ void __launch_bounds__(WPB * 32) monoN_edge_flux_kernel(MonoNP p) {
+    __shared__ unsigned s_o[WPB][10];
+    __shared__ real s_cp[WPB][10], s_cm[WPB][10];
+    const int L = p.L, ns = p.ns, nel = L * ns;
+    WARP_ENTITY(p.edgeStart, p.nEdgesLoop);
+    const int iEdge = ent;
+    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    const bool owned = (cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve);
+    const int n = owned ? p.nAdvCellsForEdge[iEdge - 1] : 0;
+    if (n == 10 && lane < 10) {
+        const real c = p.adv_coefs[IX2(lane + 1, iEdge, 15)], c3 = p.adv_coefs_3rd[IX2(lane + 1, iEdge, 15)];
+        s_o[warp][lane] = (unsigned)(p.advCellsForEdge[IX2(lane + 1, iEdge, 15)] - 1) * (unsigned)nel;
+        s_cp[warp][lane] = c + c3;
+        s_cm[warp][lane] = c - c3;
+    }
+    __syncwarp();
+    const real dvdt = p.dvEdge[iEdge - 1] * p.dt;
+    const bool zero_corr = mono_zero_corr(p.bdyMaskEdge[iEdge - 1]);
+    const real* __restrict__ uh = p.uhAvg + (size_t)(iEdge - 1) * L;
+    const real* __restrict__ o1 = p.scalars_old + (size_t)(cell1 - 1) * nel;
+    const real* __restrict__ o2 = p.scalars_old + (size_t)(cell2 - 1) * nel;
+    real* __restrict__ out_fa = p.w_fa + (size_t)(iEdge - 1) * nel;
+    real* __restrict__ out_fup = p.w_fup + (size_t)(iEdge - 1) * nel;
+    for (int ea = lane; ea < nel; ea += 64) {
+        const bool vb = ea + 32 < nel;
+        const int bo = vb ? 32 : 0;
+        const real uh_a = uh[ea / ns], uh_b = uh[(ea + bo) / ns];
+        const real so1_a = o1[ea], so1_b = o1[ea + bo], so2_a = o2[ea], so2_b = o2[ea + bo];
+        real fa_a = 0.0, fa_b = 0.0;
+        if (n == 10) {
+            const real* tab_a = (uh_a > 0) ? s_cp[warp] : s_cm[warp];
+            const real* tab_b = (uh_b > 0) ? s_cp[warp] : s_cm[warp];
+            const real* __restrict__ sp = p.scalars_new + ea;
+            real s_a = 0.0, s_b = 0.0;
+#pragma unroll
+            for (int j = 0; j < 10; j += 5) {
+                real xa[5], xb[5];
+#pragma unroll
+                for (int t = 0; t < 5; ++t) {
+                    const real* __restrict__ q = elem_ptr(sp, s_o[warp][j + t]);
+                    xa[t] = q[0];
+                    xb[t] = q[bo];
+                }
+#pragma unroll
+                for (int t = 0; t < 5; ++t) {
+                    const real ta = tab_a[j + t] * xa[t], tb = tab_b[j + t] * xb[t];
+                    if (j == 0 && t == 0) {  // the first term is assigned (TI:3928), not added to zero
+                        s_a = ta;
+                        s_b = tb;
+                    } else {
+                        s_a = s_a + ta;
+                        s_b = s_b + tb;
+                    }
+                }
+            }
+            fa_a = uh_a * s_a;
+            fa_b = uh_b * s_b;
+        } else if (n > 0) {
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int e = ea + (h ? bo : 0);
+                const real uhv = h ? uh_b : uh_a;
+                const real s3 = fsign((real)1.0, uhv);
+                real fa = 0.0;
+                for (int i = 1; i <= n; ++i) {
+                    const real scalar_weight = uhv * (p.adv_coefs[IX2(i, iEdge, 15)] + s3 * p.adv_coefs_3rd[IX2(i, iEdge, 15)]);
+                    fa = fa + scalar_weight * p.scalars_new[(size_t)(p.advCellsForEdge[IX2(i, iEdge, 15)] - 1) * nel + e];
+                }
+                if (h) fa_b = fa;
+                else fa_a = fa;
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const real uhv = h ? uh_b : uh_a;
+            real fa = h ? fa_b : fa_a;
+            const real fup = dvdt * (fmax((real)0.0, uhv) * (h ? so1_b : so1_a) + fmin((real)0.0, uhv) * (h ? so2_b : so2_a));
+            if (zero_corr) fa = fup;  // TI:4017-4021
+            out_fa[ea + 32 * h] = fa;
+            out_fup[ea + 32 * h] = fup;
+        }
+    }
+}
+
+// One horizontal batch of the limiter kernel: CNT edges starting at table slot I0, both elements of the lane.
+// All loads first, then the reference's three accumulations per edge (TI:4024-4039) with flux_tmp = dt*fa - fup
+// recomputed (TI:4012); s_sT carries a zero where the reference zeroes flux_tmp (TI:4017-4021).
+#define MONO_EDGE_BATCH(I0, CNT)                                                        \
+    {                                                                                   \
+        real xa[CNT], xb[CNT], ya[CNT], yb[CNT];                                        \
+        _Pragma("unroll") for (int t = 0; t < CNT; ++t) {                               \
+            const real* __restrict__ qf = elem_ptr(fa_base, s_eF[warp][(I0) + t]);      \
+            const real* __restrict__ qu = elem_ptr(fup_base, s_eF[warp][(I0) + t]);     \
+            xa[t] = qf[0];                                                              \
+            xb[t] = qf[bo];                                                             \
+            ya[t] = qu[0];                                                              \
+            yb[t] = qu[bo];                                                             \
+        }                                                                               \
+        _Pragma("unroll") for (int t = 0; t < CNT; ++t) {                               \
+            const real sg = s_sign[warp][(I0) + t], sT = s_sT[warp][(I0) + t];          \
+            sn_a = sn_a - sg * ya[t] * invArea;                                         \
+            sn_b = sn_b - sg * yb[t] * invArea;                                         \
+            const real sfa = sT * (p.dt * xa[t] - ya[t]), sfb = sT * (p.dt * xb[t] - yb[t]); \
+            so_a = so_a - fmax((real)0.0, sfa) * invArea;                               \
+            so_b = so_b - fmax((real)0.0, sfb) * invArea;                               \
+            si_a = si_a - fmin((real)0.0, sfa) * invArea;                               \
+            si_b = si_b - fmin((real)0.0, sfb) * invArea;                               \
+        }                                                                               \
+    }
+#define MONO_NBR_BATCH(I0, CNT)                                                         \
+    {                                                                                   \
+        real xa[CNT], xb[CNT];                                                          \
+        _Pragma("unroll") for (int t = 0; t < CNT; ++t) {                               \
+            const real* __restrict__ q = elem_ptr(old_base, s_cF[warp][(I0) + t]);      \
+            xa[t] = q[0];                                                               \
+            xb[t] = q[bo];                                                              \
+        }                                                                               \
+        _Pragma("unroll") for (int t = 0; t < CNT; ++t) {                               \
+            mx_a = fmax(mx_a, xa[t]);                                                   \
+            mn_a = fmin(mn_a, xa[t]);                                                   \
+            mx_b = fmax(mx_b, xb[t]);                                                   \
+            mn_b = fmin(mn_b, xb[t]);                                                   \
+        }                                                                               \
+    }
+
+// TI:3843-3908 (vertical high-order flux, bounds), 3969-4000 (vertical upwind update), 4024-4076 (horizontal
+// accumulation, scale factors) for every scalar of one owned cell per warp.  The cell's scalars_new / scalars_old blocks
+// and its wwAvg column are staged by bulk (TMA) copies; the rewritten vertical flux dt*wdtn - flux_upwind_arr goes to
+// shared memory (and to w_wdtn for the final update); the edge sums and the cellsOnCell bounds are direct gathers with the
+// edge / neighbour lists staged as offsets, padded to 6 or 8 with zero signs (x - 0*y == x) and the cell itself
+// (max/min are idempotent).
+// dynamic shared memory per warp: 2*tma_slot(ns*L) + tma_slot(L+1) + ns*(L+1) reals.
+__global__ void __launch_bounds__(WPB * 32, 4) monoN_cell_kernel(MonoNP p) {
+    extern __shared__ __align__(16) real s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar[WPB];
+    __shared__ unsigned s_eF[WPB][8], s_cF[WPB][8];
+    __shared__ real s_sign[WPB][8], s_sT[WPB][8];
+    const int L = p.L, L1 = L + 1, mE = p.mE, ns = p.ns, nel = L * ns, nel1 = ns * L1;
+    const int slotS = tma_slot(nel), slotW = tma_slot(L1), per_warp = 2 * slotS + slotW + ((nel1 + 3) & ~3);
+    const real eps = 1.e-20;
+    WARP_ENTITY(p.cellSolveStart, p.nCellsSolveLoop);
+    const int iCell = ent;
+    real* sc = s_dyn + (size_t)warp * per_warp;
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
+    const real* g_new = p.scalars_new + (size_t)(iCell - 1) * nel;
+    const real* g_old = p.scalars_old + (size_t)(iCell - 1) * nel;
+    const real* g_ww = p.wwAvg + (size_t)(iCell - 1) * L1;
+    if (lane == 0) {
+        mbar_init(mbar, 1);
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc);
+        unsigned total = 0;
+        tma_issue_col(s0, g_new, nel, mbar, total);
+        tma_issue_col(s0 + (unsigned)(slotS * sizeof(real)), g_old, nel, mbar, total);
+        tma_issue_col(s0 + (unsigned)(2 * slotS * sizeof(real)), g_ww, L1, mbar, total);
+        mbar_arrive_expect_tx(mbar, total);
+    }
+    const real* s_new = sc + tma_shift(g_new);                  // s_new[(k-1)*ns + q-1]
+    const real* s_old = sc + slotS + tma_shift(g_old);          // s_old[(k-1)*ns + q-1]
+    const real* s_ww = sc + 2 * slotS + tma_shift(g_ww) - 1;    // s_ww[kk], kk = 1..L+1
+    real* wd = sc + 2 * slotS + slotW;                          // wd[(kk-1)*ns + q-1], kk = 1..L+1
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const int npad = ne <= 6 ? 6 : 8;
+    if (lane < npad) {
+        const bool in = lane < ne;
+        const int iEdge = p.edgesOnCell[IX2(in ? lane + 1 : 1, iCell, mE)];
+        const int cc = in ? p.cellsOnCell[IX2(lane + 1, iCell, mE)] : iCell;
+        s_eF[warp][lane] = (unsigned)(iEdge - 1) * (unsigned)nel;
+        s_cF[warp][lane] = (unsigned)(cc - 1) * (unsigned)nel;
+        const real sg = in ? p.edgesOnCell_sign[IX2(lane + 1, iCell, mE)] : (real)0.0;
+        s_sign[warp][lane] = sg;
+        s_sT[warp][lane] = mono_zero_corr(p.bdyMaskEdge[iEdge - 1]) ? (real)0.0 : sg;
+    }
+    const real invArea = p.invAreaCell[iCell - 1];
+    __syncwarp();
+    mbar_wait(mbar, 0);
+    // ---- vertical high-order flux at every (scalar, interface) (TI:3843-3876, branch-free) and its rewrite
+    //      wdtn(k) = dt*wdtn(k) - flux_upwind_arr(k), k = 2..L (TI:3977-3993); interfaces 1 and L+1 stay 0
+    real* __restrict__ g_wd = p.w_wdtn + (size_t)(iCell - 1) * nel1;
+    for (int t = lane; t < nel1; t += 32) {
+        const int kk = t / ns + 1, q0 = t - (kk - 1) * ns;
+        const int k = min(max(kk, 2), L);
+        const int km2 = max(k - 2, 1), kp1 = min(k + 1, L);
+        const real ww = s_ww[k];
+        const real x_m2 = s_new[(km2 - 1) * ns + q0], x_m1 = s_new[(k - 2) * ns + q0], x_c = s_new[(k - 1) * ns + q0], x_p1 = s_new[(kp1 - 1) * ns + q0];
+        const real f3 = flux3(x_m2, x_m1, x_c, x_p1, ww, p.coef_3rd_order);
+        const real f2 = ww * (p.fnm[k - 1] * x_c + p.fnp[k - 1] * x_m1);
+        const real f = (k == 2 || k == L) ? f2 : f3;
+        const real fu = p.dt * (fmax((real)0.0, ww) * s_old[(k - 2) * ns + q0] + fmin((real)0.0, ww) * s_old[(k - 1) * ns + q0]);
+        const real w = (kk == 1 || kk == L1) ? (real)0.0 : (p.dt * f - fu);
+        wd[t] = w;
+        g_wd[t] = w;
+    }
+    __syncwarp();
+    const real* __restrict__ rho_old_col = p.rho_zz_old + (size_t)(iCell - 1) * L;
+    const real* __restrict__ rho_lim_col = p.rho_lim + (size_t)(iCell - 1) * L;
+    real* __restrict__ snew_col = p.w_snew + (size_t)(iCell - 1) * nel;
+    real* __restrict__ scale_col = p.w_scale + (size_t)(iCell - 1) * 2 * nel;
+    for (int ea = lane; ea < nel; ea += 64) {
+        const bool vb = ea + 32 < nel;
+        const int bo = vb ? 32 : 0;
+        const int ka = ea / ns, kb = (ea + bo) / ns;  // 0-based levels
+        real sn_a, sn_b, si_a, si_b, so_a, so_b, mx_a, mx_b, mn_a, mn_b;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const int e = ea + (h ? bo : 0), k0 = h ? kb : ka, q0 = e - k0 * ns;
+            const real so = s_old[e];
+            const real so_m = s_old[max(e - ns, q0)], so_p = s_old[min(e + ns, nel - ns + q0)];
+            const real ww_k = s_ww[k0 + 1], ww_kp = s_ww[k0 + 2];
+            const real rd = p.rdnw[k0];
+            real sn = so * rho_old_col[k0];
+            const real fu_k = p.dt * (fmax((real)0.0, ww_k) * so_m + fmin((real)0.0, ww_k) * so);     // flux_upwind_arr(k),   k >= 2
+            const real fu_kp = p.dt * (fmax((real)0.0, ww_kp) * so + fmin((real)0.0, ww_kp) * so_p);  // flux_upwind_arr(k+1), k <= L-1
+            if (k0 <= L - 2) sn = sn - fu_kp * rd;
+            if (k0 >= 1) sn = sn + fu_k * rd;
+            const real wd_k = wd[e], wd_kp = wd[e + ns];
+            const real si = -rd * (fmin((real)0.0, wd_kp) - fmax((real)0.0, wd_k));
+            const real sout = -rd * (fmax((real)0.0, wd_kp) - fmin((real)0.0, wd_k));
+            real mx, mn;
+            if (k0 == 0) {
+                mx = fmax(so, so_p);
+                mn = fmin(so, so_p);
+            } else if (k0 == L - 1) {
+                mx = fmax(so, so_m);
+                mn = fmin(so, so_m);
+            } else {
+                mx = fmax(fmax(so_m, so), so_p);
+                mn = fmin(fmin(so_m, so), so_p);
+            }
+            if (h) { sn_b = sn; si_b = si; so_b = sout; mx_b = mx; mn_b = mn; }
+            else { sn_a = sn; si_a = si; so_a = sout; mx_a = mx; mn_a = mn; }
+        }
+        const real* __restrict__ fa_base = p.w_fa + ea;
+        const real* __restrict__ fup_base = p.w_fup + ea;
+        const real* __restrict__ old_base = p.scalars_old + ea;
+        MONO_EDGE_BATCH(0, 3)
+        MONO_EDGE_BATCH(3, 3)
+        if (npad > 6) MONO_EDGE_BATCH(6, 2)
+        MONO_NBR_BATCH(0, 6)
+        if (npad > 6) MONO_NBR_BATCH(6, 2)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const int e = ea + 32 * h, k0 = h ? kb : ka;
+            const real sn = h ? sn_b : sn_a, rl = rho_lim_col[k0];
+            snew_col[e] = sn;
+            real scale_factor = ((h ? mx_b : mx_a) * rl - sn) / ((h ? si_b : si_a) + eps);
+            scale_col[e] = fmin((real)1.0, fmax((real)0.0, scale_factor));
+            scale_factor = ((h ? mn_b : mn_a) * rl - sn) / ((h ? so_b : so_a) - eps);
+            scale_col[nel + e] = fmin((real)1.0, fmax((real)0.0, scale_factor));
+        }
+    }
+}
+#undef MONO_EDGE_BATCH
+#undef MONO_NBR_BATCH
+
+// TI:4102-4138 for every scalar: limited perturbation flux on the edges of owned cells, one thread per (scalar, level, edge).
+// The upwind flux is the value stored by monoN_edge_flux_kernel (the reference recomputes the same expression).
+__global__ void __launch_bounds__(256) monoN_rescale_edge_kernel(MonoNP p) {
+    const int nel = p.L * p.ns;
+    FLAT_KC(p.nEdgesLoop, nel);
+    const int iEdge = p.edgeStart + _c0, e = k - 1;
+    const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+    if (!(cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve)) return;
+    const size_t ie = (size_t)(iEdge - 1) * nel + e;
+    real flux = p.dt * p.w_fa[ie] - p.w_fup[ie];
+    if (mono_zero_corr(p.bdyMaskEdge[iEdge - 1])) flux = 0.;
+    const real* __restrict__ s1 = p.w_scale + (size_t)(cell1 - 1) * 2 * nel + e;  // [0] scale_in, [nel] scale_out
+    const real* __restrict__ s2 = p.w_scale + (size_t)(cell2 - 1) * 2 * nel + e;
+    flux = fmax((real)0.0, flux) * fmin(s1[nel], s2[0]) + fmin((real)0.0, flux) * fmin(s1[0], s2[nel]);
+    p.w_fa[ie] = flux;
+}
+
+// TI:4145-4210 for every scalar: limited vertical fluxes, final update of the owned cells, store (clamped at zero) for
+// all cells -- cells outside the owned range keep their predictor value, as the reference's scalar_new copy does.
+__global__ void __launch_bounds__(256) monoN_update_kernel(MonoNP p) {
+    const int L = p.L, mE = p.mE, ns = p.ns, nel = L * ns;
+    FLAT_KC(p.nCellsLoop, nel);
+    const int iCell = p.cellStart + _c0, e = k - 1, k0 = e / ns;
+    const size_t is = (size_t)(iCell - 1) * nel + e;
+    real sn;
+    if (iCell >= p.cellSolveStart && iCell < p.cellSolveStart + p.nCellsSolveLoop) {
+        sn = p.w_snew[is];
+        const real* __restrict__ sc = p.w_scale + (size_t)(iCell - 1) * 2 * nel;  // [e'] scale_in, [nel + e'] scale_out
+        const real* __restrict__ wdc = p.w_wdtn + (size_t)(iCell - 1) * (size_t)(ns * (L + 1));
+        real wlo = wdc[e], whi = wdc[e + ns];
+        const real in_k = sc[e], out_k = sc[nel + e];
+        if (k0 >= 1) wlo = fmax((real)0.0, wlo) * fmin(sc[nel + e - ns], in_k) + fmin((real)0.0, wlo) * fmin(out_k, sc[e - ns]);
+        if (k0 <= L - 2) whi = fmax((real)0.0, whi) * fmin(out_k, sc[e + ns]) + fmin((real)0.0, whi) * fmin(sc[nel + e + ns], in_k);
+        const int ne = p.nEdgesOnCell[iCell - 1];
+        const real invArea = p.invAreaCell[iCell - 1];
+        for (int i = 1; i <= ne; ++i) {
+            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
+            sn = sn - p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.w_fa[(size_t)(iEdge - 1) * nel + e] * invArea;
+        }
+        sn = (sn + (-p.rdnw[k0] * (whi - wlo))) / p.rho_lim[IX2(k0 + 1, iCell, L)];
+    } else {
+        sn = p.scalars_new[is];
+    }
+    if (p.bdyMaskCell[iCell - 1] <= MPAS_NSPECZONE) p.scalars_new[is] = fmax((real)0.0, sn);
+}
+
 }  // namespace
 
 extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
@@ -558,6 +885,45 @@ extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
         KLAUNCH(mono_rho_int_kernel, (long long)p.nCellsLoop * L, 256, p);
         KCHECK("mono_rho_int_kernel");
     }
+    // ---- all scalars at once (default): needs the per-block workspace and the 6/8-slot edge tables
+    if (tune("mono_fused", 1) && maxEdges <= 8 && p.nCellsLoop > 0) {
+        const size_t nel = (size_t)L * p.ns, nel1 = (size_t)(L + 1) * p.ns, nC1 = (size_t)nCells + 1, nE1 = (size_t)nEdges + 1;
+        const size_t n_edge = (nel * nE1 + 1) & ~(size_t)1, n_wd = (nel1 * nC1 + 1) & ~(size_t)1, n_cell = (nel * nC1 + 1) & ~(size_t)1;
+        const size_t shm = (size_t)WPB * (2 * tma_slot((int)nel) + tma_slot(L + 1) + (((int)nel1 + 3) & ~3)) * sizeof(real);
+        const bool fits = ensure_dyn_smem((const void*)monoN_cell_kernel, shm);
+        real* ws = fits ? keyed_workspace(X(scale_arr), 2 * n_edge + n_wd + 3 * n_cell) : nullptr;
+        // no silent fallback: ranks / blocks taking different paths would post different numbers of exchanges
+        if (fits && !ws)
+            return fail_msg("mpas_b200_advance_scalars_mono_work: cannot allocate the all-scalars workspace (" +
+                            std::to_string((2 * n_edge + n_wd + 3 * n_cell) * sizeof(real) >> 20) +
+                            " MiB; first call must be outside stream capture); MPAS_B200_TUNE_mono_fused=0 selects the per-scalar path");
+        if (ws) {
+            MonoNP q;
+            q.L = p.L; q.mE = p.mE; q.ns = p.ns; q.nCells = nCells; q.cellStart = p.cellStart; q.nCellsLoop = p.nCellsLoop;
+            q.cellSolveStart = p.cellSolveStart; q.nCellsSolveLoop = p.nCellsSolveLoop; q.edgeStart = p.edgeStart; q.nEdgesLoop = p.nEdgesLoop;
+            q.nCellsSolve = p.nCellsSolve; q.dt = p.dt; q.coef_3rd_order = p.coef_3rd_order;
+            q.uhAvg = p.uhAvg; q.wwAvg = p.wwAvg; q.rho_zz_old = p.rho_zz_old; q.rho_lim = p.rho_lim; q.invAreaCell = p.invAreaCell; q.dvEdge = p.dvEdge;
+            q.edgesOnCell_sign = p.edgesOnCell_sign; q.fnm = p.fnm; q.fnp = p.fnp; q.rdnw = p.rdnw; q.adv_coefs = p.adv_coefs; q.adv_coefs_3rd = p.adv_coefs_3rd;
+            q.cellsOnEdge = p.cellsOnEdge; q.cellsOnCell = p.cellsOnCell; q.edgesOnCell = p.edgesOnCell; q.nEdgesOnCell = p.nEdgesOnCell;
+            q.nAdvCellsForEdge = p.nAdvCellsForEdge; q.advCellsForEdge = p.advCellsForEdge; q.bdyMaskCell = p.bdyMaskCell; q.bdyMaskEdge = p.bdyMaskEdge;
+            q.scalars_old = p.scalars_old; q.scalars_new = p.scalars_new;
+            q.w_fa = ws; q.w_fup = ws + n_edge; q.w_wdtn = ws + 2 * n_edge; q.w_snew = q.w_wdtn + n_wd; q.w_scale = q.w_snew + n_cell;
+            WLAUNCH(monoN_edge_flux_kernel, q.nEdgesLoop, 0, q);
+            KCHECK("monoN_edge_flux_kernel");
+            WLAUNCH(monoN_cell_kernel, q.nCellsSolveLoop, shm, q);
+            KCHECK("monoN_cell_kernel");
+            if (halo_fn) {
+                int rc = halo_fn(halo_ctx, 2, q.w_scale);  // TI:4098, all scalars in one message
+                if (rc) return rc;
+            }
+            KLAUNCH(monoN_rescale_edge_kernel, (long long)q.nEdgesLoop * (long long)nel, 256, q);
+            KCHECK("monoN_rescale_edge_kernel");
+            KLAUNCH(monoN_update_kernel, (long long)q.nCellsLoop * (long long)nel, 256, q);
+            KCHECK("monoN_update_kernel");
+            return 0;
+        }
+    }
+    // ---- one scalar at a time with the reference's 2-D scratch arrays (TI:3798-4212)
     for (int iScalar = 1; iScalar <= num_scalars; ++iScalar) {
         p.iScalar = iScalar;
         KLAUNCH(mono_copy_kernel, (long long)(p.nCellsLoop + 1) * L, 256, p);

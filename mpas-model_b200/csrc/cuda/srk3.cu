@@ -234,15 +234,27 @@ struct MonoCtx {
     Dycore* m;
     int iblock;
 };
-int mono_halo(void* ctx, int which, real* /*array*/) {
+int mono_halo(void* ctx, int which, real* array) {
     MonoCtx* c = (MonoCtx*)ctx;
     Dycore* m = c->m;
     const bool threaded = m->blocks.size() > 1;
+    if (which == 2) {
+        // all-scalars scale factors (2*num_scalars*nVertLevels, nCells+1) in the library's per-block workspace: a view,
+        // registered by every block's thread before the barrier
+        DBlock& b = m->blocks[c->iblock];
+        Dims d = dims(b);
+        DField df;
+        df.dev = array; df.kind = 0; df.loc = 1; df.inner = 2 * d.ns * d.L; df.owned = false;
+        df.dims = {2LL * d.ns * d.L, (long long)d.nC + 1};
+        df.bytes = (size_t)df.inner * (size_t)(d.nC + 1) * sizeof(real);
+        b.f["mono_scale_all"] = df;
+    }
     if (threaded) m->bar.wait();
     int rc = 0;
     if (c->iblock == 0) {
         try {
             if (which == 0) rc = dycore_exchange(*m, {{"scalars@1", 0}});
+            else if (which == 2) rc = dycore_exchange(*m, {{"mono_scale_all", 1}});
             else rc = dycore_exchange(*m, {{"scale_arr", 1}});
         } catch (const std::exception& e) {
             m->err = e.what();

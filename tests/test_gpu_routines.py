@@ -3,6 +3,8 @@
 state; every real field of the pool is then compared.  With FMA contraction off on both sides and gathers in
 the reference's order the kernels are expected to be BIT-exact; the only exception is pow() in
 recover(rk_step=3) / init_coupled, where CUDA's and glibc's pow may differ in the last place."""
+import os
+
 import numpy as np
 import pytest
 
@@ -56,6 +58,8 @@ def _check(blocks, gpu, ora, exact=True, tol=0.0, skip=("wdtn",)):
     assert not bad, bad
 
 
+MONO_SCRATCH = ("scalar_old", "scalar_new", "s_max", "s_min", "scale_arr", "flux_arr", "flux_upwind_tmp", "flux_tmp")
+
 CASES = [
     ("divdamp", lambda c: (c["config_dt"] / 6,)),
     ("acoustic", lambda c: (c["config_dt"] / 6, 2)),
@@ -72,6 +76,8 @@ CASES = [
     ("advance_scalars", lambda c: (c["config_dt"], 3, 2, 0)),
     ("mono", lambda c: (c["config_dt"], 1)),
     ("mono", lambda c: (c["config_dt"], 0)),
+    ("mono_per_scalar", lambda c: (c["config_dt"], 1)),
+    ("mono_per_scalar", lambda c: (c["config_dt"], 0)),
     ("substep_finish", lambda c: (1, 3)),
     ("substep_finish", lambda c: (2, 3)),
     ("substep_finish", lambda c: (3, 3)),
@@ -88,8 +94,26 @@ def test_state_upload_is_identical(state):
 def test_routine_bit_exact(state, routine, params):
     blocks, cfg, gpu, ora = state
     p = params(cfg)
+    if routine == "mono_per_scalar":
+        # the reference-shaped path: one scalar at a time through the 2-D scratch arguments, every scratch array compared
+        os.environ["MPAS_B200_TUNE_mono_fused"] = "0"
+        try:
+            gpu.call("mono", *p)
+        finally:
+            del os.environ["MPAS_B200_TUNE_mono_fused"]
+        ora.call("mono", *p)
+        _check(blocks, gpu, ora)
+        return
     gpu.call(routine, *p)
     ora.call(routine, *p)
+    if routine == "mono":
+        # default path: all scalars in one pass over library workspace; the 2-D per-scalar scratch arguments
+        # (allocated and freed around the call by atm_srk3, TI:1029-1099) are not touched -- outputs are compared
+        _check(blocks, gpu, ora, skip=("wdtn",) + MONO_SCRATCH)
+        for ib in range(len(blocks)):
+            for n in MONO_SCRATCH:
+                gpu.set_field(ib, n, ora.field(ib, n))  # later tests compare every field bit for bit
+        return
     # ke_edge is scratch the GPU path writes from the edge kernel only (same values); gradPV* are outputs
     _check(blocks, gpu, ora)
 
