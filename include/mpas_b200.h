@@ -36,6 +36,9 @@ int mpas_b200_download(void* host);
 void* mpas_b200_device_ptr(const void* host);
 int mpas_b200_synchronize(void);
 long long mpas_b200_launch_count(void);
+/* sizeof(mpas_real) of this build: 8 (default) or 4 (PRECISION=single, libmpas_b200_sp.so built with -DSINGLE_PRECISION;
+ * the reference's RKIND switch, src/framework/mpas_kind_types.F:25-29) */
+int mpas_b200_real_size(void);
 int mpas_b200_timer_start(void);    /* CUDA-event stopwatch on the library stream */
 double mpas_b200_timer_stop(void);  /* elapsed ms since timer_start, after synchronising */
 int mpas_b200_ktime_enable(int on);                /* per-kernel CUDA-event timing of eager launches */

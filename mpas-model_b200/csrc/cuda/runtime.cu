@@ -271,6 +271,7 @@ int mpas_b200_synchronize() {
 }
 
 long long mpas_b200_launch_count() { return launches(); }
+int mpas_b200_real_size() { return (int)sizeof(real); }
 
 // CUDA-event stopwatch on the library stream (bench.py times the step loop with it: torch.cuda.Event only sees
 // torch's current stream)

@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) as_cell_kernel(AsP p) {
     __shared__ unsigned s_eL[WPB][8], s_eF[WPB][8];
     __shared__ real s_sign[WPB][8];
     const int L = p.L, L1 = L + 1, mE = p.mE, ns = p.ns, nel = L * ns;
-    const int slotS = tma_slot(nel), slotW = tma_slot(L1), per_warp = slotS + slotW + ((ns * L1 + 1) & ~1);  // multiple of 16 bytes
+    const int slotS = tma_slot(nel), slotW = tma_slot(L1), per_warp = slotS + slotW + ((ns * L1 + 3) & ~3);  // multiple of 16 bytes in either precision
     WARP_ENTITY(p.cellSolveStart, p.nCellsSolveLoop);
     const int iCell = ent;
     if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) return;
@@ -851,7 +851,7 @@ extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
     KCHECK("as_edge_kernel");
     if (p.nCellsSolveLoop > 0) {
         if (p.mE > 8) return fail_msg("mpas_b200_advance_scalars_work: maxEdges > 8 not supported");
-        const size_t shm = (size_t)WPB * (tma_slot(p.L * p.ns) + tma_slot(p.L + 1) + ((p.ns * (p.L + 1) + 1) & ~1)) * sizeof(real);
+        const size_t shm = (size_t)WPB * (tma_slot(p.L * p.ns) + tma_slot(p.L + 1) + ((p.ns * (p.L + 1) + 3) & ~3)) * sizeof(real);
         WLAUNCH(as_cell_kernel, p.nCellsSolveLoop, shm, p);
         KCHECK("as_cell_kernel");
     }

@@ -10,7 +10,11 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libmpas_b200.so")
+# MPAS_B200_PRECISION=single selects the PRECISION=single build (RKIND = 4 bytes, mpas_kind_types.F:25-29): the same
+# sources compiled with -DSINGLE_PRECISION.  The host harness inside it stays double; real fields are converted on
+# upload (dycore.cu: add_field) and by Dycore.field / set_field below.  One precision per process.
+SINGLE = os.environ.get("MPAS_B200_PRECISION", "double").lower() in ("single", "sp", "4")
+LIB_PATH = os.path.join(_HERE, "libmpas_b200_sp.so" if SINGLE else "libmpas_b200.so")
 _lib = None
 
 
@@ -22,6 +26,8 @@ def lib():
                 f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
                 "(there is no CPU fallback)")
         _lib = C.CDLL(LIB_PATH, mode=C.RTLD_GLOBAL)
+        if _lib.mpas_b200_real_size() != (4 if SINGLE else 8):
+            raise RuntimeError(f"{LIB_PATH}: sizeof(mpas_real) = {_lib.mpas_b200_real_size()} does not match MPAS_B200_PRECISION")
         _lib.mpas_b200_last_error.restype = C.c_char_p
         _lib.mpas_host_case_create.restype = C.c_void_p
         _lib.mpas_host_case_create.argtypes = [C.c_int, C.c_int, C.c_int]
@@ -298,6 +304,13 @@ class Dycore:
     def field(self, ib, name, out=None):
         kind, loc, dims = self.blocks[ib].info(name)
         shape = tuple(reversed(dims))
+        if SINGLE and kind == 0:  # device mirror is float32; callers see float64 like the host pools
+            tmp = np.empty(shape, dtype=np.float32)
+            self._chk(lib().mpas_b200_dycore_get_field(self.h, ib, name.encode(), tmp.ctypes.data, tmp.nbytes))
+            if out is None:
+                return tmp.astype(np.float64)
+            out[...] = tmp
+            return out
         if out is None:
             out = np.empty(shape, dtype=np.float64 if kind == 0 else np.int32)
         self._chk(lib().mpas_b200_dycore_get_field(self.h, ib, name.encode(), out.ctypes.data, out.nbytes))
@@ -305,6 +318,8 @@ class Dycore:
 
     def set_field(self, ib, name, arr):
         arr = np.ascontiguousarray(arr)
+        if SINGLE and arr.dtype == np.float64:
+            arr = arr.astype(np.float32)
         self._chk(lib().mpas_b200_dycore_set_field(self.h, ib, name.encode(), arr.ctypes.data, arr.nbytes))
         self.sync()
 

@@ -23,6 +23,15 @@ def test_library_loads_and_exports_every_declared_symbol():
     assert not missing, missing
 
 
+def test_single_precision_library_exports_the_same_abi_with_4_byte_reals():
+    """libmpas_b200_sp.so = the same sources with -DSINGLE_PRECISION (PRECISION=single, mpas_kind_types.F:25-29)."""
+    L = ctypes.CDLL(os.path.join(common.PKG, "libmpas_b200_sp.so"), mode=ctypes.RTLD_LOCAL)
+    missing = [n for n in _declared() if not hasattr(L, n)]
+    assert not missing, missing
+    assert L.mpas_b200_real_size() == 4
+    assert common.host.lib().mpas_b200_real_size() == 8
+
+
 def test_no_compute_without_gpu_is_loud():
     if common.has_gpu():
         return
