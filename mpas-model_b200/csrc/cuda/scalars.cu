@@ -23,7 +23,16 @@ namespace {
 
 const bool config_apply_lbcs = false;  // regional LBCs are out of scope
 
+// x / ns for the small flattened (scalar, level) indices of this file without the ~20-instruction run-time division:
+// magic = floor(2^32 / ns) + 1 gives the exact quotient for x * ns < 2^32 (ns = 1 is passed through).
+struct FastDiv {
+    unsigned d, magic;
+    __host__ void set(int ns) { d = (unsigned)ns; magic = ns > 1 ? (unsigned)(0x100000000ULL / (unsigned)ns) + 1u : 0u; }
+    __device__ __forceinline__ int operator()(int x) const { return d == 1 ? x : (int)__umulhi((unsigned)x, magic); }
+};
+
 struct AsP {
+    FastDiv nsdiv;
     int L, mE, ns, edgeStart, nEdgesLoop, cellSolveStart, nCellsSolveLoop;
     real dt, coef_3rd_order, weight_time_old, weight_time_new;
     const real *scalar_old, *rho_zz_old, *rho_zz_new, *uhAvg, *wwAvg, *edgesOnCell_sign, *invAreaCell, *fnm, *fnp, *rdnw, *adv_coefs, *adv_coefs_3rd;
@@ -61,8 +70,8 @@ __global__ void __launch_bounds__(WPB * 32) as_edge_kernel(AsP p) {
     for (int ea = lane; ea < nel; ea += 64) {
         const bool vb = ea + 32 < nel;
         const int bo = vb ? 32 : 0;
-        const real* tab_a = signbit(uh[ea / ns]) ? s_cm[warp] : s_cp[warp];
-        const real* tab_b = signbit(uh[(ea + bo) / ns]) ? s_cm[warp] : s_cp[warp];
+        const real* tab_a = signbit(uh[p.nsdiv(ea)]) ? s_cm[warp] : s_cp[warp];
+        const real* tab_b = signbit(uh[p.nsdiv(ea + bo)]) ? s_cm[warp] : s_cp[warp];
         const real* __restrict__ sp = p.scalar_new + ea;
         real s_a = 0.0, s_b = 0.0;
         for (int j = 0; j < npad; j += 5) {
@@ -138,7 +147,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) as_cell_kernel(AsP p) {
     mbar_wait(mbar, 0);
     // ---- vertical flux at every (scalar, interface), TI:3436-3470, branch-free
     for (int t = lane; t < ns * L1; t += 32) {
-        const int kk = t / ns + 1, q0 = t - (kk - 1) * ns;  // interface kk, scalar q0 (0-based)
+        const int kk = p.nsdiv(t) + 1, q0 = t - (kk - 1) * ns;  // interface kk, scalar q0 (0-based)
         const int k = min(max(kk, 2), L);
         const int km2 = max(k - 2, 1), kp1 = min(k + 1, L);
         const real ww = s_ww[k];
@@ -157,7 +166,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) as_cell_kernel(AsP p) {
     for (int ea = lane; ea < nel; ea += 64) {
         const bool vb = ea + 32 < nel;
         const int bo = vb ? 32 : 0;
-        const int ka = ea / ns, kb = (ea + bo) / ns;  // 0-based levels
+        const int ka = p.nsdiv(ea), kb = p.nsdiv(ea + bo);  // 0-based levels
         real col_a = 0.0, col_b = 0.0;
         {
             const real* __restrict__ hf = p.horiz_flux_arr + ea;
@@ -509,6 +518,7 @@ __global__ void __launch_bounds__(256) mono_update_kernel(MonoP p) {
 //   w_scale     (2*ns*L, nCells+1) [scale_in | scale_out] per cell            (scale_arr)
 // s_max / s_min stay in registers.  Every expression and every summation order is the reference's.
 struct MonoNP {
+    FastDiv nsdiv;
     int L, mE, ns, nCells;
     int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, nCellsSolve;
     real dt, coef_3rd_order;
@@ -522,7 +532,8 @@ __device__ __forceinline__ bool mono_zero_corr(int bm) { return (config_apply_lb
 
 // TI:3916-3961 + 4007-4022 for every scalar of one edge per warp: w_fa = high-order flux (0 off the owned edges),
 // w_fup = upwind flux (all edges).  Two (scalar, level) elements per lane, 10-cell stencil staged as in mono_edge_flux_kernel.
-__global__ void __launch_bounds__(WPB * 32) monoN_edge_flux_kernel(MonoNP p) {
+template <int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) monoN_edge_flux_kernel(MonoNP p) {
     __shared__ unsigned s_o[WPB][10];
     __shared__ real s_cp[WPB][10], s_cm[WPB][10];
     const int L = p.L, ns = p.ns, nel = L * ns;
@@ -548,7 +559,7 @@ __global__ void __launch_bounds__(WPB * 32) monoN_edge_flux_kernel(MonoNP p) {
     for (int ea = lane; ea < nel; ea += 64) {
         const bool vb = ea + 32 < nel;
         const int bo = vb ? 32 : 0;
-        const real uh_a = uh[ea / ns], uh_b = uh[(ea + bo) / ns];
+        const real uh_a = uh[p.nsdiv(ea)], uh_b = uh[p.nsdiv(ea + bo)];
         const real so1_a = o1[ea], so1_b = o1[ea + bo], so2_a = o2[ea], so2_b = o2[ea + bo];
         real fa_a = 0.0, fa_b = 0.0;
         if (n == 10) {
@@ -655,7 +666,8 @@ __global__ void __launch_bounds__(WPB * 32) monoN_edge_flux_kernel(MonoNP p) {
 // edge / neighbour lists staged as offsets, padded to 6 or 8 with zero signs (x - 0*y == x) and the cell itself
 // (max/min are idempotent).
 // dynamic shared memory per warp: 2*tma_slot(ns*L) + tma_slot(L+1) + ns*(L+1) reals.
-__global__ void __launch_bounds__(WPB * 32, 4) monoN_cell_kernel(MonoNP p) {
+template <int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) monoN_cell_kernel(MonoNP p) {
     extern __shared__ __align__(16) real s_dyn[];
     __shared__ __align__(8) unsigned long long s_bar[WPB];
     __shared__ unsigned s_eF[WPB][8], s_cF[WPB][8];
@@ -702,7 +714,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) monoN_cell_kernel(MonoNP p) {
     //      wdtn(k) = dt*wdtn(k) - flux_upwind_arr(k), k = 2..L (TI:3977-3993); interfaces 1 and L+1 stay 0
     real* __restrict__ g_wd = p.w_wdtn + (size_t)(iCell - 1) * nel1;
     for (int t = lane; t < nel1; t += 32) {
-        const int kk = t / ns + 1, q0 = t - (kk - 1) * ns;
+        const int kk = p.nsdiv(t) + 1, q0 = t - (kk - 1) * ns;
         const int k = min(max(kk, 2), L);
         const int km2 = max(k - 2, 1), kp1 = min(k + 1, L);
         const real ww = s_ww[k];
@@ -723,7 +735,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) monoN_cell_kernel(MonoNP p) {
     for (int ea = lane; ea < nel; ea += 64) {
         const bool vb = ea + 32 < nel;
         const int bo = vb ? 32 : 0;
-        const int ka = ea / ns, kb = (ea + bo) / ns;  // 0-based levels
+        const int ka = p.nsdiv(ea), kb = p.nsdiv(ea + bo);  // 0-based levels
         real sn_a, sn_b, si_a, si_b, so_a, so_b, mx_a, mx_b, mn_a, mn_b;
 #pragma unroll
         for (int h = 0; h < 2; ++h) {
@@ -800,7 +812,7 @@ __global__ void __launch_bounds__(256) monoN_rescale_edge_kernel(MonoNP p) {
 __global__ void __launch_bounds__(256) monoN_update_kernel(MonoNP p) {
     const int L = p.L, mE = p.mE, ns = p.ns, nel = L * ns;
     FLAT_KC(p.nCellsLoop, nel);
-    const int iCell = p.cellStart + _c0, e = k - 1, k0 = e / ns;
+    const int iCell = p.cellStart + _c0, e = k - 1, k0 = p.nsdiv(e);
     const size_t is = (size_t)(iCell - 1) * nel + e;
     real sn;
     if (iCell >= p.cellSolveStart && iCell < p.cellSolveStart + p.nCellsSolveLoop) {
@@ -831,7 +843,7 @@ extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
     (void)rho_edge; (void)qv_init; (void)zgrid; (void)cellStart; (void)cellEnd; (void)vertexStart; (void)vertexEnd; (void)vertexSolveStart; (void)vertexSolveEnd;
     (void)edgeSolveStart; (void)edgeSolveEnd;
     AsP p;
-    p.L = nVertLevels; p.mE = maxEdges; p.ns = num_scalars; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1;
+    p.L = nVertLevels; p.mE = maxEdges; p.ns = num_scalars; p.nsdiv.set(num_scalars); p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1;
     p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
     real weight_time_new = 1.;
     if (advance_density) {  // TI:3296-3304
@@ -890,7 +902,9 @@ extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
         const size_t nel = (size_t)L * p.ns, nel1 = (size_t)(L + 1) * p.ns, nC1 = (size_t)nCells + 1, nE1 = (size_t)nEdges + 1;
         const size_t n_edge = (nel * nE1 + 1) & ~(size_t)1, n_wd = (nel1 * nC1 + 1) & ~(size_t)1, n_cell = (nel * nC1 + 1) & ~(size_t)1;
         const size_t shm = (size_t)WPB * (2 * tma_slot((int)nel) + tma_slot(L + 1) + (((int)nel1 + 3) & ~3)) * sizeof(real);
-        const bool fits = ensure_dyn_smem((const void*)monoN_cell_kernel, shm);
+        static const int cell_minb = tune("monoN_cell_minb", 4), edge_minb = tune("monoN_edge_minb", 5);
+        const void* cell_fn = cell_minb == 2 ? (const void*)monoN_cell_kernel<2> : cell_minb == 3 ? (const void*)monoN_cell_kernel<3> : (const void*)monoN_cell_kernel<4>;
+        const bool fits = ensure_dyn_smem(cell_fn, shm);
         real* ws = fits ? keyed_workspace(X(scale_arr), 2 * n_edge + n_wd + 3 * n_cell) : nullptr;
         // no silent fallback: ranks / blocks taking different paths would post different numbers of exchanges
         if (fits && !ws)
@@ -899,7 +913,7 @@ extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
                             " MiB; first call must be outside stream capture); MPAS_B200_TUNE_mono_fused=0 selects the per-scalar path");
         if (ws) {
             MonoNP q;
-            q.L = p.L; q.mE = p.mE; q.ns = p.ns; q.nCells = nCells; q.cellStart = p.cellStart; q.nCellsLoop = p.nCellsLoop;
+            q.L = p.L; q.mE = p.mE; q.ns = p.ns; q.nsdiv.set(p.ns); q.nCells = nCells; q.cellStart = p.cellStart; q.nCellsLoop = p.nCellsLoop;
             q.cellSolveStart = p.cellSolveStart; q.nCellsSolveLoop = p.nCellsSolveLoop; q.edgeStart = p.edgeStart; q.nEdgesLoop = p.nEdgesLoop;
             q.nCellsSolve = p.nCellsSolve; q.dt = p.dt; q.coef_3rd_order = p.coef_3rd_order;
             q.uhAvg = p.uhAvg; q.wwAvg = p.wwAvg; q.rho_zz_old = p.rho_zz_old; q.rho_lim = p.rho_lim; q.invAreaCell = p.invAreaCell; q.dvEdge = p.dvEdge;
@@ -908,9 +922,13 @@ extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
             q.nAdvCellsForEdge = p.nAdvCellsForEdge; q.advCellsForEdge = p.advCellsForEdge; q.bdyMaskCell = p.bdyMaskCell; q.bdyMaskEdge = p.bdyMaskEdge;
             q.scalars_old = p.scalars_old; q.scalars_new = p.scalars_new;
             q.w_fa = ws; q.w_fup = ws + n_edge; q.w_wdtn = ws + 2 * n_edge; q.w_snew = q.w_wdtn + n_wd; q.w_scale = q.w_snew + n_cell;
-            WLAUNCH(monoN_edge_flux_kernel, q.nEdgesLoop, 0, q);
+            if (edge_minb == 5) WLAUNCH(monoN_edge_flux_kernel<5>, q.nEdgesLoop, 0, q);
+            else if (edge_minb == 6) WLAUNCH(monoN_edge_flux_kernel<6>, q.nEdgesLoop, 0, q);
+            else WLAUNCH(monoN_edge_flux_kernel<4>, q.nEdgesLoop, 0, q);
             KCHECK("monoN_edge_flux_kernel");
-            WLAUNCH(monoN_cell_kernel, q.nCellsSolveLoop, shm, q);
+            if (cell_minb == 2) WLAUNCH(monoN_cell_kernel<2>, q.nCellsSolveLoop, shm, q);
+            else if (cell_minb == 3) WLAUNCH(monoN_cell_kernel<3>, q.nCellsSolveLoop, shm, q);
+            else WLAUNCH(monoN_cell_kernel<4>, q.nCellsSolveLoop, shm, q);
             KCHECK("monoN_cell_kernel");
             if (halo_fn) {
                 int rc = halo_fn(halo_ctx, 2, q.w_scale);  // TI:4098, all scalars in one message
