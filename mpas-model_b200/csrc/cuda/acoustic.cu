@@ -18,6 +18,7 @@ using namespace mpasb200;
 namespace {
 
 struct AcEdgeP {
+    KMagic km;
     int L, nCellsSolve, edgeStart, nEdgesLoop, small_step;
     real dts, c2;
     const int* cellsOnEdge;
@@ -352,6 +353,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
 }
 
 struct DivDampP {
+    KMagic km;
     int L, nCellsSolve, edgeStart, nEdgesLoop;
     real coef_divdamp;
     const int* cellsOnEdge;
@@ -382,7 +384,7 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
     const int L = nVertLevels;
     {
         AcEdgeP p;
-        p.L = L; p.nCellsSolve = nCellsSolve; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.small_step = small_step;
+        p.L = L; p.km.set(L, L + 1); p.nCellsSolve = nCellsSolve; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.small_step = small_step;
         p.dts = dts; p.c2 = c2;
         p.cellsOnEdge = X(cellsOnEdge);
         p.rtheta_pp = X(rtheta_pp); p.rho_pp = X(rho_pp); p.zz = X(zz); p.exner = X(exner); p.cqu = X(cqu); p.zxu = X(zxu);
@@ -415,6 +417,7 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
 extern "C" int mpas_b200_divergence_damping_3d(MPAS_DIVDAMP_ARGS) {
     (void)nCells; (void)nEdges;
     DivDampP p;
+    p.km.set(nVertLevels, nVertLevels + 1);
     const real rdts = (real)1.0 / dts;
     p.coef_divdamp = (real)2.0 * smdiv * config_len_disp * rdts;
     p.L = nVertLevels; p.nCellsSolve = nCellsSolve; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1;

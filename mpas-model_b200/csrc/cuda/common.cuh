@@ -253,8 +253,34 @@ void ktime_end();
         }                                                                                               \
     } while (0)
 
-// flattened (k, column) thread mapping: k fastest so that a warp reads contiguous levels
-#define FLAT_KC(ncols, nk)                                                   \
+// Column index of a flat thread index without the ~25-instruction 64-bit division: the host precomputes
+// magic = floor(2^64 / nk) + 1 for the (at most two) inner extents a parameter block is used with, and
+// umul64hi(t, magic) is the exact quotient for t * nk < 2^64.  Any other extent takes the plain division.
+struct KMagic {
+    int n0 = 0, n1 = 0;
+    unsigned long long m0 = 0, m1 = 0;
+    static unsigned long long magic(int nk) { return 0xFFFFFFFFFFFFFFFFULL / (unsigned long long)nk + 1ULL; }
+    void set(int a, int b = 0) {
+        n0 = a > 1 ? a : 0; m0 = n0 ? magic(a) : 0;
+        n1 = b > 1 ? b : 0; m1 = n1 ? magic(b) : 0;
+    }
+    __device__ __forceinline__ unsigned long long div(unsigned long long t, int nk) const {
+        if (nk == n0) return __umul64hi(t, m0);
+        if (nk == n1) return __umul64hi(t, m1);
+        return t / (unsigned long long)nk;
+    }
+};
+
+// flattened (k, column) thread mapping: k fastest so that a warp reads contiguous levels.  Expects the kernel's
+// parameter block `p` to carry a KMagic member `km` (set on the host for the extents the block is launched with).
+#define FLAT_KC(ncols, nk)                                                                   \
+    const unsigned long long _t = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;  \
+    if (_t >= (unsigned long long)(ncols) * (unsigned long long)(nk)) return;                 \
+    const int _c0 = (int)p.km.div(_t, (nk));                                                  \
+    const int k = (int)(_t - (unsigned long long)_c0 * (unsigned long long)(nk)) + 1
+
+// the same mapping with the plain 64-bit division (kernels whose integer pipe is the bottleneck: smlstep)
+#define FLAT_KC_DIV(ncols, nk)                                               \
     long long _t = (long long)blockIdx.x * blockDim.x + threadIdx.x;         \
     if (_t >= (long long)(ncols) * (long long)(nk)) return;                  \
     const int _c0 = (int)(_t / (nk));                                        \

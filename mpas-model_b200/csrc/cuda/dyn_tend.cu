@@ -30,6 +30,7 @@ using namespace mpasb200;
 namespace {
 
 struct DtP {
+    KMagic km;
     int L, mE, mE2, vD, rk_step, nCellsSolve;
     int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, edgeSolveStart, edgeSolveEnd, nEdgesSolveLoop;
     int vertexStart, nVerticesLoop;
@@ -772,7 +773,7 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     if (nVertLevels < 4) return fail_msg("mpas_b200_compute_dyn_tend_work: nVertLevels must be >= 4");
     if (vertexDegree != 3) return fail_msg("mpas_b200_compute_dyn_tend_work: vertexDegree must be 3");
     DtP p;
-    p.L = nVertLevels; p.mE = maxEdges; p.mE2 = maxEdges2; p.vD = vertexDegree; p.rk_step = rk_step; p.nCellsSolve = nCellsSolve;
+    p.L = nVertLevels; p.km.set(nVertLevels, nVertLevels + 1); p.mE = maxEdges; p.mE2 = maxEdges2; p.vD = vertexDegree; p.rk_step = rk_step; p.nCellsSolve = nCellsSolve;
     p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
     p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.edgeSolveStart = edgeSolveStart; p.edgeSolveEnd = edgeSolveEnd;
     p.nEdgesSolveLoop = edgeSolveEnd - edgeSolveStart + 1; p.vertexStart = vertexStart; p.nVerticesLoop = vertexEnd - vertexStart + 1;

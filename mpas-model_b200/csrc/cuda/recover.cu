@@ -16,6 +16,7 @@ using namespace mpasb200;
 namespace {
 
 struct RecCellP {
+    KMagic km;
     int L, cellStart, nCellsLoop, rk_step, nCells;
     real dt, invNs;
     const real *rw_save, *rw_p, *rtheta_pp, *rtheta_p_save, *rt_diabatic_tend, *rho_p_save, *rho_pp, *rho_base;
@@ -70,6 +71,7 @@ __global__ void set_garbage_column_kernel(real* a, int L, int col, real v) {  //
 }
 
 struct RecEdgeP {
+    KMagic km;
     int L, edgeStart, nEdgesLoop;
     real invNs;
     const int* cellsOnEdge;
@@ -91,6 +93,7 @@ __global__ void __launch_bounds__(256) recover_edge_kernel(RecEdgeP p) {
 }
 
 struct RecWP {
+    KMagic km;
     int L, mE, cellStart, nCellsLoop;
     real cf1, cf2, cf3;
     const int *bdyMaskCell, *nEdgesOnCell, *edgesOnCell;
@@ -154,7 +157,7 @@ struct SmlP {
 template <int NE>
 __global__ void __launch_bounds__(256) smlstep_kernel(SmlP p) {
     const int L = p.L, L1 = L + 1, mE = p.mE;
-    FLAT_KC(p.nCellsLoop, L);
+    FLAT_KC_DIV(p.nCellsLoop, L);
     if (k < 2) return;
     const int iCell = p.cellStart + _c0;
     if (p.bdyMaskCell[iCell - 1] > MPAS_NRELAXZONE) return;
@@ -202,7 +205,7 @@ extern "C" int mpas_b200_recover_large_step_variables_work(MPAS_RECOVER_ARGS) {
     const real invNs = 1 / (real)ns;
     {
         RecCellP p;
-        p.L = L; p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.rk_step = rk_step; p.nCells = nCells;
+        p.L = L; p.km.set(L, L + 1); p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.rk_step = rk_step; p.nCells = nCells;
         p.dt = dt; p.invNs = invNs;
         p.rw_save = X(rw_save); p.rw_p = X(rw_p); p.rtheta_pp = X(rtheta_pp); p.rtheta_p_save = X(rtheta_p_save);
         p.rt_diabatic_tend = X(rt_diabatic_tend); p.rho_p_save = X(rho_p_save); p.rho_pp = X(rho_pp); p.rho_base = X(rho_base);
@@ -214,7 +217,7 @@ extern "C" int mpas_b200_recover_large_step_variables_work(MPAS_RECOVER_ARGS) {
     }
     {
         RecEdgeP p;
-        p.L = L; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.invNs = invNs;
+        p.L = L; p.km.set(L, L + 1); p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.invNs = invNs;
         p.cellsOnEdge = X(cellsOnEdge); p.ru_save = X(ru_save); p.ru_p = X(ru_p); p.rho_zz = d_rho_zz;
         p.ruAvg = X(ruAvg); p.ru = X(ru); p.u = X(u);
         KLAUNCH(recover_edge_kernel, (long long)p.nEdgesLoop * L, 256, p);
@@ -222,7 +225,7 @@ extern "C" int mpas_b200_recover_large_step_variables_work(MPAS_RECOVER_ARGS) {
     }
     {
         RecWP p;
-        p.L = L; p.mE = maxEdges; p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1;
+        p.L = L; p.km.set(L, L + 1); p.mE = maxEdges; p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1;
         p.cf1 = cf1; p.cf2 = cf2; p.cf3 = cf3;
         p.bdyMaskCell = X(bdyMaskCell); p.nEdgesOnCell = X(nEdgesOnCell); p.edgesOnCell = X(edgesOnCell);
         p.edgesOnCell_sign = X(edgesOnCell_sign); p.zb_cell = X(zb_cell); p.zb3_cell = X(zb3_cell); p.ru = X(ru); p.rho_zz = d_rho_zz;

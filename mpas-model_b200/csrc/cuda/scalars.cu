@@ -213,6 +213,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) as_cell_kernel(AsP p) {
 
 // ---------------------------------------------------------------------------------------------
 struct MonoP {
+    KMagic km;
     int L, mE, ns, iScalar, nCells;
     int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, nCellsSolve;
     int advance_density;
@@ -518,6 +519,7 @@ __global__ void __launch_bounds__(256) mono_update_kernel(MonoP p) {
 //   w_scale     (2*ns*L, nCells+1) [scale_in | scale_out] per cell            (scale_arr)
 // s_max / s_min stay in registers.  Every expression and every summation order is the reference's.
 struct MonoNP {
+    KMagic km;
     FastDiv nsdiv;
     int L, mE, ns, nCells;
     int cellStart, nCellsLoop, cellSolveStart, nCellsSolveLoop, edgeStart, nEdgesLoop, nCellsSolve;
@@ -809,7 +811,7 @@ __global__ void __launch_bounds__(256) monoN_rescale_edge_kernel(MonoNP p) {
 
 // TI:4145-4210 for every scalar: limited vertical fluxes, final update of the owned cells, store (clamped at zero) for
 // all cells -- cells outside the owned range keep their predictor value, as the reference's scalar_new copy does.
-__global__ void __launch_bounds__(256) monoN_update_kernel(MonoNP p) {
+__global__ void __launch_bounds__(256, 5) monoN_update_kernel(MonoNP p) {
     const int L = p.L, mE = p.mE, ns = p.ns, nel = L * ns;
     FLAT_KC(p.nCellsLoop, nel);
     const int iCell = p.cellStart + _c0, e = k - 1, k0 = p.nsdiv(e);
@@ -825,10 +827,24 @@ __global__ void __launch_bounds__(256) monoN_update_kernel(MonoNP p) {
         if (k0 <= L - 2) whi = fmax((real)0.0, whi) * fmin(out_k, sc[e + ns]) + fmin((real)0.0, whi) * fmin(sc[nel + e + ns], in_k);
         const int ne = p.nEdgesOnCell[iCell - 1];
         const real invArea = p.invAreaCell[iCell - 1];
-        for (int i = 1; i <= ne; ++i) {
-            const int iEdge = p.edgesOnCell[IX2(i, iCell, mE)];
-            sn = sn - p.edgesOnCell_sign[IX2(i, iCell, mE)] * p.w_fa[(size_t)(iEdge - 1) * nel + e] * invArea;
+        // load-first: edge indices and signs of all (<= 8) slots, then the fluxes, then the sum in the reference's order;
+        // slots beyond nEdgesOnCell repeat slot 1 and are left out of the sum
+        const int* eoc = p.edgesOnCell + (size_t)(iCell - 1) * mE;
+        const real* sgc = p.edgesOnCell_sign + (size_t)(iCell - 1) * mE;
+        int ed[8];
+        real sg[8], fl[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) ed[i] = eoc[i < ne ? i : 0];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            if (i < 6 || ne > 6) {
+                sg[i] = sgc[i < ne ? i : 0];
+                fl[i] = p.w_fa[(size_t)(ed[i] - 1) * nel + e];
+            }
         }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+            if (i < ne) sn = sn - sg[i] * fl[i] * invArea;
         sn = (sn + (-p.rdnw[k0] * (whi - wlo))) / p.rho_lim[IX2(k0 + 1, iCell, L)];
     } else {
         sn = p.scalars_new[is];
@@ -873,7 +889,7 @@ extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
 extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
     (void)nEdges; (void)vertexStart; (void)vertexEnd; (void)vertexSolveStart; (void)vertexSolveEnd; (void)edgeSolveStart; (void)edgeSolveEnd;
     MonoP p;
-    p.L = nVertLevels; p.mE = maxEdges; p.ns = num_scalars; p.iScalar = 0; p.nCells = nCells;
+    p.L = nVertLevels; p.km.set(nVertLevels, nVertLevels + 1); p.mE = maxEdges; p.ns = num_scalars; p.iScalar = 0; p.nCells = nCells;
     p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1; p.cellSolveStart = cellSolveStart; p.nCellsSolveLoop = cellSolveEnd - cellSolveStart + 1;
     p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.nCellsSolve = nCellsSolve; p.advance_density = advance_density;
     p.dt = dt; p.coef_3rd_order = coef_3rd_order;
@@ -913,7 +929,7 @@ extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
                             " MiB; first call must be outside stream capture); MPAS_B200_TUNE_mono_fused=0 selects the per-scalar path");
         if (ws) {
             MonoNP q;
-            q.L = p.L; q.mE = p.mE; q.ns = p.ns; q.nsdiv.set(p.ns); q.nCells = nCells; q.cellStart = p.cellStart; q.nCellsLoop = p.nCellsLoop;
+            q.L = p.L; q.km.set(p.L * p.ns); q.mE = p.mE; q.ns = p.ns; q.nsdiv.set(p.ns); q.nCells = nCells; q.cellStart = p.cellStart; q.nCellsLoop = p.nCellsLoop;
             q.cellSolveStart = p.cellSolveStart; q.nCellsSolveLoop = p.nCellsSolveLoop; q.edgeStart = p.edgeStart; q.nEdgesLoop = p.nEdgesLoop;
             q.nCellsSolve = p.nCellsSolve; q.dt = p.dt; q.coef_3rd_order = p.coef_3rd_order;
             q.uhAvg = p.uhAvg; q.wwAvg = p.wwAvg; q.rho_zz_old = p.rho_zz_old; q.rho_lim = p.rho_lim; q.invAreaCell = p.invAreaCell; q.dvEdge = p.dvEdge;

@@ -25,6 +25,7 @@ int d2d(void* dst, const void* src, size_t bytes) {
     } while (0)
 
 struct MoistP {
+    KMagic km;
     int L, ns, ms, me, cellStart, nCellsLoop, edgeStart, nEdgesLoop, nCellsSolve;
     const int* cellsOnEdge;
     const real* scalars;
@@ -58,6 +59,7 @@ __global__ void __launch_bounds__(256) moist_edge_kernel(MoistP p) {
 }
 
 struct VicP {
+    KMagic km;
     int L, cellSolveStart, nCellsLoop;
     real dtseps, rcv, c2;
     const real *zz, *cqw, *p_, *t, *rb, *rtb, *pb, *rt, *rdzw, *fzm, *fzp, *rdzu, *qtot;
@@ -195,6 +197,7 @@ __global__ void __launch_bounds__(WPB * 32) vert_imp_kernel(VicP p) {
 }
 
 struct AxP {
+    KMagic km;
     long long n;
     real s;
     const real *a, *b;
@@ -210,6 +213,7 @@ __global__ void __launch_bounds__(256) ax_kernel(AxP p) {
 }
 
 struct IcdP {
+    KMagic km;
     int L, mE, ns, index_qv, cellStart, nCellsLoop, edgeStart, nEdgesLoop;
     const int *cellsOnEdge, *nEdgesOnCell, *edgesOnCell;
     const real *edgesOnCell_sign, *theta, *rho, *rho_base, *theta_base, *zz, *scalars, *u, *w, *fzm, *fzp, *zb_cell, *zb3_cell;
@@ -297,7 +301,7 @@ extern "C" int mpas_b200_compute_moist_coefficients(MPAS_MOIST_ARGS) {
     (void)nCells; (void)nEdges; (void)vertexStart; (void)vertexEnd; (void)cellSolveStart; (void)cellSolveEnd; (void)vertexSolveStart; (void)vertexSolveEnd;
     (void)edgeSolveStart; (void)edgeSolveEnd;
     MoistP p;
-    p.L = nVertLevels; p.ns = num_scalars; p.ms = moist_start; p.me = moist_end; p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1;
+    p.L = nVertLevels; p.km.set(nVertLevels, nVertLevels + 1); p.ns = num_scalars; p.ms = moist_start; p.me = moist_end; p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1;
     p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.nCellsSolve = nCellsSolve;
     p.cellsOnEdge = X(cellsOnEdge); p.scalars = X(scalars); p.cqw = X(cqw); p.cqu = X(cqu); p.qtot = X(qtot);
     KLAUNCH(moist_cell_kernel, (long long)p.nCellsLoop * p.L, 256, p);
@@ -384,6 +388,7 @@ extern "C" int mpas_b200_rk_dynamics_substep_finish(MPAS_SUBSTEPFINISH_ARGS) {
 // ---- mpas_reconstruct_2d (operators/mpas_vector_reconstruction.F:195-305)
 namespace {
 struct RecP {
+    KMagic km;
     int L, mE, nCellsLoop, on_a_sphere;
     const real *u, *coeffs, *latCell, *lonCell;
     const int *nEdgesOnCell, *edgesOnCell;
@@ -446,7 +451,7 @@ __global__ void __launch_bounds__(256) reconstruct_kernel(RecP p) {
 extern "C" int mpas_b200_reconstruct_2d(MPAS_RECONSTRUCT_ARGS) {
     (void)nCells; (void)nEdges;
     RecP p;
-    p.L = nVertLevels; p.mE = maxEdges; p.nCellsLoop = nCellsLoop; p.on_a_sphere = on_a_sphere;
+    p.L = nVertLevels; p.km.set(nVertLevels, nVertLevels + 1); p.mE = maxEdges; p.nCellsLoop = nCellsLoop; p.on_a_sphere = on_a_sphere;
     p.u = X(u); p.coeffs = X(coeffs_reconstruct); p.latCell = X(latCell); p.lonCell = X(lonCell);
     p.nEdgesOnCell = X(nEdgesOnCell); p.edgesOnCell = X(edgesOnCell);
     p.ux = X(uReconstructX); p.uy = X(uReconstructY); p.uz = X(uReconstructZ); p.uzonal = X(uReconstructZonal); p.umerid = X(uReconstructMeridional);
@@ -461,7 +466,7 @@ extern "C" int mpas_b200_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS) {
     (void)nCells; (void)nEdges; (void)vertexStart; (void)vertexEnd; (void)cellSolveStart; (void)cellSolveEnd; (void)vertexSolveStart; (void)vertexSolveEnd;
     (void)edgeSolveStart; (void)edgeSolveEnd;
     IcdP p;
-    p.L = nVertLevels; p.mE = maxEdges; p.ns = num_scalars; p.index_qv = index_qv; p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1;
+    p.L = nVertLevels; p.km.set(nVertLevels, nVertLevels + 1); p.mE = maxEdges; p.ns = num_scalars; p.index_qv = index_qv; p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1;
     p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1;
     p.cellsOnEdge = X(cellsOnEdge); p.nEdgesOnCell = X(nEdgesOnCell); p.edgesOnCell = X(edgesOnCell); p.edgesOnCell_sign = X(edgesOnCell_sign);
     p.theta = X(theta); p.rho = X(rho); p.rho_base = X(rho_base); p.theta_base = X(theta_base); p.zz = X(zz); p.scalars = X(scalars); p.u = X(u); p.w = X(w);

@@ -17,6 +17,7 @@ using namespace mpasb200;
 namespace {
 
 struct SdP {
+    KMagic km;
     int L, mE, mE2, vD;
     int cellStart, nCellsLoop, vertexStart, nVerticesLoop, edgeStart, nEdgesLoop;
     int reconstruct_v;
@@ -174,7 +175,7 @@ __global__ void __launch_bounds__(256) sd_edge_kernel(SdP p) {
 extern "C" int mpas_b200_compute_solve_diagnostics_work(MPAS_SOLVEDIAG_ARGS) {
     (void)nCells; (void)nEdges; (void)nVertices; (void)cellsOnVertex;
     SdP p;
-    p.L = nVertLevels; p.mE = maxEdges; p.mE2 = maxEdges2; p.vD = vertexDegree;
+    p.L = nVertLevels; p.km.set(nVertLevels, nVertLevels + 1); p.mE = maxEdges; p.mE2 = maxEdges2; p.vD = vertexDegree;
     if (vertexDegree != 3) return fail_msg("mpas_b200_compute_solve_diagnostics_work: vertexDegree must be 3 (TI:5683-5690 hard-codes three edges)");
     p.cellStart = cellStart; p.nCellsLoop = cellEnd - cellStart + 1;
     p.vertexStart = vertexStart; p.nVerticesLoop = vertexEnd - vertexStart + 1;
