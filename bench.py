@@ -363,7 +363,7 @@ def run_b200(a):
             "config": {"workload": workload_name(a), "nCells": LEVEL_CELLS[a.level], "nVertLevels": a.levels, "num_scalars": a.scalars, "config_dt_s": dt_model,
                        "simulated_days_per_day": value * dt_model, "partition": "METIS k-way, %d blocks" % N if N > 1 else "single block",
                        "l2_policy": "no flush needed: one step streams ~%.0f GB through a 126 MB L2" % step_gb, "cuda_graph": use_graph,
-                       "halo_exchanges_per_step": exchanges / a.steps, "setup_seconds": t_setup, "max_abs_u": umax, "max_abs_w": wmax},
+                       "halo_exchanges_per_step": exchanges / a.steps, "halo_transport": dy.halo_transport(), "setup_seconds": t_setup, "max_abs_u": umax, "max_abs_w": wmax},
             "roofline": roofline, "phases": phases, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
         }
         print(json.dumps(line), flush=True)

@@ -82,6 +82,11 @@ int mpas_b200_dycore_exchange(void* h, const char* name, int layer /* 0 = all */
  * "moist", "substep_finish"; params as documented in dycore.cu */
 int mpas_b200_dycore_call(void* h, const char* routine, const double* params, int nparams);
 long mpas_b200_dycore_exchange_count(void* h);
+/* how halo messages travel between the ranks: 0 one rank (no messages), 1 NCCL grouped send/recv (the replacement of the
+ * MPI_Irecv/Isend pairs of mpas_dmpar.F:5430-5452, 5466-5476), 2 peer-to-peer stores into the neighbours' receive windows
+ * (CUDA IPC over NVLink, switched on after the second step when every rank can map every other); -2 a peer-to-peer wait
+ * timed out since the last call.  MPAS_B200_TUNE_p2p=0 keeps NCCL. */
+int mpas_b200_dycore_halo_transport(void* h);
 int mpas_b200_dycore_set_option(void* h, const char* name, int value); /* "timing", "graph", "aggregate" */
 int mpas_b200_dycore_timer_count(void* h);
 int mpas_b200_dycore_timer_get(void* h, int idx, char* name, int cap, double* ms, long* calls);

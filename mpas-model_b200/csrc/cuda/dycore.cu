@@ -2,6 +2,7 @@
 // The step sequence itself is in srk3.cu.
 #include "dycore.h"
 
+#include <algorithm>
 #include <cstring>
 #include <stdexcept>
 
@@ -68,6 +69,18 @@ int dycore_exchange(Dycore& m, const std::vector<XField>& fields) {
             plans[b] = it->second;
         }
     }
+    if (m.nranks > 1 && m.p2p.on && P == 1) {
+        // peer-to-peer: pack straight into the neighbours' windows, publish, wait + unpack (halo.h)
+        HaloPlan* p = plans[0];
+        P2PSideTab snd, rcv;
+        if (p->send.nbr != p->recv.nbr || halo_p2p_tab(m.p2p, p->send, true, snd) || halo_p2p_tab(m.p2p, p->recv, false, rcv))
+            return fail_msg("dycore_exchange: exchange '" + key + "' does not fit the peer-to-peer protocol (message larger than the window, or it does not "
+                            "send to exactly the ranks it receives from); run with MPAS_B200_TUNE_p2p=0");
+        int rc = halo_pack_p2p(p, snd, m.p2p);
+        if (!rc) rc = halo_signal_p2p(snd, rcv, m.p2p);
+        if (!rc) rc = halo_unpack_p2p(p, rcv, m.p2p);
+        return rc;
+    }
     for (int b = 0; b < P; ++b) {
         int rc = halo_pack(plans[b]);
         if (rc) return rc;
@@ -105,6 +118,106 @@ int dycore_exchange(Dycore& m, const std::vector<XField>& fields) {
         int rc = halo_unpack(plans[b]);
         if (rc) return rc;
     }
+    return 0;
+}
+
+// ---- peer-to-peer windows ------------------------------------------------------------------------------------------------
+void dycore_p2p_teardown(Dycore& m) {
+    P2P& pp = m.p2p;
+    for (int r = 0; r < (int)pp.peer.size(); ++r)
+        if (pp.peer[r] && pp.peer[r] != pp.win) cudaIpcCloseMemHandle(pp.peer[r]);
+    pp.peer.clear();
+    if (pp.win) cudaFree(pp.win);
+    if (pp.seq_send) cudaFree(pp.seq_send);
+    if (pp.seq_recv) cudaFree(pp.seq_recv);
+    if (pp.d_timeout) cudaFree(pp.d_timeout);
+    pp.win = nullptr; pp.seq_send = pp.seq_recv = nullptr; pp.d_timeout = nullptr;
+    pp.on = false;
+}
+
+int dycore_p2p_setup(Dycore& m) {
+    P2P& pp = m.p2p;
+    if (pp.tried) return 0;
+    pp.tried = true;
+    if (m.nranks < 2 || !m.have_comm || m.blocks.size() != 1 || m.nranks > MPAS_P2P_MAXN || !tune("p2p", 1)) return 0;
+    pp.rank = m.rank;
+    pp.nranks = m.nranks;
+    // slot capacity: the largest message of any plan built so far (both time-level parities have run), on any rank
+    long long cap = 0;
+    for (auto& kv : m.blocks[0].halo.plans) {
+        for (long long c : kv.second->send.cnt) cap = std::max(cap, c);
+        for (long long c : kv.second->recv.cnt) cap = std::max(cap, c);
+    }
+    cap = (cap + 65535) & ~65535LL;  // a multiple of 2^16 is exact in the float of the allreduce of a single-precision build
+    // the two-slot protocol relies on pairwise back-pressure: every plan must send to exactly the ranks it receives from
+    bool symmetric = true;
+    for (auto& kv : m.blocks[0].halo.plans) symmetric = symmetric && kv.second->send.nbr == kv.second->recv.nbr;
+    const int HW = 64 / (int)sizeof(real);  // reals per IPC handle
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    real* d_tmp = nullptr;
+    if (cudaMalloc(&d_tmp, (size_t)(2 + (m.nranks + 1) * HW) * sizeof(real)) != cudaSuccess) return fail_msg("dycore_p2p_setup: cudaMalloc");
+    auto allmax = [&](double v, double& out) -> int {
+        real hv = (real)v;
+        cudaMemcpyAsync(d_tmp, &hv, sizeof(real), cudaMemcpyHostToDevice, stream());
+        if (m.nccl.allreduce_max(d_tmp, d_tmp + 1, 1, stream())) return 1;
+        cudaMemcpyAsync(&hv, d_tmp + 1, sizeof(real), cudaMemcpyDeviceToHost, stream());
+        if (cudaStreamSynchronize(stream()) != cudaSuccess) return 1;
+        out = (double)hv;
+        return 0;
+    };
+    double gcap = 0;
+    if (allmax((double)cap, gcap)) { cudaFree(d_tmp); return fail_msg(std::string("dycore_p2p_setup: allreduce: ") + m.nccl.last_error()); }
+    pp.cap = (long long)gcap;
+    bool ok = pp.cap > 0 && symmetric;
+    // window + counters
+    const size_t wbytes = P2P::flag_bytes(m.nranks) + (size_t)m.nranks * 2 * (size_t)pp.cap * sizeof(real);
+    cudaIpcMemHandle_t mine;
+    std::memset(&mine, 0, sizeof(mine));
+    if (ok) ok = cudaMalloc(&pp.win, wbytes) == cudaSuccess;
+    if (ok) ok = cudaMemsetAsync(pp.win, 0, wbytes, stream()) == cudaSuccess;
+    if (ok) ok = cudaIpcGetMemHandle(&mine, pp.win) == cudaSuccess;
+    if (ok) ok = cudaMalloc(&pp.seq_send, m.nranks * sizeof(unsigned long long)) == cudaSuccess && cudaMalloc(&pp.seq_recv, m.nranks * sizeof(unsigned long long)) == cudaSuccess &&
+                 cudaMalloc(&pp.d_timeout, sizeof(int)) == cudaSuccess;
+    if (ok) {
+        cudaMemsetAsync(pp.seq_send, 0, m.nranks * sizeof(unsigned long long), stream());
+        cudaMemsetAsync(pp.seq_recv, 0, m.nranks * sizeof(unsigned long long), stream());
+        cudaMemsetAsync(pp.d_timeout, 0, sizeof(int), stream());
+    }
+    cudaGetLastError();
+    // every rank's handle to every rank (a failed rank still takes part, with a zero handle)
+    real* d_mine = d_tmp + 2;
+    real* d_all = d_tmp + 2 + HW;
+    cudaMemcpyAsync(d_mine, &mine, 64, cudaMemcpyHostToDevice, stream());
+    int nrc = m.nccl.group_start();
+    for (int r = 0; r < m.nranks && !nrc; ++r) {
+        if (r == m.rank) continue;
+        nrc = m.nccl.recv(d_all + (size_t)r * HW, HW, r, stream());
+        if (!nrc) nrc = m.nccl.send(d_mine, HW, r, stream());
+    }
+    if (!nrc) nrc = m.nccl.group_end();
+    std::vector<cudaIpcMemHandle_t> all(m.nranks);
+    cudaMemcpyAsync(all.data(), d_all, (size_t)m.nranks * 64, cudaMemcpyDeviceToHost, stream());
+    if (cudaStreamSynchronize(stream()) != cudaSuccess || nrc) ok = false;
+    pp.peer.assign(m.nranks, nullptr);
+    if (ok) {
+        pp.peer[m.rank] = pp.win;
+        for (int r = 0; r < m.nranks && ok; ++r) {
+            if (r == m.rank) continue;
+            void* q = nullptr;
+            ok = cudaIpcOpenMemHandle(&q, all[r], cudaIpcMemLazyEnablePeerAccess) == cudaSuccess;
+            pp.peer[r] = (char*)q;
+        }
+    }
+    cudaGetLastError();
+    // all or nothing (also the barrier that orders every rank's window clear before the first peer store)
+    double anyfail = 1;
+    const int arc = allmax(ok ? 0.0 : 1.0, anyfail);
+    cudaFree(d_tmp);
+    if (arc || anyfail != 0.0) {
+        dycore_p2p_teardown(m);
+        return 0;  // stay on NCCL
+    }
+    pp.on = true;
     return 0;
 }
 
@@ -175,6 +288,7 @@ void mpas_b200_dycore_destroy(void* h) {
     Dycore* m = (Dycore*)h;
     if (!m) return;
     cudaStreamSynchronize(stream());
+    dycore_p2p_teardown(*m);
     for (auto& b : m->blocks) {
         auto sa = b.f.find("scale_arr");
         if (sa != b.f.end()) release_keyed_workspace(sa->second.dev);  // the all-scalars mono workspace of this block
@@ -298,6 +412,22 @@ int mpas_b200_dycore_call(void* h, const char* routine, const double* params, in
 }
 
 long mpas_b200_dycore_exchange_count(void* h) { return ((Dycore*)h)->nExchanges; }
+
+// 0: no inter-process exchange (one rank), 1: NCCL grouped send/recv, 2: peer-to-peer stores into mapped windows.
+// Negative: a peer-to-peer wait timed out since the last call (a rank died or the ranks disagree about the sequence).
+int mpas_b200_dycore_halo_transport(void* h) {
+    Dycore* m = (Dycore*)h;
+    if (m->nranks < 2) return 0;
+    if (!m->p2p.on) return 1;
+    int t = 0;
+    cudaMemcpyAsync(&t, m->p2p.d_timeout, sizeof(int), cudaMemcpyDeviceToHost, stream());
+    cudaStreamSynchronize(stream());
+    if (t) {
+        cudaMemsetAsync(m->p2p.d_timeout, 0, sizeof(int), stream());
+        return -2;
+    }
+    return 2;
+}
 
 int mpas_b200_dycore_set_option(void* h, const char* name, int value) {
     Dycore* m = (Dycore*)h;

@@ -56,6 +56,7 @@ struct Dycore {
     int rank = 0, nranks = 1;
     Nccl nccl;
     bool have_comm = false;
+    P2P p2p;  // peer-to-peer windows, set up after the second (eager) step when every rank can map every other
     long nExchanges = 0;
     bool timing = false;
     bool aggregate = true;
@@ -81,6 +82,8 @@ struct XField {
 };
 
 int dycore_exchange(Dycore& m, const std::vector<XField>& fields);
+int dycore_p2p_setup(Dycore& m);   // collective; leaves m.p2p.on false (NCCL path) when any rank cannot
+void dycore_p2p_teardown(Dycore& m);
 int dycore_init(Dycore& m);
 int dycore_step(Dycore& m);
 int dycore_call(Dycore& m, const std::string& routine, const double* prm, int nprm);

@@ -26,6 +26,72 @@ __global__ void __launch_bounds__(256) halo_copy_kernel(real* __restrict__ array
     else array[ia] = buf[ib];
 }
 
+// ---- peer-to-peer variants (halo.h): the packed buffer is the receiver's window slot of this (source, destination) pair
+__device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+
+// window[dst][me][parity][pos - off + j] = array[(idx-1)*inner + j]; parity = (messages sent to dst so far + 1) & 1
+__global__ void __launch_bounds__(256) halo_pack_p2p_kernel(const real* __restrict__ array, const int* __restrict__ idx, const long long* __restrict__ pos,
+                                                            const unsigned char* __restrict__ seg, long long n, int inner, P2PSideTab tab,
+                                                            const unsigned long long* __restrict__ seq_send) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n * inner) {
+        const long long e = t / inner;
+        const int j = (int)(t - e * inner);
+        const int s = seg[e];
+        const unsigned long long m = seq_send[tab.rank[s]] + 1ULL;
+        real* dst = tab.slot[s] + (size_t)(m & 1ULL) * (size_t)tab.cap;
+        dst[(size_t)(pos[e] - tab.off[s]) + j] = array[(size_t)(idx[e] - 1) * inner + j];
+    }
+    __threadfence_system();  // the peer stores of this thread are performed before the grid ends (the signal kernel follows)
+}
+
+// one thread per neighbour: count the message and publish its number to the receiver; count the messages about to be received
+__global__ void halo_signal_p2p_kernel(P2PSideTab snd, P2PSideTab rcv, unsigned long long* seq_send, unsigned long long* seq_recv) {
+    const int t = threadIdx.x;
+    if (t < snd.n) {
+        const unsigned long long m = seq_send[snd.rank[t]] + 1ULL;
+        seq_send[snd.rank[t]] = m;
+        __threadfence_system();
+        st_release_sys(snd.flag[t], m);
+    } else if (t >= MPAS_P2P_MAXN && t - MPAS_P2P_MAXN < rcv.n) {
+        seq_recv[rcv.rank[t - MPAS_P2P_MAXN]] += 1ULL;
+    }
+}
+
+// waits until every source of the plan has published the message expected now, then
+// array[(idx-1)*inner + j] = window[me][src][parity][pos - off + j]
+__global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(real* __restrict__ array, const int* __restrict__ idx, const long long* __restrict__ pos,
+                                                              const unsigned char* __restrict__ seg, long long n, int inner, P2PSideTab tab,
+                                                              const unsigned long long* __restrict__ seq_recv, int* timeout_flag) {
+    if ((int)threadIdx.x < tab.n) {
+        const unsigned long long want = seq_recv[tab.rank[threadIdx.x]];
+        const long long t0 = clock64();
+        while (ld_acquire_sys(tab.flag[threadIdx.x]) < want) {
+            if (clock64() - t0 > 8000000000LL) {  // ~4 s: a peer died or the ranks disagree about the exchange sequence
+                *timeout_flag = 1;
+                break;
+            }
+            __nanosleep(100);
+        }
+    }
+    __syncthreads();
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n * inner) return;
+    const long long e = t / inner;
+    const int j = (int)(t - e * inner);
+    const int s = seg[e];
+    const unsigned long long m = seq_recv[tab.rank[s]];
+    const real* src = tab.slot[s] + (size_t)(m & 1ULL) * (size_t)tab.cap;
+    array[(size_t)(idx[e] - 1) * inner + j] = __ldcg(src + (size_t)(pos[e] - tab.off[s]) + j);  // written by the peer: not through L1
+}
+
 bool layer_selected(int mask, int layer) { return mask == 0 || (mask & (1 << (layer - 1))); }
 
 void build_side(const std::vector<HaloItem>& items, const std::vector<HaloList> lists[4], bool is_send, HaloSide& side) {
@@ -37,8 +103,11 @@ void build_side(const std::vector<HaloItem>& items, const std::vector<HaloList> 
     const size_t nI = items.size();
     std::vector<std::vector<int>> idx(nI);
     std::vector<std::vector<long long>> pos(nI);
+    std::vector<std::vector<unsigned char>> seg(nI);
     long long cursor = 0;
+    int inbr = -1;
     for (int n : side.nbr) {
+        ++inbr;
         side.off.push_back(cursor);
         for (size_t i = 0; i < nI; ++i) {
             const HaloItem& it = items[i];
@@ -54,6 +123,7 @@ void build_side(const std::vector<HaloItem>& items, const std::vector<HaloList> 
                     const int slot = is_send ? l->dest[e] : l->src[e];
                     idx[i].push_back(local);
                     pos[i].push_back(cursor + (long long)(slot - 1) * it.inner);
+                    seg[i].push_back((unsigned char)std::min(inbr, 255));
                 }
                 cursor += (long long)l->src.size() * it.inner;
             }
@@ -64,15 +134,19 @@ void build_side(const std::vector<HaloItem>& items, const std::vector<HaloList> 
     for (size_t i = 0; i < nI; ++i) {
         int* di = nullptr;
         long long* dp = nullptr;
+        unsigned char* ds = nullptr;
         side.n.push_back((long long)idx[i].size());
         if (!idx[i].empty()) {
             cudaMalloc(&di, idx[i].size() * sizeof(int));
             cudaMalloc(&dp, pos[i].size() * sizeof(long long));
+            cudaMalloc(&ds, seg[i].size());
             cudaMemcpy(di, idx[i].data(), idx[i].size() * sizeof(int), cudaMemcpyHostToDevice);
             cudaMemcpy(dp, pos[i].data(), pos[i].size() * sizeof(long long), cudaMemcpyHostToDevice);
+            cudaMemcpy(ds, seg[i].data(), seg[i].size(), cudaMemcpyHostToDevice);
         }
         side.d_idx.push_back(di);
         side.d_pos.push_back(dp);
+        side.d_seg.push_back(ds);
     }
     if (side.total > 0) cudaMalloc(&side.d_buf, side.total * sizeof(real));
 }
@@ -80,6 +154,7 @@ void build_side(const std::vector<HaloItem>& items, const std::vector<HaloList> 
 void free_side(HaloSide& s) {
     for (int* p : s.d_idx) cudaFree(p);
     for (long long* p : s.d_pos) cudaFree(p);
+    for (unsigned char* p : s.d_seg) cudaFree(p);
     cudaFree(s.d_buf);
 }
 
@@ -123,6 +198,59 @@ int halo_unpack(HaloPlan* p) {
     }
     cudaError_t e = cudaGetLastError();
     if (e != cudaSuccess) return fail("halo_unpack", e);
+    return 0;
+}
+
+int halo_p2p_tab(const P2P& pp, const HaloSide& side, bool is_send, P2PSideTab& tab) {
+    tab.n = (int)side.nbr.size();
+    tab.cap = pp.cap;
+    if (tab.n > MPAS_P2P_MAXN) return 1;
+    for (int s = 0; s < tab.n; ++s) {
+        const int r = side.nbr[s];
+        if (side.cnt[s] > pp.cap || r < 0 || r >= pp.nranks) return 1;
+        tab.rank[s] = r;
+        tab.off[s] = side.off[s];
+        // send: slot (source = me) and flag (for me) in the destination's window; recv: slot and flag of the source in mine
+        tab.slot[s] = is_send ? pp.slot(pp.peer[r], pp.rank, 0) : pp.slot(pp.win, r, 0);
+        tab.flag[s] = is_send ? pp.flag(pp.peer[r], pp.rank) : pp.flag(pp.win, r);
+    }
+    return 0;
+}
+
+int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2P& pp) {
+    for (size_t i = 0; i < p->items.size(); ++i) {
+        const long long n = p->send.n[i];
+        if (n == 0) continue;
+        const HaloItem& it = p->items[i];
+        halo_pack_p2p_kernel<<<cdiv(n * it.inner, 256), 256, 0, stream()>>>(it.array, p->send.d_idx[i], p->send.d_pos[i], p->send.d_seg[i], n, it.inner, snd,
+                                                                            pp.seq_send);
+        count_launch();
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("halo_pack_p2p", e);
+    return 0;
+}
+
+int halo_signal_p2p(const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp) {
+    if (snd.n == 0 && rcv.n == 0) return 0;
+    halo_signal_p2p_kernel<<<1, 2 * MPAS_P2P_MAXN, 0, stream()>>>(snd, rcv, pp.seq_send, pp.seq_recv);
+    count_launch();
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("halo_signal_p2p", e);
+    return 0;
+}
+
+int halo_unpack_p2p(HaloPlan* p, const P2PSideTab& rcv, const P2P& pp) {
+    for (size_t i = 0; i < p->items.size(); ++i) {
+        const long long n = p->recv.n[i];
+        if (n == 0) continue;
+        const HaloItem& it = p->items[i];
+        halo_unpack_p2p_kernel<<<cdiv(n * it.inner, 256), 256, 0, stream()>>>(it.array, p->recv.d_idx[i], p->recv.d_pos[i], p->recv.d_seg[i], n, it.inner, rcv,
+                                                                              pp.seq_recv, pp.d_timeout);
+        count_launch();
+    }
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail("halo_unpack_p2p", e);
     return 0;
 }
 

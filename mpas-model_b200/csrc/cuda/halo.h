@@ -34,6 +34,7 @@ struct HaloSide {                      // send or recv side of a plan
     std::vector<int*> d_idx;           // per item: local element index (1-based) per list element
     std::vector<long long*> d_pos;     // per item: buffer offset (elements) per list element
     std::vector<long long> n;          // per item: number of list elements
+    std::vector<unsigned char*> d_seg; // per item: index into nbr[] of the neighbour each list element belongs to
     real* d_buf = nullptr;
     long long total = 0;
 };
@@ -65,6 +66,41 @@ struct Nccl {
     void destroy();
     const char* last_error();
 };
+
+// ---- peer-to-peer exchange over NVLink (one process per GPU, all GPUs of one node) -----------------------------------
+// The NCCL send/recv pair of an exchange costs ~40 us for these few-hundred-kilobyte messages: latency, not bandwidth.
+// With the peers' receive windows mapped into this process (CUDA IPC) the pack kernel stores straight into the
+// neighbour's window, one thread then publishes a sequence number per neighbour (st.release.sys) and the neighbour's
+// unpack kernel waits for it (ld.acquire.sys): three plain kernels per exchange, graph-capturable, no proxy thread.
+// Window of a rank: [nranks flags (u64) padded to 256 B][nranks sources x 2 parities x cap reals].  Message m of the
+// pair (src -> dst) goes to parity m & 1: src cannot send message m + 2 before it has unpacked dst's message m + 1,
+// which dst sends only after unpacking m, so two slots per pair suffice.  The per-pair message counters live in device
+// memory (seq_send / seq_recv), so a replayed graph advances them by itself.
+#define MPAS_P2P_MAXN 32
+struct P2PSideTab {  // kernel argument, one per side of a plan
+    real* slot[MPAS_P2P_MAXN];                 // parity-0 slot of this pair: in the peer's window (send) / in mine (recv)
+    long long off[MPAS_P2P_MAXN];              // first element of the neighbour's segment in the packed numbering
+    unsigned long long* flag[MPAS_P2P_MAXN];   // send: the peer's flag for me; recv: my flag for the source
+    int rank[MPAS_P2P_MAXN];                   // neighbour rank
+    int n;
+    long long cap;
+};
+struct P2P {
+    bool on = false, tried = false;
+    int rank = 0, nranks = 1;
+    long long cap = 0;            // slot capacity (reals), the same on every rank
+    char* win = nullptr;          // this rank's window
+    std::vector<char*> peer;      // every rank's window as mapped here (peer[rank] == win)
+    unsigned long long *seq_send = nullptr, *seq_recv = nullptr;  // device, nranks each
+    int* d_timeout = nullptr;     // device: set when a wait gave up (the exchange then delivered stale data)
+    static size_t flag_bytes(int nranks) { return ((size_t)nranks * 8 + 255) & ~(size_t)255; }
+    real* slot(char* w, int src, int par) const { return (real*)(w + flag_bytes(nranks)) + ((size_t)src * 2 + par) * (size_t)cap; }
+    unsigned long long* flag(char* w, int src) const { return (unsigned long long*)w + src; }
+};
+int halo_p2p_tab(const P2P& pp, const HaloSide& side, bool is_send, P2PSideTab& tab);  // non-zero: a message exceeds cap
+int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2P& pp);
+int halo_signal_p2p(const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp);
+int halo_unpack_p2p(HaloPlan* p, const P2PSideTab& rcv, const P2P& pp);
 
 HaloPlan* halo_build_plan(HaloBlock& blk, const std::vector<HaloItem>& items);
 void halo_free_plan(HaloPlan* p);

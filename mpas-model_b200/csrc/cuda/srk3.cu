@@ -521,6 +521,9 @@ int dycore_step(Dycore& m) {
     m.parity ^= 1;
     m.steps_done++;
     flush_timers(m);
+    // both time-level parities have built their exchange plans: switch the exchanges from NCCL send/recv to
+    // peer-to-peer stores when every rank can map every other rank's window (collective, before the graphs are captured)
+    if (m.steps_done == 2 && m.nranks > 1) return dycore_p2p_setup(m);
     return 0;
 }
 

@@ -103,6 +103,7 @@ def lib():
         _lib.mpas_b200_dycore_call.argtypes = [C.c_void_p, C.c_char_p, C.POINTER(C.c_double), C.c_int]
         _lib.mpas_b200_dycore_exchange_count.restype = C.c_long
         _lib.mpas_b200_dycore_exchange_count.argtypes = [C.c_void_p]
+        _lib.mpas_b200_dycore_halo_transport.argtypes = [C.c_void_p]
         _lib.mpas_b200_dycore_set_option.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
         _lib.mpas_b200_dycore_timer_count.argtypes = [C.c_void_p]
         _lib.mpas_b200_dycore_timer_get.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]
@@ -328,6 +329,13 @@ class Dycore:
 
     def exchange_count(self):
         return lib().mpas_b200_dycore_exchange_count(self.h)
+
+    def halo_transport(self):
+        """'none' (one rank), 'nccl' or 'p2p' (stores into the neighbours' mapped receive windows); raises after a p2p timeout"""
+        t = lib().mpas_b200_dycore_halo_transport(self.h)
+        if t < 0:
+            raise RuntimeError("peer-to-peer halo exchange timed out waiting for a neighbour")
+        return {0: "none", 1: "nccl", 2: "p2p"}[t]
 
     def launch_count(self):
         return lib().mpas_b200_launch_count()

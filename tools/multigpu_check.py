@@ -46,9 +46,10 @@ def main():
     e1 = b1.field("indexToEdgeID")[:-1]; inv = np.empty(len(e1), dtype=np.int64); inv[e1 - 1] = np.arange(len(e1))
     same = np.array_equal(dy.field(0, "u@1")[:nE], d1.field(0, "u@1")[inv[eids - 1]])
     ok &= same
+    transport = dy.halo_transport()  # raises after a peer-to-peer timeout
     t = torch.tensor([1 if ok else 0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print("MULTIGPU_CHECK world=%d level=%d steps=%d graph=%d exchanges/step=%.0f -> %s" % (world, level, steps, graph, dy.exchange_count() / steps, "BITWISE EQUAL" if t.item() == 1 else "MISMATCH"), flush=True)
+        print("MULTIGPU_CHECK world=%d level=%d steps=%d graph=%d transport=%s exchanges/step=%.0f -> %s" % (world, level, steps, graph, transport, dy.exchange_count() / steps, "BITWISE EQUAL" if t.item() == 1 else "MISMATCH"), flush=True)
     dy.close(); d1.close()
     dist.destroy_process_group()
     sys.exit(0 if t.item() == 1 else 1)
