@@ -36,18 +36,37 @@ __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned l
     asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
 }
 
+// every field of the exchange group in one launch: item i covers the flat threads [start[i], start[i+1])
+#define MPAS_P2P_MAXITEMS 12
+struct P2PItems {
+    real* array[MPAS_P2P_MAXITEMS];
+    const int* idx[MPAS_P2P_MAXITEMS];
+    const long long* pos[MPAS_P2P_MAXITEMS];
+    const unsigned char* seg[MPAS_P2P_MAXITEMS];
+    long long start[MPAS_P2P_MAXITEMS + 1];
+    int inner[MPAS_P2P_MAXITEMS];
+    int n;
+};
+__device__ __forceinline__ int p2p_find_item(const P2PItems& it, long long t) {
+    int i = 0;
+#pragma unroll 1
+    while (i + 1 < it.n && t >= it.start[i + 1]) ++i;
+    return i;
+}
+
 // window[dst][me][parity][pos - off + j] = array[(idx-1)*inner + j]; parity = (messages sent to dst so far + 1) & 1
-__global__ void __launch_bounds__(256) halo_pack_p2p_kernel(const real* __restrict__ array, const int* __restrict__ idx, const long long* __restrict__ pos,
-                                                            const unsigned char* __restrict__ seg, long long n, int inner, P2PSideTab tab,
-                                                            const unsigned long long* __restrict__ seq_send) {
+__global__ void __launch_bounds__(256) halo_pack_p2p_kernel(P2PItems it, P2PSideTab tab, const unsigned long long* __restrict__ seq_send) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t < n * inner) {
-        const long long e = t / inner;
-        const int j = (int)(t - e * inner);
-        const int s = seg[e];
+    if (t < it.start[it.n]) {
+        const int i = p2p_find_item(it, t);
+        const long long u = t - it.start[i];
+        const int inner = it.inner[i];
+        const long long e = u / inner;
+        const int j = (int)(u - e * inner);
+        const int s = it.seg[i][e];
         const unsigned long long m = seq_send[tab.rank[s]] + 1ULL;
         real* dst = tab.slot[s] + (size_t)(m & 1ULL) * (size_t)tab.cap;
-        dst[(size_t)(pos[e] - tab.off[s]) + j] = array[(size_t)(idx[e] - 1) * inner + j];
+        dst[(size_t)(it.pos[i][e] - tab.off[s]) + j] = it.array[i][(size_t)(it.idx[i][e] - 1) * inner + j];
     }
     __threadfence_system();  // the peer stores of this thread are performed before the grid ends (the signal kernel follows)
 }
@@ -67,9 +86,7 @@ __global__ void halo_signal_p2p_kernel(P2PSideTab snd, P2PSideTab rcv, unsigned 
 
 // waits until every source of the plan has published the message expected now, then
 // array[(idx-1)*inner + j] = window[me][src][parity][pos - off + j]
-__global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(real* __restrict__ array, const int* __restrict__ idx, const long long* __restrict__ pos,
-                                                              const unsigned char* __restrict__ seg, long long n, int inner, P2PSideTab tab,
-                                                              const unsigned long long* __restrict__ seq_recv, int* timeout_flag) {
+__global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(P2PItems it, P2PSideTab tab, const unsigned long long* __restrict__ seq_recv, int* timeout_flag) {
     if ((int)threadIdx.x < tab.n) {
         const unsigned long long want = seq_recv[tab.rank[threadIdx.x]];
         const long long t0 = clock64();
@@ -83,13 +100,16 @@ __global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(real* __restrict__
     }
     __syncthreads();
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n * inner) return;
-    const long long e = t / inner;
-    const int j = (int)(t - e * inner);
-    const int s = seg[e];
+    if (t >= it.start[it.n]) return;
+    const int i = p2p_find_item(it, t);
+    const long long u = t - it.start[i];
+    const int inner = it.inner[i];
+    const long long e = u / inner;
+    const int j = (int)(u - e * inner);
+    const int s = it.seg[i][e];
     const unsigned long long m = seq_recv[tab.rank[s]];
     const real* src = tab.slot[s] + (size_t)(m & 1ULL) * (size_t)tab.cap;
-    array[(size_t)(idx[e] - 1) * inner + j] = __ldcg(src + (size_t)(pos[e] - tab.off[s]) + j);  // written by the peer: not through L1
+    it.array[i][(size_t)(it.idx[i][e] - 1) * inner + j] = __ldcg(src + (size_t)(it.pos[i][e] - tab.off[s]) + j);  // written by the peer: not through L1
 }
 
 bool layer_selected(int mask, int layer) { return mask == 0 || (mask & (1 << (layer - 1))); }
@@ -217,18 +237,35 @@ int halo_p2p_tab(const P2P& pp, const HaloSide& side, bool is_send, P2PSideTab& 
     return 0;
 }
 
-int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2P& pp) {
-    for (size_t i = 0; i < p->items.size(); ++i) {
-        const long long n = p->send.n[i];
-        if (n == 0) continue;
-        const HaloItem& it = p->items[i];
-        halo_pack_p2p_kernel<<<cdiv(n * it.inner, 256), 256, 0, stream()>>>(it.array, p->send.d_idx[i], p->send.d_pos[i], p->send.d_seg[i], n, it.inner, snd,
-                                                                            pp.seq_send);
-        count_launch();
+namespace {
+// item descriptors of one side, in chunks of MPAS_P2P_MAXITEMS (one launch per chunk; exchange groups have <= 8 fields)
+template <class F>
+int p2p_for_chunks(HaloPlan* p, const HaloSide& side, F&& launch) {
+    size_t i = 0;
+    while (i < p->items.size()) {
+        P2PItems it;
+        it.n = 0;
+        it.start[0] = 0;
+        for (; i < p->items.size() && it.n < MPAS_P2P_MAXITEMS; ++i) {
+            if (side.n[i] == 0) continue;
+            const int k = it.n++;
+            it.array[k] = p->items[i].array; it.idx[k] = side.d_idx[i]; it.pos[k] = side.d_pos[i]; it.seg[k] = side.d_seg[i];
+            it.inner[k] = p->items[i].inner;
+            it.start[k + 1] = it.start[k] + side.n[i] * p->items[i].inner;
+        }
+        if (it.n > 0) launch(it);
     }
     cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return fail("halo_pack_p2p", e);
+    if (e != cudaSuccess) return fail("halo p2p launch", e);
     return 0;
+}
+}  // namespace
+
+int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2P& pp) {
+    return p2p_for_chunks(p, p->send, [&](const P2PItems& it) {
+        halo_pack_p2p_kernel<<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, snd, pp.seq_send);
+        count_launch();
+    });
 }
 
 int halo_signal_p2p(const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp) {
@@ -241,17 +278,10 @@ int halo_signal_p2p(const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp)
 }
 
 int halo_unpack_p2p(HaloPlan* p, const P2PSideTab& rcv, const P2P& pp) {
-    for (size_t i = 0; i < p->items.size(); ++i) {
-        const long long n = p->recv.n[i];
-        if (n == 0) continue;
-        const HaloItem& it = p->items[i];
-        halo_unpack_p2p_kernel<<<cdiv(n * it.inner, 256), 256, 0, stream()>>>(it.array, p->recv.d_idx[i], p->recv.d_pos[i], p->recv.d_seg[i], n, it.inner, rcv,
-                                                                              pp.seq_recv, pp.d_timeout);
+    return p2p_for_chunks(p, p->recv, [&](const P2PItems& it) {
+        halo_unpack_p2p_kernel<<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, rcv, pp.seq_recv, pp.d_timeout);
         count_launch();
-    }
-    cudaError_t e = cudaGetLastError();
-    if (e != cudaSuccess) return fail("halo_unpack_p2p", e);
-    return 0;
+    });
 }
 
 // ---- NCCL via dlopen ------------------------------------------------------------------------
