@@ -301,12 +301,12 @@ def run_b200(a):
                 "traffic": None, "peak_source": peak_src,
                 "note": "achieved = SURVEY 8(d) words x 8 B x owned cell-levels per call / CUDA-event time per call (eager pass after the timed region)"}
     # traffic: DRAM bytes (read + write) per call of the dominant routine from the committed ncu capture of this same command
-    # (profiles/r01_c_dram_traffic.json, tools/dram_traffic.py); only valid for the default workload on one GPU
+    # (profiles/r01_d_dram_traffic.json, tools/dram_traffic.py); only valid for the default workload on one GPU
     try:
         if N == 1 and a.level == 7 and a.levels == 55 and a.scalars == 4:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_c_dram_traffic.json")))
+            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_d_dram_traffic.json")))
             roofline["traffic"] = tr[dom]["dram_GB_per_step"] / phases[dom]["calls_per_step"]
-            roofline["traffic_unit"] = "GB per call (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_c_dram_traffic.csv)"
+            roofline["traffic_unit"] = "GB per call (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_d_dram_traffic.csv)"
             roofline["algorithmic_GB_per_call"] = phases[dom]["algorithmic_GB_per_call"]
             roofline["whole_step_traffic_GB"] = tr["_whole_step"]["dram_GB_per_step"]
     except Exception:

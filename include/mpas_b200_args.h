@@ -176,7 +176,9 @@ typedef double mpas_real;
 
 /* Halo-exchange hook for the two exchanges embedded in atm_advance_scalars_mono_work
  * (TI:3757 scalars_old, all halo layers; TI:4098 scale_arr, halo layer 1).  which: 0 = scalars_old
- * (num_scalars, nVertLevels, nCells+1), 1 = scale_arr (nVertLevels, 2, nCells+1).  NULL = single block. */
+ * (num_scalars, nVertLevels, nCells+1), 1 = scale_arr (nVertLevels, 2, nCells+1) of the per-scalar path,
+ * 2 = the scale factors of ALL scalars at once, a library workspace array (2*num_scalars*nVertLevels, nCells+1)
+ * passed as `array` (default all-scalars path, halo layer 1).  NULL = single block. */
 typedef int (*mpas_halo_fn)(void *ctx, int which, mpas_real *array);
 
 /* atm_advance_scalars_mono_work, TI:3612-3621 (block/state replaced by the exchange hook) */

@@ -1,6 +1,6 @@
 """Per-kernel and per-routine DRAM traffic from an ncu CSV with dram__bytes_read.sum, dram__bytes_write.sum and
 gpu__time_duration.sum of every launch of `bench.py --steps 2 --warmup 3 --no-graph` (7 steps after init).
-usage: python tools/dram_traffic.py gpurun_out/dram.csv profiles/r01_c_dram_traffic.json > profiles/r01_c_dram_traffic.csv"""
+usage: python tools/dram_traffic.py gpurun_out/dram.csv profiles/r01_d_dram_traffic.json > profiles/r01_d_dram_traffic.csv"""
 import csv
 import json
 import re
@@ -10,7 +10,7 @@ from collections import OrderedDict
 ROUTINE = [("dt_", "atm_compute_dyn_tend"), ("acoustic_", "atm_advance_acoustic_step"), ("divdamp", "atm_divergence_damping_3d"),
            ("recover_", "atm_recover_large_step_variables"), ("set_garbage", "atm_recover_large_step_variables"), ("smlstep", "small_step_prep"),
            ("sd_", "atm_compute_solve_diagnostics"), ("vert_imp", "atm_compute_vert_imp_coefs"), ("cofrz", "atm_compute_vert_imp_coefs"),
-           ("as_", "atm_advance_scalars"), ("mono_", "atm_advance_scalars_mono"), ("ax_", "atm_advance_scalars_mono"),
+           ("as_", "atm_advance_scalars"), ("mono_", "atm_advance_scalars_mono"), ("monoN_", "atm_advance_scalars_mono"), ("ax_", "atm_advance_scalars_mono"),
            ("moist_", "atm_compute_moist_coefficients"), ("substep_finish", "atm_rk_dynamics_substep_finish"), ("halo_", "halo_exchange")]
 NSTEPS = 7  # 3 warm-up + 2 timed + 2 steps of the eager per-routine timing pass
 
