@@ -50,8 +50,8 @@ struct DtP {
 
 // Load-first flat kernels: the index loads of all stencil slots, then the data loads (in batches that fit the register
 // budget), then the sums in the reference's order.  Slots beyond nEdgesOnCell repeat slot 1 and are left out of the sums.
-template <int NE, bool SMAG>
-__global__ void __launch_bounds__(256, SMAG ? 3 : 4) dt_cell_pre_kernel(DtP p) {
+template <int NE, bool SMAG, int MINB = (SMAG ? 3 : 4)>
+__global__ void __launch_bounds__(256, MINB) dt_cell_pre_kernel(DtP p) {
     const int L = p.L, L1 = L + 1, mE = p.mE;
     FLAT_KC(p.nCellsLoop, L);
     const int iCell = p.cellStart + _c0;
@@ -128,7 +128,8 @@ __global__ void __launch_bounds__(256, SMAG ? 3 : 4) dt_cell_pre_kernel(DtP p) {
     }
 }
 
-__global__ void __launch_bounds__(256) dt_edge_mix_kernel(DtP p) {  // rk_step == 1 only
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) dt_edge_mix_kernel(DtP p) {  // rk_step == 1 only
     const int L = p.L;
     FLAT_KC(p.nEdgesLoop, L);
     const int iEdge = p.edgeStart + _c0;
@@ -165,7 +166,8 @@ __global__ void __launch_bounds__(256) dt_vertex_mix_kernel(DtP p) {  // rk_step
     p.delsq_vorticity[IX2(k, iVertex, L)] = s;
 }
 
-__global__ void __launch_bounds__(256) dt_cell_mix_kernel(DtP p) {  // rk_step == 1
+template <int MINB>
+__global__ void __launch_bounds__(256, MINB) dt_cell_mix_kernel(DtP p) {  // rk_step == 1
     const int L = p.L, L1 = L + 1, mE = p.mE;
     FLAT_KC(p.nCellsLoop, L1);
     const int iCell = p.cellStart + _c0;
@@ -228,8 +230,8 @@ __global__ void __launch_bounds__(256) dt_cell_mix_kernel(DtP p) {  // rk_step =
 // (c + c3, c - c3), padded with zero coefficients to a multiple of FUNR (flux + 0*x == flux exactly, flux is never -0);
 // each lane selects its table by the sign of its own ru once per level.
 #define FUNR 5
-template <bool RK1>
-__global__ void __launch_bounds__(WPB * 32) dt_edge_flux_kernel(DtP p, real* __restrict__ ft, real* __restrict__ fw, real* __restrict__ ft2) {
+template <bool RK1, int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) dt_edge_flux_kernel(DtP p, real* __restrict__ ft, real* __restrict__ fw, real* __restrict__ ft2) {
     __shared__ unsigned s_ot[WPB][20], s_ow[WPB][20];
     __shared__ real s_cp[WPB][20], s_cm[WPB][20];
     const int L = p.L, L1 = L + 1;
@@ -824,7 +826,9 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
         const bool smag = (rk_step == 1 && config_horiz_mixing == 1);
         const long long nt = (long long)p.nCellsLoop * L;
         if (maxEdges <= 6) {
-            if (smag) KLAUNCH((dt_cell_pre_kernel<6, true>), nt, 256, p);
+            static const int pre_minb = tune("dt_pre_minb", 4);
+            if (smag && pre_minb == 4) KLAUNCH((dt_cell_pre_kernel<6, true, 4>), nt, 256, p);
+            else if (smag) KLAUNCH((dt_cell_pre_kernel<6, true>), nt, 256, p);
             else KLAUNCH((dt_cell_pre_kernel<6, false>), nt, 256, p);
         } else {
             if (smag) KLAUNCH((dt_cell_pre_kernel<8, true>), nt, 256, p);
@@ -833,13 +837,17 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     }
     KCHECK("dt_cell_pre_kernel");
     if (rk_step == 1) {
-        KLAUNCH(dt_edge_mix_kernel, (long long)p.nEdgesLoop * L, 256, p);
+        static const int emix_minb = tune("dt_emix_minb", 6), cmix_minb = tune("dt_cmix_minb", 0);
+        if (emix_minb == 6) KLAUNCH(dt_edge_mix_kernel<6>, (long long)p.nEdgesLoop * L, 256, p);
+        else KLAUNCH(dt_edge_mix_kernel<0>, (long long)p.nEdgesLoop * L, 256, p);
         KCHECK("dt_edge_mix_kernel");
         if (p.h_mom_eddy_visc4 > (real)0.0) {
             KLAUNCH(dt_vertex_mix_kernel, (long long)p.nVerticesLoop * L, 256, p);
             KCHECK("dt_vertex_mix_kernel");
         }
-        KLAUNCH(dt_cell_mix_kernel, (long long)p.nCellsLoop * (L + 1), 256, p);
+        if (cmix_minb == 5) KLAUNCH(dt_cell_mix_kernel<5>, (long long)p.nCellsLoop * (L + 1), 256, p);
+        else if (cmix_minb == 6) KLAUNCH(dt_cell_mix_kernel<6>, (long long)p.nCellsLoop * (L + 1), 256, p);
+        else KLAUNCH(dt_cell_mix_kernel<0>, (long long)p.nCellsLoop * (L + 1), 256, p);
         KCHECK("dt_cell_mix_kernel");
     }
     if (maxEdges > 8 || maxEdges2 > 16) return fail_msg("mpas_b200_compute_dyn_tend_work: maxEdges > 8 or maxEdges2 > 16 not supported");
@@ -848,8 +856,11 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     real* fw = workspace(1, nEL);
     real* ft2 = workspace(2, nEL);
     if (!ft || !fw || !ft2) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace");
-    if (rk_step == 1) WLAUNCH(dt_edge_flux_kernel<true>, p.nEdgesLoop, 0, p, ft, fw, ft2);
-    else WLAUNCH(dt_edge_flux_kernel<false>, p.nEdgesLoop, 0, p, ft, fw, ft2);
+    static const int flux_minb = tune("dt_flux_minb", 6);
+    if (rk_step == 1) WLAUNCH((dt_edge_flux_kernel<true, 0>), p.nEdgesLoop, 0, p, ft, fw, ft2);
+    else if (flux_minb == 5) WLAUNCH((dt_edge_flux_kernel<false, 5>), p.nEdgesLoop, 0, p, ft, fw, ft2);
+    else if (flux_minb == 6) WLAUNCH((dt_edge_flux_kernel<false, 6>), p.nEdgesLoop, 0, p, ft, fw, ft2);
+    else WLAUNCH((dt_edge_flux_kernel<false, 0>), p.nEdgesLoop, 0, p, ft, fw, ft2);
     KCHECK("dt_edge_flux_kernel");
     {
         const size_t shm = (size_t)WPB * (rk_step == 1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * tma_slot(L + 1) * sizeof(real);

@@ -24,7 +24,7 @@ struct RecCellP {
     real *wwAvg, *w, *rw, *rtheta_p, *rho_p, *rho_zz, *exner, *pressure_p, *theta_m;
 };
 
-__global__ void __launch_bounds__(256) recover_cell_kernel(RecCellP p) {
+__global__ void __launch_bounds__(256, 8) recover_cell_kernel(RecCellP p) {
     const int L = p.L, L1 = L + 1;
     FLAT_KC(p.nCellsLoop, L1);
     const int iCell = p.cellStart + _c0;
@@ -105,7 +105,7 @@ struct RecWP {
 // dependent add (index loads, then ru / zb / zb3 loads, then the sum in the reference's order), so a thread waits for
 // memory twice instead of twice per edge.  Slots beyond nEdgesOnCell repeat edge 1 and are skipped in the sum.
 template <int NE>
-__global__ void __launch_bounds__(256, NE <= 6 ? 3 : 2) recover_w_kernel(RecWP p) {
+__global__ void __launch_bounds__(256, NE <= 6 ? 4 : 2) recover_w_kernel(RecWP p) {
     const int L = p.L, L1 = L + 1, mE = p.mE;
     FLAT_KC(p.nCellsLoop, L);
     const int iCell = p.cellStart + _c0;

@@ -108,7 +108,8 @@ enum { ASC_SCAL, ASC_WW, ASC_NTMA };
 // per (scalar, interface) into shared memory; the edge sum is a direct gather, two elements per lane, the edge list
 // staged as offsets and signs padded to 6 or 8 with zero signs (x - 0*y == x).
 // dynamic shared memory per warp: tma_slot(ns*L) + tma_slot(L+1) + ns*(L+1) reals.
-__global__ void __launch_bounds__(WPB * 32, 4) as_cell_kernel(AsP p) {
+template <int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) as_cell_kernel(AsP p) {
     extern __shared__ __align__(16) real s_dyn[];
     __shared__ __align__(8) unsigned long long s_bar[WPB];
     __shared__ unsigned s_eL[WPB][8], s_eF[WPB][8];
@@ -880,7 +881,10 @@ extern "C" int mpas_b200_advance_scalars_work(MPAS_ADVSCALARS_ARGS) {
     if (p.nCellsSolveLoop > 0) {
         if (p.mE > 8) return fail_msg("mpas_b200_advance_scalars_work: maxEdges > 8 not supported");
         const size_t shm = (size_t)WPB * (tma_slot(p.L * p.ns) + tma_slot(p.L + 1) + ((p.ns * (p.L + 1) + 3) & ~3)) * sizeof(real);
-        WLAUNCH(as_cell_kernel, p.nCellsSolveLoop, shm, p);
+        static const int ascell_minb = tune("as_cell_minb", 4);
+        if (ascell_minb == 5) WLAUNCH(as_cell_kernel<5>, p.nCellsSolveLoop, shm, p);
+        else if (ascell_minb == 6) WLAUNCH(as_cell_kernel<6>, p.nCellsSolveLoop, shm, p);
+        else WLAUNCH(as_cell_kernel<4>, p.nCellsSolveLoop, shm, p);
         KCHECK("as_cell_kernel");
     }
     return 0;
