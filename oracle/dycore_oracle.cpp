@@ -652,7 +652,7 @@ int oracle_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
                 for (int k = 1; k <= L; ++k) {
                     real cl = (c_s * config_len_disp);
                     kdiff[IX2(k, iCell, L)] = std::min((cl * cl) * std::sqrt(d_diag[k] * d_diag[k] + d_off_diag[k] * d_off_diag[k]),
-                                                       (0.01 * (config_len_disp * config_len_disp)) * invDt);
+                                                       (real)((0.01 * (config_len_disp * config_len_disp)) * invDt));
                 }
             }
             h_mom_eddy_visc4 = config_visc4_2dsmag * (config_len_disp * config_len_disp * config_len_disp);
@@ -665,9 +665,9 @@ int oracle_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
         }
         if (config_mpas_cam_coef > 0.0) {
             for (int iCell = cellStart; iCell <= cellEnd; ++iCell) {
-                kdiff[IX2(L - 2, iCell, L)] = std::max(kdiff[IX2(L - 2, iCell, L)], 2.0833 * config_len_disp * config_mpas_cam_coef);
-                kdiff[IX2(L - 1, iCell, L)] = std::max(kdiff[IX2(L - 1, iCell, L)], 2.0 * 2.0833 * config_len_disp * config_mpas_cam_coef);
-                kdiff[IX2(L, iCell, L)] = std::max(kdiff[IX2(L, iCell, L)], 4.0 * 2.0833 * config_len_disp * config_mpas_cam_coef);
+                kdiff[IX2(L - 2, iCell, L)] = std::max(kdiff[IX2(L - 2, iCell, L)], (real)(2.0833 * config_len_disp * config_mpas_cam_coef));
+                kdiff[IX2(L - 1, iCell, L)] = std::max(kdiff[IX2(L - 1, iCell, L)], (real)(2.0 * 2.0833 * config_len_disp * config_mpas_cam_coef));
+                kdiff[IX2(L, iCell, L)] = std::max(kdiff[IX2(L, iCell, L)], (real)(4.0 * 2.0833 * config_len_disp * config_mpas_cam_coef));
             }
         }
     }

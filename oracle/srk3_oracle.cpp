@@ -9,6 +9,7 @@
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
+#include <list>
 #include <map>
 #include <mutex>
 #include <stdexcept>
@@ -92,6 +93,7 @@ struct Barrier {
 
 struct OModel {
     std::vector<OBlock> blocks;
+    std::list<std::vector<real>> owned;  // single-precision build: float copies of the double host pools
     Barrier bar;
     std::string err;
     long nExchanges = 0;
@@ -454,6 +456,25 @@ int oracle_model_set_field(void* h, int ib, const char* name, void* ptr, int inn
     OModel* m = (OModel*)h;
     OField f;
     f.ptr = ptr; f.inner = inner; f.loc = loc;
+    m->blocks[ib].f[name] = f;
+    return 0;
+}
+// sizeof(mpas_real) of this build (liboracle_sp.so = -DSINGLE_PRECISION, the reference's PRECISION=single)
+int oracle_real_size() { return (int)sizeof(real); }
+// A REAL field of the (double) host pool.  The double build works in place on `ptr`; the single-precision build keeps
+// its own float copy (owned by the model, handed out by oracle_model_get_field).
+int oracle_model_set_field_f64(void* h, int ib, const char* name, double* ptr, long long count, int inner, int loc) {
+    OModel* m = (OModel*)h;
+    OField f;
+    f.inner = inner; f.loc = loc;
+    if (sizeof(real) == sizeof(double)) {
+        f.ptr = ptr;
+    } else {
+        m->owned.emplace_back((size_t)count);
+        std::vector<real>& v = m->owned.back();
+        for (long long i = 0; i < count; ++i) v[(size_t)i] = (real)ptr[i];
+        f.ptr = v.data();
+    }
     m->blocks[ib].f[name] = f;
     return 0;
 }

@@ -29,8 +29,10 @@ host = load_pkg_module("host")
 ORACLE_DIR = os.path.join(ROOT, "oracle")
 ORACLE_LIB = os.path.join(ORACLE_DIR, "_build", "liboracle.so")
 ORACLE_PERF_LIB = os.path.join(ORACLE_DIR, "_build", "liboracle_perf.so")  # -O3 -march=native: the timed CPU baseline
+ORACLE_SP_LIB = os.path.join(ORACLE_DIR, "_build", "liboracle_sp.so")  # mpas_real = float (PRECISION=single)
 _oracle = None
 _oracle_perf = None
+_oracle_sp = None
 
 # nominal grid spacing (m) and time step (s) per icosahedral level; config_dt scales with dx from the
 # Registry default 720 s at 120 km (Registry.xml nhyd_model record)
@@ -42,8 +44,15 @@ def level_config(level):
     return dict(config_dt=720.0 * dx / 120000.0, config_len_disp=dx)
 
 
-def oracle(perf=False):
-    global _oracle, _oracle_perf
+def oracle(perf=False, single=False):
+    global _oracle, _oracle_perf, _oracle_sp
+    if single:
+        if _oracle_sp is None:
+            if not os.path.exists(ORACLE_SP_LIB):
+                subprocess.check_call(["make", "-s", "-C", ORACLE_DIR])
+            _oracle_sp = _bind_oracle(C.CDLL(ORACLE_SP_LIB))
+            assert _oracle_sp.oracle_real_size() == 4
+        return _oracle_sp
     if perf:
         if _oracle_perf is None:
             if not os.path.exists(ORACLE_PERF_LIB):
@@ -75,14 +84,18 @@ def _bind_oracle(L):
         L.oracle_model_exchange_count.argtypes = [C.c_void_p]
         L.oracle_model_get_field.restype = C.c_void_p
         L.oracle_model_get_field.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
+        L.oracle_model_set_field_f64.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int]
     return L
 
 
 class OracleModel:
     """P virtual ranks of the oracle dycore operating in place on the host blocks' pools."""
 
-    def __init__(self, blocks, cfg, perf=False):
-        self.L = oracle(perf)
+    def __init__(self, blocks, cfg, perf=False, single=False):
+        """single=True: the float build of the oracle; it keeps its own float copies of the real fields (the host pools stay
+        untouched), field() then returns float32 arrays."""
+        self.L = oracle(perf, single)
+        self.single = single
         self.blocks = blocks
         self.h = self.L.oracle_model_create(len(blocks))
         self._keep = []
@@ -91,7 +104,10 @@ class OracleModel:
                 kind, loc, dims = b.info(name)
                 inner = int(np.prod(dims[:-1])) if len(dims) > 1 else 1
                 ptr = host.lib().mpas_host_block_field_ptr(b.h, name.encode())
-                self.L.oracle_model_set_field(self.h, ib, name.encode(), ptr, inner, loc)
+                if kind == 0:
+                    self.L.oracle_model_set_field_f64(self.h, ib, name.encode(), ptr, int(np.prod(dims)), inner, loc)
+                else:
+                    self.L.oracle_model_set_field(self.h, ib, name.encode(), ptr, inner, loc)
             allcfg = dict(b.cfg())
             allcfg.update(cfg)
             for k, v in allcfg.items():
@@ -127,7 +143,7 @@ class OracleModel:
         kind, loc, dims = b.info(name)
         ptr = self.L.oracle_model_get_field(self.h, ib, name.encode())
         n = int(np.prod(dims))
-        ct = C.c_double if kind == 0 else C.c_int32
+        ct = (C.c_float if self.single else C.c_double) if kind == 0 else C.c_int32
         return np.ctypeslib.as_array(C.cast(ptr, C.POINTER(ct)), shape=(n,)).reshape(tuple(reversed(dims)))
 
     def exchange_count(self):

@@ -36,3 +36,5 @@ def test_single_precision_build_within_1e5_of_the_double_oracle(blocks):
         for name in ("u@1", "theta_m@1", "rho_zz@1", "scalars@1"):
             assert res[name] <= TOL_SINGLE, (nsteps, name, res[name])
         assert res["w_abs_over_max_u"] <= TOL_SINGLE, (nsteps, res)
+        for name, e in res["vs_float_oracle"].items():  # float kernels against the float oracle
+            assert e <= TOL_SINGLE, (nsteps, name, e)

@@ -6,7 +6,8 @@ Run as its own process (one precision per process, mpas-model_b200/host.py):
 
 The float32 device dycore (libmpas_b200_sp.so, the same kernel sources with -DSINGLE_PRECISION) and the double CPU
 oracle start from the same JW state (the oracle's in double, the device's rounded to float on upload) and take 1 and
-10 steps; one JSON line with the relative L2 difference of every prognostic field after each is printed.
+10 steps; one JSON line with the relative L2 difference of every prognostic field after each is printed, plus the
+difference to the FLOAT build of the oracle (oracle/_build/liboracle_sp.so) under "vs_float_oracle".
 The reference's single build rounds the same way: RKIND reals everywhere (src/framework/mpas_kind_types.F:25-29).
 """
 import argparse
@@ -39,8 +40,10 @@ def main():
             s[:-1, :, 1] = (np.cos(lat) ** 2)[:-1, None]
     cfg = common.level_config(a.level)
     gpu = common.GpuModel(blocks, cfg)
-    ora = common.OracleModel(blocks, cfg)
+    ora32 = common.OracleModel(blocks, cfg, single=True)  # float build of the oracle: its own float copies of the initial pools
+    ora = common.OracleModel(blocks, cfg)                 # double oracle, in place on the host pools
     gpu.init()
+    ora32.init()
     ora.init()
     names = ["u@1", "w@1", "theta_m@1", "rho_zz@1", "scalars@1"]
     out = {"real_size": 4, "level": a.level, "nVertLevels": a.levels, "num_scalars": a.scalars, "blocks": a.blocks, "after": {}}
@@ -48,8 +51,14 @@ def main():
     for target in (1, 10):
         gpu.step(target - done)
         ora.step(target - done)
+        ora32.step(target - done)
         done = target
         res = {}
+        # float kernels against the FLOAT oracle (same rounding of the inputs; the oracle evaluates expressions with double
+        # literals in double, the kernels in float, so this is close but not bitwise)
+        res["vs_float_oracle"] = {n: max(float(common.rel_l2(gpu.field(ib, n)[:int(b.cfg()[{1: "nCellsSolve", 2: "nEdgesSolve", 3: "nVerticesSolve"}[b.info(n)[1]]])],
+                                                             ora32.field(ib, n)[:int(b.cfg()[{1: "nCellsSolve", 2: "nEdgesSolve", 3: "nVerticesSolve"}[b.info(n)[1]]])]))
+                                         for ib, b in enumerate(blocks)) for n in names if n != "w@1"}
         for n in names:
             worst = 0.0
             for ib, b in enumerate(blocks):
