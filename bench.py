@@ -209,7 +209,9 @@ def run_b200(a):
     case = host.HostCase(a.level, lloyd_iters=a.lloyd, sfc=True)
     if N > 1:
         case.partition(N, "metis")
-    block = case.build_block(rank, nVertLevels=a.levels, init_case=2, num_scalars=a.scalars, full_fields=True)
+    # "lean": the work / tendency arrays (all zero at start, 83 % of a block's words) get no host storage, their device mirrors
+    # are created zero-filled from the metadata -- what lets the 15 km mesh be set up by 2..8 ranks within the host's memory
+    block = case.build_block(rank, nVertLevels=a.levels, init_case=2, num_scalars=a.scalars, full_fields="lean")
     set_tracers(block, a.scalars)
     cfg = common.level_config(a.level)
     dy = host.Dycore([block], cfg, rank=rank, nranks=N, device=local_rank)

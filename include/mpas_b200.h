@@ -108,6 +108,9 @@ void* mpas_host_case_block(void* h, int iBlock);
 int mpas_host_block_nfields(void* b);
 int mpas_host_block_field_info(void* b, int idx, char* name, int name_cap, int* kind, int* loc, int* ndims, long long* dims);
 void* mpas_host_block_field_ptr(void* b, const char* name);
+/* lean blocks (mpas_host_case_build_block full_fields = 2): the work arrays that are all zero when a block has been built
+ * get no host storage until mpas_host_block_field_ptr is asked for them; 1 = no storage yet, 0 = has storage, -1 = no such field */
+int mpas_host_block_field_is_lean(void* block, const char* name);
 int mpas_host_block_ncfg(void* b);
 int mpas_host_block_cfg_info(void* b, int idx, char* name, int name_cap, double* value);
 int mpas_host_block_nexch(void* b, int kind, int which);

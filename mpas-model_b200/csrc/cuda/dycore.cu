@@ -315,6 +315,7 @@ int mpas_b200_dycore_attach_block(void* h, int iLocal, void* hostBlock) {
         const mpas::Field& fl = kv.second;
         std::vector<long long> dims(fl.dims.begin(), fl.dims.end());
         const void* src = fl.kind == mpas::FK_REAL ? (const void*)fl.r.data() : (const void*)fl.i.data();
+        if (fl.kind == mpas::FK_REAL && fl.zero && fl.r.empty()) src = nullptr;  // lean block: zero-filled mirror from the metadata alone
         int rc = add_field(blk, kv.first, src, fl.kind == mpas::FK_REAL ? 0 : 1, (int)fl.loc, dims);
         if (rc) return rc;
     }

@@ -125,7 +125,7 @@ int mpas_host_case_build_block(void* h, int iBlock, int nVertLevels, int init_ca
     init_case_jw(blk->mesh, hc->cfg, p);
     core_init_derived(blk->mesh, hc->cfg, p);
     init_reconstruct(blk->mesh, p);
-    allocate_dycore_fields(blk->mesh, hc->cfg, p, full_fields != 0);
+    allocate_dycore_fields(blk->mesh, hc->cfg, p, full_fields);
     p.cfg["config_coef_3rd_order"] = hc->cfg.coef_3rd_order;
     hc->blocks[iBlock] = std::move(blk);
     return 0;
@@ -156,7 +156,16 @@ void* mpas_host_block_field_ptr(void* b, const char* name) {
     Pool& p = ((Block*)b)->pool;
     auto it = p.f.find(name);
     if (it == p.f.end()) { mpas::g_last_error = std::string("no field ") + name; return nullptr; }
+    it->second.materialize();  // a lean block's zero field gets its host storage when somebody looks at it
     return it->second.kind == FK_REAL ? (void*)it->second.r.data() : (void*)it->second.i.data();
+}
+
+// 1: the field is an all-zero real field of a lean block that has no host storage (yet); 0 otherwise; -1 unknown name
+int mpas_host_block_field_is_lean(void* b, const char* name) {
+    Pool& p = ((Block*)b)->pool;
+    auto it = p.f.find(name);
+    if (it == p.f.end()) return -1;
+    return (it->second.kind == FK_REAL && it->second.zero && it->second.r.empty()) ? 1 : 0;
 }
 
 int mpas_host_block_ncfg(void* b) { return (int)((Block*)b)->pool.cfg.size(); }

@@ -51,6 +51,6 @@ void core_init_derived(const Mesh& m, const InitConfig& cfg, Pool& p);
 void init_reconstruct(const Mesh& m, Pool& p);
 
 // allocate the remaining state/diag/tend fields the dycore uses (zero filled)
-void allocate_dycore_fields(const Mesh& m, const InitConfig& cfg, Pool& p, bool full);
+void allocate_dycore_fields(const Mesh& m, const InitConfig& cfg, Pool& p, int full);  // 0 none, 1 with host storage, 2 lean (Field::zero)
 
 }  // namespace mpas

@@ -196,12 +196,20 @@ void core_init_derived(const Mesh& m, const InitConfig& cfg, Pool& p) {
 
 // State/diag/tend fields of the dycore (Registry.xml:1412 state, :1506 diag, :1709 tend).
 // full=false allocates only what a device-resident run still needs on the host.
-void allocate_dycore_fields(const Mesh& m, const InitConfig& cfg, Pool& p, bool full) {
+// full = 2 ("lean"): the same fields, but without host storage (Field::zero) -- they are all zero at this point, the last
+// step of building a block, and the device mirrors are created zero-filled from the metadata; a 15 km block then needs
+// 3 GB of host memory instead of 20.
+void allocate_dycore_fields(const Mesh& m, const InitConfig& cfg, Pool& p, int full) {
     const int nC = m.nCells + 1, nE = m.nEdges + 1, nV = m.nVertices + 1, L = cfg.nVertLevels, ns = cfg.num_scalars;
-    auto C = [&](const char* n) { if (!p.has(n)) p.addr(n, LOC_CELL, {L, nC}); };
-    auto C1 = [&](const char* n) { if (!p.has(n)) p.addr(n, LOC_CELL, {L + 1, nC}); };
-    auto E = [&](const char* n) { if (!p.has(n)) p.addr(n, LOC_EDGE, {L, nE}); };
-    auto V = [&](const char* n) { if (!p.has(n)) p.addr(n, LOC_VERTEX, {L, nV}); };
+    auto add = [&](const char* n, FieldLoc loc, std::vector<int64_t> dims) {
+        if (p.has(n)) return;
+        if (full == 2) p.addz(n, loc, dims);
+        else p.addr(n, loc, dims);
+    };
+    auto C = [&](const char* n) { add(n, LOC_CELL, {L, nC}); };
+    auto C1 = [&](const char* n) { add(n, LOC_CELL, {L + 1, nC}); };
+    auto E = [&](const char* n) { add(n, LOC_EDGE, {L, nE}); };
+    auto V = [&](const char* n) { add(n, LOC_VERTEX, {L, nV}); };
     if (!p.has("scalars@1")) p.addr("scalars@1", LOC_CELL, {ns, L, nC});
     if (!full) return;
     for (const char* n : {"u@2", "ru", "ru_save", "ru_p", "ruAvg", "ruAvg_split", "rho_edge", "pv_edge", "v", "cqu", "gradPVn", "gradPVt",
@@ -215,11 +223,11 @@ void allocate_dycore_fields(const Mesh& m, const InitConfig& cfg, Pool& p, bool 
                           "rt_diabatic_tend", "scalar_old", "scalar_new", "s_max", "s_min", "rho_zz_int", "uReconstructX", "uReconstructY",
                           "uReconstructZ", "uReconstructZonal", "uReconstructMeridional"}) C(n);
     for (const char* n : {"vorticity", "pv_vertex", "ke_vertex", "delsq_vorticity"}) V(n);
-    if (!p.has("scalars@2")) p.addr("scalars@2", LOC_CELL, {ns, L, nC});
-    if (!p.has("scalars_tend")) p.addr("scalars_tend", LOC_CELL, {ns, L, nC});
-    if (!p.has("scale_arr")) p.addr("scale_arr", LOC_CELL, {L, 2, nC});
-    if (!p.has("horiz_flux_arr")) p.addr("horiz_flux_arr", LOC_EDGE, {ns, L, nE});
-    if (!p.has("cofrz")) p.addr("cofrz", LOC_NONE, {L});
+    add("scalars@2", LOC_CELL, {ns, L, nC});
+    add("scalars_tend", LOC_CELL, {ns, L, nC});
+    add("scale_arr", LOC_CELL, {L, 2, nC});
+    add("horiz_flux_arr", LOC_EDGE, {ns, L, nE});
+    add("cofrz", LOC_NONE, {L});
 }
 
 }  // namespace mpas

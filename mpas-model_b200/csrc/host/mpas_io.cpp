@@ -193,6 +193,7 @@ void write_restart_block(const std::string& path, const Block& b, const std::vec
     const int index_qv = p.cfg.count("index_qv") ? (int)p.cfg.at("index_qv") : 1;
     std::vector<double> col;
     for (const std::string& n : names) {
+        const_cast<Field&>(p.f.at(n)).materialize();  // lean block: a zero field gets storage before it is read (contents unchanged)
         const Field& fl = p.f.at(n);
         const std::vector<int>& ids = ids_of(b.mesh, fl.loc);
         const int nown = owned_count(b.mesh, fl.loc);
@@ -244,6 +245,7 @@ int read_restart_block(const std::string& path, Block& b) {
         if (fl.dims.size() == 3) {
             const int ns = (int)fl.dims[0], L = (int)fl.dims[1];
             if (restart_var_name(kv.first) != "scalars") continue;
+            fl.materialize();
             col.resize(L);
             bool any = false;
             for (int iq = 1; iq <= ns; ++iq) {
@@ -259,6 +261,7 @@ int read_restart_block(const std::string& path, Block& b) {
         } else {
             const int id = f.find_var(restart_var_name(kv.first));
             if (id < 0) continue;
+            fl.materialize();
             const nc::Var& v = f.vars[id];
             if (!v.record) continue;
             const int64_t inner = fl.inner();

@@ -30,6 +30,14 @@ struct Field {
     std::vector<int64_t> dims;  // Fortran order, fastest first; last dim includes the +1 element
     std::vector<real_t> r;
     std::vector<int32_t> i;
+    // zero = true: a real field whose every element is 0 and whose host storage has not been allocated (the scratch /
+    // tendency / work arrays of a "lean" block: 83 % of a block's words).  The device mirror is created zero-filled from
+    // the metadata alone; materialize() gives it host storage when somebody wants to look at it.
+    bool zero = false;
+    void materialize() {
+        if (zero && r.empty()) r.assign((size_t)count(), 0.0);
+        zero = false;
+    }
     int64_t count() const {
         int64_t n = 1;
         for (auto d : dims) n *= d;
@@ -55,6 +63,17 @@ struct Pool {
         fl.r.assign((size_t)fl.count(), 0.0);
         return fl;
     }
+    Field& addz(const std::string& name, FieldLoc loc, std::vector<int64_t> dims) {  // all-zero real field without host storage
+        Field& fl = f[name];
+        fl.name = name;
+        fl.kind = FK_REAL;
+        fl.loc = loc;
+        fl.dims = dims;
+        fl.r.clear();
+        fl.r.shrink_to_fit();
+        fl.zero = true;
+        return fl;
+    }
     Field& addi(const std::string& name, FieldLoc loc, std::vector<int64_t> dims) {
         Field& fl = f[name];
         fl.name = name;
@@ -70,7 +89,11 @@ struct Pool {
         if (it == f.end()) throw std::runtime_error("pool: no field '" + name + "'");
         return it->second;
     }
-    real_t* R(const std::string& name) { return get(name).r.data(); }
+    real_t* R(const std::string& name) {
+        Field& fl = get(name);
+        fl.materialize();
+        return fl.r.data();
+    }
     int32_t* I(const std::string& name) { return get(name).i.data(); }
     double c(const std::string& name) const {
         auto it = cfg.find(name);

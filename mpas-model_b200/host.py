@@ -44,6 +44,7 @@ def lib():
                                                     C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_longlong)]
         _lib.mpas_host_block_field_ptr.restype = C.c_void_p
         _lib.mpas_host_block_field_ptr.argtypes = [C.c_void_p, C.c_char_p]
+        _lib.mpas_host_block_field_is_lean.argtypes = [C.c_void_p, C.c_char_p]
         _lib.mpas_host_block_ncfg.argtypes = [C.c_void_p]
         _lib.mpas_host_block_cfg_info.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_double)]
         _lib.mpas_host_block_nexch.argtypes = [C.c_void_p, C.c_int, C.c_int]
@@ -147,6 +148,10 @@ class Block:
             self._load_info()
         return self._info[name]
 
+    def is_lean(self, name):
+        """True while `name` is an all-zero work array of a lean block without host storage (field() gives it storage)"""
+        return lib().mpas_host_block_field_is_lean(self.h, name.encode()) == 1
+
     def field(self, name):
         kind, loc, dims = self.info(name)
         ptr = lib().mpas_host_block_field_ptr(self.h, name.encode())
@@ -247,8 +252,10 @@ class HostCase:
         return out
 
     def build_block(self, iblock=0, nVertLevels=26, init_case=2, num_scalars=1, full_fields=True, keep_zb=False):
-        rc = lib().mpas_host_case_build_block(self.h, iblock, nVertLevels, init_case, num_scalars, 1 if full_fields else 0,
-                                              1 if keep_zb else 0)
+        # full_fields: False = initial state only, True = every dycore field with host storage, "lean" = every dycore field, the
+        # all-zero work arrays (83 % of the words) without host storage until somebody asks for them (pool.h Field::zero)
+        mode = 2 if full_fields == "lean" else (1 if full_fields else 0)
+        rc = lib().mpas_host_case_build_block(self.h, iblock, nVertLevels, init_case, num_scalars, mode, 1 if keep_zb else 0)
         if rc:
             raise RuntimeError(last_error())
         return Block(self, lib().mpas_host_case_block(self.h, iblock), iblock)
