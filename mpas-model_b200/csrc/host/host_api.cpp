@@ -1,6 +1,9 @@
 // C ABI of the host-side harness (mesh generation, decomposition, initial conditions).
 // Declared in include/mpas_b200.h.  Handles are opaque pointers; errors return non-zero /
 // NULL and leave a message retrievable through mpas_b200_last_error().
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <string>
@@ -118,13 +121,27 @@ int mpas_host_case_build_block(void* h, int iBlock, int nVertLevels, int init_ca
     hc->cfg.num_scalars = num_scalars;
     hc->cfg.keep_zb = keep_zb != 0;
     auto blk = std::make_unique<Block>();
+    const bool timing = getenv("MPAS_HOST_TIMING") != nullptr;  // per-phase wall times of the block set-up on stderr
+    auto t0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char* what) {
+        if (!timing) return;
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "mpas_host_case_build_block: %-32s %.2f s\n", what, std::chrono::duration<double>(t1 - t0).count());
+        t0 = t1;
+    };
     build_block(hc->global, hc->part, hc->nBlocks, iBlock, 2, *blk);
+    lap("build_block (decomposition)");
     Pool& p = blk->pool;
     mesh_to_pool(blk->mesh, p);
+    lap("mesh_to_pool");
     init_advection_and_deformation(blk->mesh, p);
+    lap("init_advection_and_deformation");
     init_case_jw(blk->mesh, hc->cfg, p);
+    lap("init_case_jw");
     core_init_derived(blk->mesh, hc->cfg, p);
+    lap("core_init_derived");
     init_reconstruct(blk->mesh, p);
+    lap("init_reconstruct");
     allocate_dycore_fields(blk->mesh, hc->cfg, p, full_fields);
     p.cfg["config_coef_3rd_order"] = hc->cfg.coef_3rd_order;
     hc->blocks[iBlock] = std::move(blk);
