@@ -1,16 +1,18 @@
 #!/usr/bin/env python
 """Benchmark of the B200-native MPAS-Atmosphere SRK3 dycore step (BASELINE.json metric: dycore timesteps/sec).
 
-  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--level 7] [--levels 55] [--scalars 4]
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--level 9] [--levels 55] [--scalars 1]
 
 One "step" = one full atm_srk3 dycore step (dynamics substeps + acoustic loop + monotonic scalar transport + every
 halo exchange) of the Jablonowski-Williamson baroclinic wave on an in-harness icosahedral Voronoi mesh.
-N = 1 workload: BASELINE.json configs[1] (x1.163842 = icosahedral level 7, 60 km, 55 levels, qv + 3 passive tracers);
-the 15 km mesh the metric is quoted on needs ~160 GB of resident fields in double as built and does not fit one GPU
-next to its host-side generation (DESIGN.md "Memory").  N > 1: the same mesh METIS-partitioned over N ranks (strong scaling),
-one process per GPU, halo exchange over NCCL.
+Default workload at EVERY N: the mesh the metric is quoted on, BASELINE.json configs[3] -- x1.2621442 = icosahedral
+level 9, 15 km, 55 levels, qv only (configs[3] names no tracers) -- one block at N = 1, METIS-partitioned over N ranks for
+N > 1 (strong scaling), one process per GPU, halo exchange over NVLink peer stores / NCCL.  If the device cannot hold it
+(a caught out-of-memory) the run falls back one icosahedral level at a time and says so in config.workload.
+`--level 7 --scalars 4` is BASELINE.json configs[1] (x1.163842, 60 km, qv + 3 passive tracers).
 """
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -22,24 +24,29 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(ROOT, "tests"))
 
 LEVEL_CELLS = {l: 10 * 4 ** l + 2 for l in range(3, 12)}
-# algorithmic words (8-byte reals read+written once) per owned cell-level and call, SURVEY.md section 8(a)/(d);
-# mixed entries are the per-call average over one dt with the Registry defaults
-def words_per_call(ns):
-    return {
-        "atm_compute_dyn_tend": (79 + 39 + 39) / 3.0,
-        "atm_advance_acoustic_step": (3 * 31 + 48) / 4.0,
-        "atm_divergence_damping_3d": 9.0,
-        "atm_recover_large_step_variables": (47 + 47 + 51) / 3.0,
-        "atm_advance_scalars_mono": 25.0 * ns + 11,
-        "atm_advance_scalars": 10.0 * ns + 7,
-        "atm_compute_solve_diagnostics": (39 + 39 + 42) / 3.0,
-        "atm_compute_vert_imp_coefs": 16.0,
-        "small_step_prep": 18.0,
-        "atm_rk_dynamics_substep_finish": 30.0,
-        "atm_rk_integration_setup": 20.0 + 2 * ns,
-        "atm_compute_moist_coefficients": 6.0 + ns,
-        "mpas_reconstruct": 8.0,  # u over the 3 edges per cell + 5 outputs (mpas_vector_reconstruction.F:254-288)
-    }
+LEVEL_KM = {5: 240, 6: 120, 7: 60, 8: 30, 9: 15, 10: 7.5, 11: 3.75}
+DEFAULT_LEVEL = 9
+
+
+def words_per_call(ns, L, minimal=False):
+    """algorithmic words (reals read + written once) per owned cell-level and call, generated from the per-routine array table
+    roofline/arrays.yaml (tools/roofline_words.py; it also cross-checks them against ncu dram bytes).  Default = the arrays the
+    REFERENCE's loops touch, the figure of SURVEY.md section 8(a)/(d) (dyn_tend 74 / 41 against the survey's hand count 79 / 39);
+    minimal = without the physics-coupling / output-only arrays the library does not even allocate (memory diet)."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import roofline_words
+    return roofline_words.words_per_call(ns, L, with_optional=not minimal)
+
+
+def kernel_source_sha():
+    """identifies the kernel sources a profile capture belongs to (a capture of other sources is refused)"""
+    h = hashlib.sha256()
+    d = os.path.join(ROOT, "mpas-model_b200", "csrc", "cuda")
+    for f in sorted(os.listdir(d)):
+        if f.endswith((".cu", ".cuh", ".h")):
+            h.update(f.encode())
+            h.update(open(os.path.join(d, f), "rb").read())
+    return h.hexdigest()[:16]
 
 
 class ClockSampler:
@@ -92,22 +99,38 @@ def parse():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--level", type=int, default=7, help="icosahedral level: 6=120 km, 7=60 km, 8=30 km, 9=15 km")
+    ap.add_argument("--level", type=int, default=None, help="icosahedral level: 6=120 km, 7=60 km, 8=30 km, 9=15 km (default 9, the metric's mesh)")
     ap.add_argument("--levels", type=int, default=55)
-    ap.add_argument("--scalars", type=int, default=4)
+    ap.add_argument("--scalars", type=int, default=None, help="num_scalars (default: 1 = qv at level >= 9 as configs[3], 4 = qv + 3 tracers below as configs[1])")
     ap.add_argument("--lloyd", type=int, default=5)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--ktime", action="store_true", help="also print per-kernel CUDA-event times of one eager step to stderr")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
-    ap.add_argument("--cpu-seconds", type=float, default=20.0, help="target CPU time of the bounded cpu_baseline sample")
-    return ap.parse_args()
+    ap.add_argument("--cpu-seconds", type=float, default=30.0, help="target CPU time of the bounded cpu_baseline sample")
+    ap.add_argument("--precision", default=None, choices=["double", "single"], help="single = the PRECISION=single build (dtype f32), an extra line")
+    a = ap.parse_args()
+    a.auto_level = a.level is None
+    if a.level is None:
+        a.level = DEFAULT_LEVEL
+    a.auto_scalars = a.scalars is None
+    if a.scalars is None:
+        a.scalars = 1 if a.level >= 9 else 4
+    return a
 
 
-def workload_name(a):
-    dx = {6: 120, 7: 60, 8: 30, 9: 15, 10: 7.5, 11: 3.75}.get(a.level, 0)
-    return "JW baroclinic wave, icosahedral level %d (x1.%d, %s km), %d levels, %d scalars (qv + %d passive tracers), dycore only" % (
-        a.level, LEVEL_CELLS[a.level], dx, a.levels, a.scalars, a.scalars - 1)
+def workload_name(level, levels, ns, note=""):
+    tr = "qv only" if ns == 1 else "qv + %d passive tracers" % (ns - 1)
+    return "JW baroclinic wave, icosahedral level %d (x1.%d, %s km), %d levels, %d scalars (%s), dycore only%s" % (
+        level, LEVEL_CELLS[level], LEVEL_KM.get(level, 0), levels, ns, tr, note)
+
+
+def config_dict(a, level, ns, note=""):
+    """identical in the b200 and the reference arm for the same command line"""
+    import common
+    return {"workload": workload_name(level, a.levels, ns, note), "nCells": LEVEL_CELLS[level], "nVertLevels": a.levels, "num_scalars": ns,
+            "config_dt_s": common.level_config(level)["config_dt"],
+            "partition": "METIS k-way, %d blocks" % a.gpus if a.gpus > 1 else "single block", "l2_policy": "no flush needed: one step streams far more than the 126 MB L2"}
 
 
 def set_tracers(block, ns):
@@ -127,59 +150,73 @@ def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
-def run_cpu_sample(a, level, nsteps_max, target_seconds):
-    """Time the CPU restatement (oracle perf build: -O3 -march=native, OpenMP over all host cores) on `level`."""
+def use_all_cores(share=1):
+    """torch.distributed.run exports OMP_NUM_THREADS=1 to its workers: set the OpenMP thread count of the host harness and of
+    the CPU oracle explicitly (all host cores / `share` processes)"""
     import common
-    cores = os.cpu_count()
+    n = max(1, (os.cpu_count() or 1) // share)
+    common.host.hostlib().mpas_host_set_num_threads(n)
+    return n
+
+
+def cpu_model(a, level, ns, threads):
+    """the CPU restatement (oracle perf build: -O3 -march=native, OpenMP) of the same case on `level`, initialised"""
+    import common
+    common.oracle(perf=True).oracle_set_num_threads(threads)
     case = common.host.HostCase(level, lloyd_iters=a.lloyd, sfc=True)
-    block = case.build_block(0, nVertLevels=a.levels, init_case=2, num_scalars=a.scalars, full_fields=True)
-    set_tracers(block, a.scalars)
+    block = case.build_block(0, nVertLevels=a.levels, init_case=2, num_scalars=ns, full_fields=True)
+    set_tracers(block, ns)
     m = common.OracleModel([block], common.level_config(level), perf=True)
     m.init()
+    return case, block, m
+
+
+def cpu_sample_level(a, ns, threads, nsteps, budget_s, max_level):
+    """largest icosahedral level <= max_level whose `nsteps` steps fit `budget_s` of CPU time, from a one-step probe on level 5"""
+    case, block, m = cpu_model(a, 5, ns, threads)
+    m.step(1)
     t0 = time.perf_counter()
-    n = 0
-    while n < nsteps_max:
-        m.step(1)
-        n += 1
-        if time.perf_counter() - t0 >= target_seconds:
-            break
-    dt = time.perf_counter() - t0
-    return n, dt, cores, case.nCells
+    m.step(1)
+    per_cell = (time.perf_counter() - t0) / case.nCells
+    level = 5
+    while level < max_level and per_cell * LEVEL_CELLS[level + 1] * nsteps <= budget_s:
+        level += 1
+    return level
+
+
+def phase_ms(m, nsteps):
+    return {k: {"ms_per_step": v[0] / nsteps, "calls_per_step": v[1] / nsteps} for k, v in m.timers().items()}
 
 
 def run_reference(a):
     """--impl reference: the reference's CPU implementation of the path.  The Fortran reference cannot be built on this
     image (no gfortran / MPI / netCDF: SURVEY.md F1), so this arm times the C++/OpenMP line-by-line restatement of the
-    same loops (oracle/, perf build) on all host cores."""
+    same loops (oracle/, perf build) on ALL host cores; only libmpas_host.so (mesh, JW state: no CUDA) and the oracle are
+    loaded.  Each step is a bounded sample of the workload: the same case on a smaller icosahedral level, steps/s scaled by
+    the cell ratio (the loops are linear in the number of cells)."""
     rank, local_rank, world = dist_env()
     if rank != 0:
         return
+    threads = use_all_cores(1)
     total = a.steps + a.warmup
-    # bounded sample: pick the largest mesh whose (steps + warmup) fit ~150 s, probing from the small side
-    level = min(a.level, 5)
-    n, dt, cores, ncells = run_cpu_sample(a, level, 1, 0.0)
-    per_cell_step = dt / ncells
-    while level < a.level and per_cell_step * LEVEL_CELLS[level + 1] * total < 150.0:
-        level += 1
-    import common
-    case = common.host.HostCase(level, lloyd_iters=a.lloyd, sfc=True)
-    block = case.build_block(0, nVertLevels=a.levels, init_case=2, num_scalars=a.scalars, full_fields=True)
-    set_tracers(block, a.scalars)
-    m = common.OracleModel([block], common.level_config(level), perf=True)
-    m.init()
+    level = cpu_sample_level(a, a.scalars, threads, total, 150.0, min(a.level, 7))
+    case, block, m = cpu_model(a, level, a.scalars, threads)
     m.step(a.warmup)
+    m.reset_timers()
     t0 = time.perf_counter()
     m.step(a.steps)
     dt = time.perf_counter() - t0
     scale = case.nCells / float(LEVEL_CELLS[a.level])
     value = a.steps / dt * scale
-    sample = "%d steps of the same case on icosahedral level %d (%d of %d cells), steps/s scaled by the cell ratio %.4f" % (
-        a.steps, level, case.nCells, LEVEL_CELLS[a.level], scale)
+    sample = "%d steps of the same case on icosahedral level %d (%d of %d cells) in %.1f s on %d OpenMP threads, steps/s scaled by the cell ratio %.5f" % (
+        a.steps, level, case.nCells, LEVEL_CELLS[a.level], dt, threads, scale)
     line = {
         "impl": "reference", "metric": "dycore timesteps/sec", "value": value, "unit": "steps/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": 1000.0 / value, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": workload_name(a), "note": "reference Fortran (gfortran+MPI) unavailable on this image; C++/OpenMP restatement of the same loops"},
-        "cpu_baseline": {"value": value, "unit": "steps/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": config_dict(a, a.level, a.scalars),
+        "note": "reference Fortran (gfortran+MPI) unavailable on this image; C++/OpenMP restatement of the same loops, all host cores",
+        "cpu_baseline": {"value": value, "unit": "steps/s", "cores": threads, "kind": "port", "sample": sample,
+                         "phases_ms_on_sample_mesh": phase_ms(m, a.steps)},
         "e2e": {"value": value, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -188,6 +225,7 @@ def run_reference(a):
 
 E2E_FIELDS = ["u@1", "w@1", "theta_m@1", "rho_zz@1", "scalars@1", "ru", "rw", "rho_p", "rtheta_p", "exner", "pressure_p", "rho_edge", "pv_edge", "v", "ke",
               "divergence", "vorticity"]  # the restart set the step reads at a step boundary (Registry.xml restart stream)
+CHECKSUM_FIELDS = ["u@1", "w@1", "theta_m@1", "rho_zz@1", "scalars@1"]
 
 
 def run_b200(a):
@@ -202,19 +240,50 @@ def run_b200(a):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the dycore has no CPU fallback")
     torch.cuda.set_device(local_rank)
+    dist = None
     if N > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
-    t_setup = time.perf_counter()
-    case = host.HostCase(a.level, lloyd_iters=a.lloyd, sfc=True)
-    if N > 1:
-        case.partition(N, "metis")
-    # "lean": the work / tendency arrays (all zero at start, 83 % of a block's words) get no host storage, their device mirrors
-    # are created zero-filled from the metadata -- what lets the 15 km mesh be set up by 2..8 ranks within the host's memory
-    block = case.build_block(rank, nVertLevels=a.levels, init_case=2, num_scalars=a.scalars, full_fields="lean")
-    set_tracers(block, a.scalars)
-    cfg = common.level_config(a.level)
-    dy = host.Dycore([block], cfg, rank=rank, nranks=N, device=local_rank)
+    threads = use_all_cores(N)
+
+    def all_ok(ok):
+        if N == 1:
+            return ok
+        t = torch.tensor([1 if ok else 0], dtype=torch.int32, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
+
+    # ---- set-up, with the out-of-memory fallback (one icosahedral level at a time, decided collectively)
+    level, ns, note = a.level, a.scalars, ""
+    while True:
+        t_setup = time.perf_counter()
+        case = host.HostCase(level, lloyd_iters=a.lloyd, sfc=True)
+        if N > 1:
+            case.partition(N, "metis")
+        # "lean": the work / tendency arrays (all zero at start, 83 % of a block's words) get no host storage, their device mirrors
+        # are created zero-filled from the metadata
+        block = case.build_block(rank, nVertLevels=a.levels, init_case=2, num_scalars=ns, full_fields="lean")
+        set_tracers(block, ns)
+        cfg = common.level_config(level)
+        dy, err = None, ""
+        try:
+            dy = host.Dycore([block], cfg, rank=rank, nranks=N, device=local_rank)
+        except RuntimeError as e:
+            err = str(e)
+            if "out of memory" not in err:
+                raise
+        if all_ok(dy is not None):
+            break
+        if dy is not None:
+            dy.close()
+        dy = None
+        if not a.auto_level or level <= 7:
+            raise SystemExit("level %d does not fit the device memory: %s" % (level, err))
+        del block, case
+        note = " [fallback: level %d did not fit the device memory of %d GPU(s)]" % (a.level, N)
+        level -= 1
+        if a.auto_scalars:
+            ns = 1 if level >= 9 else 4
     if N > 1:
         obj = [host.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(obj, src=0)
@@ -239,6 +308,13 @@ def run_b200(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def sum_over_ranks_u64(x):
+        if N == 1:
+            return x
+        t = torch.tensor([x - (1 << 64) if x >= (1 << 63) else x], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)  # two's complement wrap-around = addition mod 2^64
+        return int(t.item()) & ((1 << 64) - 1)
+
     L_ = host.lib()
     dy.step(a.warmup)
     barrier()
@@ -258,6 +334,10 @@ def run_b200(a):
     wmax, umax = dy.max_abs("w@1"), dy.max_abs("u@1")
     if not (np.isfinite(wmax) and np.isfinite(umax) and umax < 300.0):
         raise SystemExit("integration blew up: max|u| = %r max|w| = %r" % (umax, wmax))
+    # owned prognostic state after warmup + steps steps as one integer per field: equal for every N (decomposition test)
+    checksum = {n.split("@")[0]: "0x%016x" % sum_over_ranks_u64(dy.checksum(n)) for n in CHECKSUM_FIELDS}
+    transport = dy.halo_transport()
+    device_gb = max_over_ranks(dy.device_bytes() / 1e9)
 
     # ---- per-routine timing pass (CUDA events around every routine call, eager launches) -> roofline
     peaks = {}
@@ -286,50 +366,63 @@ def run_b200(a):
         tot = sum(float(r[1]) for r in rows)
         for r in sorted(rows, key=lambda r: -float(r[1])):
             print("KTIME %-28s %8.3f ms/step %5.1f calls/step %8.1f us/call %5.1f%%" % (r[0], float(r[1]) / 2, int(r[2]) / 2, 1e3 * float(r[1]) / int(r[2]), 100 * float(r[1]) / tot), file=sys.stderr)
-    words = words_per_call(a.scalars)
-    nCS_total = nCS
+    words = words_per_call(ns, L)
+    words_min = words_per_call(ns, L, minimal=True)
     phases = {}
     for name, (tms, calls) in timers.items():
         per_call = tms / max(calls, 1)
         e = {"ms_per_step": tms / nt, "calls_per_step": calls / nt, "ms_per_call": per_call}
         if name in words and per_call > 0:
-            gb = words[name] * 8.0 * nCS_total * L / 1e9
+            gb = words[name] * (4.0 if host.SINGLE else 8.0) * nCS * L / 1e9
             e["algorithmic_GB_per_call"] = gb
             e["achieved_GBs"] = gb / (per_call / 1000.0)
             e["frac"] = e["achieved_GBs"] / peak_gbs
+            e["words_per_cell_level"] = words[name]
+            e["frac_minimal_words"] = e["frac"] * words_min[name] / words[name]
         phases[name] = e
     dom = max((n for n in phases if n in words), key=lambda n: phases[n]["ms_per_step"])
     roofline = {"bound": "hbm", "kernel": dom, "achieved": phases[dom]["achieved_GBs"], "peak": peak_gbs, "unit": "GB/s", "frac": phases[dom]["frac"],
                 "traffic": None, "peak_source": peak_src,
-                "note": "achieved = SURVEY 8(d) words x 8 B x owned cell-levels per call / CUDA-event time per call (eager pass after the timed region)"}
-    # traffic: DRAM bytes (read + write) per call of the dominant routine from the committed ncu capture of this same command
-    # (profiles/r01_d_dram_traffic.json, tools/dram_traffic.py); only valid for the default workload on one GPU
+                "note": "achieved = roofline/arrays.yaml words x sizeof(real) x owned cell-levels per call / CUDA-event time per call (eager pass after the timed region)"}
+    # traffic: DRAM bytes (read + write) per call of the dominant routine from the committed ncu capture of these kernel sources
+    # (profiles/r02_dram_traffic.json, tools/dram_traffic.py).  The capture is of configs[1] (level 7, 4 scalars); a capture of other
+    # kernel sources is refused, other workloads scale it by the cell count (traffic per cell-level does not depend on the mesh size)
     try:
-        if N == 1 and a.level == 7 and a.levels == 55 and a.scalars == 4:
-            tr = json.load(open(os.path.join(ROOT, "profiles", "r01_d_dram_traffic.json")))
-            roofline["traffic"] = tr[dom]["dram_GB_per_step"] / phases[dom]["calls_per_step"]
-            roofline["traffic_unit"] = "GB per call (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r01_d_dram_traffic.csv)"
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r02_dram_traffic.json")))
+        if tr.get("_kernel_source_sha") != kernel_source_sha():
+            roofline["traffic_note"] = "committed ncu capture is of other kernel sources (%s, now %s): not used" % (tr.get("_kernel_source_sha"), kernel_source_sha())
+        elif N == 1 and a.levels == int(tr["_nVertLevels"]) and ns == int(tr["_num_scalars"]) and not host.SINGLE:
+            scale = LEVEL_CELLS[level] / float(tr["_nCells"])
+            roofline["traffic"] = tr[dom]["dram_GB_per_step"] / phases[dom]["calls_per_step"] * scale
+            roofline["traffic_unit"] = "GB per call (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_dram_traffic.csv%s)" % (
+                "" if scale == 1.0 else ", captured on %d cells and scaled by the cell ratio" % int(tr["_nCells"]))
             roofline["algorithmic_GB_per_call"] = phases[dom]["algorithmic_GB_per_call"]
-            roofline["whole_step_traffic_GB"] = tr["_whole_step"]["dram_GB_per_step"]
-    except Exception:
-        pass
+            roofline["whole_step_traffic_GB"] = tr["_whole_step"]["dram_GB_per_step"] * scale
+        else:
+            roofline["traffic_note"] = "the committed ncu capture is 1 GPU, %s levels, %s scalars, f64" % (tr["_nVertLevels"], tr["_num_scalars"])
+    except Exception as e:
+        roofline["traffic_note"] = "no usable capture: %s" % (e,)
     step_gb = sum(phases[n]["algorithmic_GB_per_call"] * phases[n]["calls_per_step"] for n in phases if "algorithmic_GB_per_call" in phases[n])
-    roofline["whole_step"] = {"algorithmic_GB": step_gb, "achieved_GBs": step_gb * value * (1 if N == 1 else 1), "frac": step_gb * value / peak_gbs}
+    # whole job: `value` steps/s, every rank streams its own step_gb per step (max-over-ranks time), roofline per GPU
+    roofline["whole_step"] = {"algorithmic_GB": step_gb, "achieved_GBs": step_gb * value, "frac": step_gb * value / peak_gbs,
+                              "note": "per GPU: this rank's owned cell-levels; time = the max-over-ranks step"}
 
     # ---- e2e: the same step through the public API with HOST buffers (pinned), copies inside the timed region
     e2e = None
     if not a.no_e2e:
         bufs = {}
         h2d = 0
+        real_np = np.float32 if host.SINGLE else np.float64
         for n in E2E_FIELDS:
             kind, loc, dims = block.info(n)
             cnt = int(np.prod(dims))
-            t = torch.empty(cnt, dtype=torch.float64).pin_memory()
+            t = torch.empty(cnt, dtype=torch.float32 if host.SINGLE else torch.float64).pin_memory()
             arr = t.numpy()
-            dy.field(0, n, out=arr.reshape(tuple(reversed(dims))))
+            rc = L_.mpas_b200_dycore_get_field(dy.h, 0, n.encode(), arr.ctypes.data, arr.nbytes)
+            assert rc == 0, host.last_error()
             bufs[n] = (t, arr)
             h2d += arr.nbytes
-        ke = max(1, min(a.steps, 5))
+        ke = max(1, min(a.steps, 5 if level < 9 else 3))
         barrier()
         L_.mpas_b200_timer_start()
         for _ in range(ke):
@@ -342,30 +435,36 @@ def run_b200(a):
                 assert rc == 0
         ems = max_over_ranks(L_.mpas_b200_timer_stop())
         e2e = {"value": ke / (ems / 1000.0), "unit": "steps/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": h2d, "steps": ke,
-               "what": "per step: upload the %d-field restart set from pinned host memory, one dycore step, download the same set" % len(E2E_FIELDS)}
+               "what": "per step: upload the %d-field restart set from pinned host memory, one dycore step, download the same set (bytes: this rank)" % len(E2E_FIELDS)}
+        del bufs
 
-    # ---- CPU baseline (rank 0, N = 1): bounded sample of the same workload on the host cores
+    # ---- CPU baseline (rank 0, N = 1): bounded sample of the same workload on the host cores, >= 10 steps, per-phase times
     cpu = None
     if rank == 0 and N == 1 and not a.no_cpu_baseline:
-        lvl = a.level
-        n, dt_, cores, ncells = run_cpu_sample(a, min(lvl, 5), 1, 0.0)
-        while lvl > 5 and dt_ / ncells * LEVEL_CELLS[lvl] > a.cpu_seconds:
-            lvl -= 1
-        n, dt_, cores, ncells = run_cpu_sample(a, lvl, 3, a.cpu_seconds)
-        scale = ncells / float(LEVEL_CELLS[a.level])
-        cpu = {"value": n / dt_ * scale, "unit": "steps/s", "cores": cores, "kind": "port",
-               "sample": "%d step(s) of the same case on icosahedral level %d (%d of %d cells) in %.1f s, scaled by the cell ratio; C++/OpenMP restatement, -O3 -march=native"
-                         % (n, lvl, ncells, LEVEL_CELLS[a.level], dt_)}
+        nst = 10
+        lvl = cpu_sample_level(a, ns, threads, nst + 1, a.cpu_seconds, min(level, 7))
+        ccase, cblock, m = cpu_model(a, lvl, ns, threads)
+        m.step(1)
+        m.reset_timers()
+        t0 = time.perf_counter()
+        m.step(nst)
+        dt_ = time.perf_counter() - t0
+        scale = ccase.nCells / float(LEVEL_CELLS[level])
+        cpu = {"value": nst / dt_ * scale, "unit": "steps/s", "cores": threads, "kind": "port",
+               "sample": "%d steps (after 1 warm-up step) of the same case on icosahedral level %d (%d of %d cells) in %.1f s, scaled by the cell ratio; "
+                         "C++/OpenMP restatement, -O3 -march=native; the Fortran reference cannot be built on this box" % (nst, lvl, ccase.nCells, LEVEL_CELLS[level], dt_),
+               "phases_ms_on_sample_mesh": phase_ms(m, nst)}
 
     if rank == 0:
         dt_model = cfg["config_dt"]
         line = {
             "metric": "dycore timesteps/sec", "value": value, "unit": "steps/s", "n_gpus": N, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps,
-            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(a), "nCells": LEVEL_CELLS[a.level], "nVertLevels": a.levels, "num_scalars": a.scalars, "config_dt_s": dt_model,
-                       "simulated_days_per_day": value * dt_model, "partition": "METIS k-way, %d blocks" % N if N > 1 else "single block",
-                       "l2_policy": "no flush needed: one step streams ~%.0f GB through a 126 MB L2" % step_gb, "cuda_graph": use_graph,
-                       "halo_exchanges_per_step": exchanges / a.steps, "halo_transport": dy.halo_transport(), "setup_seconds": t_setup, "max_abs_u": umax, "max_abs_w": wmax},
+            "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32" if host.SINGLE else "f64", "data": "synthetic",
+            "config": config_dict(a, level, ns, note),
+            "run": {"simulated_days_per_day": value * dt_model, "cuda_graph": use_graph, "halo_exchanges_per_step": exchanges / a.steps, "halo_transport": transport,
+                    "setup_seconds": t_setup, "host_threads": threads, "device_GB_per_rank": device_gb, "max_abs_u": umax, "max_abs_w": wmax,
+                    "state_checksum": checksum, "state_checksum_after_steps": a.warmup + a.steps,
+                    "state_checksum_what": "sum mod 2^64 of the bit patterns of the owned u, w, theta_m, rho_zz, scalars over all ranks: equal for every N"},
             "roofline": roofline, "phases": phases, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clk,
         }
         print(json.dumps(line), flush=True)
@@ -376,6 +475,8 @@ def run_b200(a):
 
 if __name__ == "__main__":
     args = parse()
+    if args.precision == "single":
+        os.environ["MPAS_B200_PRECISION"] = "single"
     if args.impl == "reference":
         run_reference(args)
     else:

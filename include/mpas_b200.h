@@ -13,7 +13,8 @@
  * src/framework/mpas_dmpar.F:5386-5748) run as pack kernel -> NCCL grouped send/recv (or
  * device copies between blocks of one process) -> unpack kernel.
  *
- * Layer 0 (host harness: mesh, decomposition, initial conditions): mpas_host_*.
+ * Layer 0 (host harness: mesh, decomposition, initial conditions) lives in its own library without CUDA:
+ * libmpas_host.so, include/mpas_host.h.
  */
 #ifndef MPAS_B200_H
 #define MPAS_B200_H
@@ -87,7 +88,14 @@ long mpas_b200_dycore_exchange_count(void* h);
  * (CUDA IPC over NVLink, switched on after the second step when every rank can map every other); -2 a peer-to-peer wait
  * timed out since the last call.  MPAS_B200_TUNE_p2p=0 keeps NCCL. */
 int mpas_b200_dycore_halo_transport(void* h);
-int mpas_b200_dycore_set_option(void* h, const char* name, int value); /* "timing", "graph", "aggregate" */
+int mpas_b200_dycore_set_option(void* h, const char* name, int value); /* "timing", "graph", "aggregate"; "diet" (before attach_block) */
+/* memory diet (default on; option "diet" = 0 before attach_block gives every pool array its own mirror): arrays only physics or
+ * output use (gradPVn/t, ke_edge, tend_*_physics, rthdynten, tend_rtheta_adv, rt_diabatic_tend: optional arguments of the work
+ * routines) get no mirror, and phase-local scratch (the delsq_* / dpdz arrays of TI:592-605, the mono scratch of TI:1029-1050,
+ * horiz_flux_arr) plus the library workspace of the same phases are views of ONE arena per block, as the reference allocates and
+ * frees them around each phase.  1 = `name` is such a view (valid only inside its phase), 0 = own storage, -1 = no mirror */
+int mpas_b200_dycore_field_is_scratch_view(void* h, int iLocal, const char* name);
+long long mpas_b200_dycore_device_bytes(void* h); /* bytes of device memory held by the blocks' mirrors and arenas */
 int mpas_b200_dycore_timer_count(void* h);
 int mpas_b200_dycore_timer_get(void* h, int idx, char* name, int cap, double* ms, long* calls);
 int mpas_b200_dycore_timer_reset(void* h);
@@ -95,50 +103,9 @@ double mpas_b200_dycore_global_max_abs(void* h, const char* name); /* summarize_
 /* global min / max over owned elements of every stride-th element from offset (one scalar of scalars(:,k,iCell)): the
  * reductions summarize_timestep prints for w, u and the scalars, TI:6758-7010 (mpas_dmpar_min_real / max_real) */
 int mpas_b200_dycore_global_minmax(void* h, const char* name, long long offset, long long stride, double* min_out, double* max_out);
-
-/* ---- Layer 0: host harness (mesh, partition, JW initial state) ---- */
-void* mpas_host_case_create(int level, int lloyd_iters, int sfc);
-void mpas_host_case_destroy(void* h);
-int mpas_host_case_dims(void* h, int* nCells, int* nEdges, int* nVertices, int* maxEdges, int* maxEdges2);
-int mpas_host_case_permutation(void* h, int kind, int* out);
-int mpas_host_case_partition(void* h, int nBlocks, int method, const char* prefix);
-int mpas_host_case_get_partition(void* h, int* out);
-int mpas_host_case_build_block(void* h, int iBlock, int nVertLevels, int init_case, int num_scalars, int full_fields, int keep_zb);
-void* mpas_host_case_block(void* h, int iBlock);
-int mpas_host_block_nfields(void* b);
-int mpas_host_block_field_info(void* b, int idx, char* name, int name_cap, int* kind, int* loc, int* ndims, long long* dims);
-void* mpas_host_block_field_ptr(void* b, const char* name);
-/* lean blocks (mpas_host_case_build_block full_fields = 2): the work arrays that are all zero when a block has been built
- * get no host storage until mpas_host_block_field_ptr is asked for them; 1 = no storage yet, 0 = has storage, -1 = no such field */
-int mpas_host_block_field_is_lean(void* block, const char* name);
-int mpas_host_block_ncfg(void* b);
-int mpas_host_block_cfg_info(void* b, int idx, char* name, int name_cap, double* value);
-int mpas_host_block_nexch(void* b, int kind, int which);
-int mpas_host_block_exch_info(void* b, int kind, int which, int idx, int* endPoint, int* haloLayer, int* nlist);
-int mpas_host_block_exch_lists(void* b, int kind, int which, int idx, int* srcList, int* destList);
-
-/* ---- on-disk files: MPAS grid / restart files in the netCDF classic formats (CDF-1/2/5), the formats
- * of the reference's streams (Registry.xml:397-1125, mpas_bootstrapping.F:79-423); no netCDF library is used ---- */
-int mpas_host_case_write_grid(void* h, const char* path, int version);
-void* mpas_host_case_create_from_grid(const char* path, int sfc);
-int mpas_host_case_create_restart(void* h, int iBlock, const char* path, int version, const char* names_csv, const char* xtime);
-int mpas_host_block_write_restart(void* b, const char* path, const char* names_csv);
-int mpas_host_block_read_restart(void* b, const char* path);
-void* mpas_nc_open(const char* path);
-void* mpas_nc_create(const char* path, int version);
-int mpas_nc_close(void* h);
-int mpas_nc_inq(void* h, int* version, int* ndims, int* nvars, int* ngatts, long long* numrecs);
-int mpas_nc_dim_info(void* h, int idx, char* name, int name_cap, long long* len);
-int mpas_nc_var_info(void* h, int idx, char* name, int name_cap, int* type, int* ndims, int* dimids, long long* count);
-int mpas_nc_gatt_text(void* h, const char* name, char* out, int cap);
-int mpas_nc_get_double(void* h, const char* name, double* out);
-int mpas_nc_get_int(void* h, const char* name, int* out);
-int mpas_nc_def_dim(void* h, const char* name, long long len);
-int mpas_nc_def_var(void* h, const char* name, int type, int ndims, const int* dimids);
-int mpas_nc_put_gatt_text(void* h, const char* name, const char* value);
-int mpas_nc_enddef(void* h, long long numrecs);
-int mpas_nc_put_double(void* h, int varid, long long rec, long long start, long long count, const double* data);
-int mpas_nc_put_int(void* h, int varid, long long rec, long long start, long long count, const int* data);
+/* sum (mod 2^64) of the bit patterns of this process's OWNED elements of a decomposed real field; added over the ranks it is
+ * the same number for every partition of the mesh (owned-element arithmetic is partition independent) */
+int mpas_b200_dycore_checksum(void* h, const char* name, unsigned long long* out);
 
 #ifdef __cplusplus
 }

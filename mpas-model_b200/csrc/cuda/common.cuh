@@ -188,14 +188,26 @@ int fail_msg(const std::string& msg);
 long long launches();                  // kernels launched by the library so far
 void count_launch(int n = 1);
 
-// Persistent device workspace owned by the library (the reference allocates/deallocates its scratch around every
-// phase, TI:592-626; here it lives for the life of the process).  Grows on demand; never call inside stream capture
-// before the first eager step has sized it.
-real* workspace(int slot, size_t count);
-// Per-block persistent workspace keyed by an address that identifies the block; nullptr if it cannot be granted
-// (out of memory, or a first call inside a stream capture): callers then take their workspace-free path.
-real* keyed_workspace(const void* key, size_t count);
+// Per-block persistent workspace keyed by (an address that identifies the block, slot); nullptr if it cannot be
+// granted (out of memory, a first call inside a stream capture, or a provided view that is too small): the caller
+// reports an error.  Slots: 0 = all-scalars monotonic transport (key scale_arr), 1 = dyn_tend edge fluxes (key tend_u).
+real* keyed_workspace(const void* key, size_t count, int slot = 0);
+// A device-resident Dycore hands the library a view of its own scratch arena instead (not owned, never freed here).
+void provide_keyed_workspace(const void* key, int slot, real* p, size_t count);
 void release_keyed_workspace(const void* key);
+
+// Layout of the all-scalars monotonic-transport workspace (scalars.cu): [flux_arr | flux_upwind | wdtn | scalar_new | scale(2)],
+// every piece num_scalars wide.  Shared with dycore.cu, which provides it as a view of the block's scratch arena.
+struct MonoWsLayout {
+    size_t n_edge, n_wd, n_cell, total;
+    MonoWsLayout(int L, int ns, int nCells, int nEdges) {
+        const size_t nel = (size_t)L * ns, nel1 = (size_t)(L + 1) * ns, nC1 = (size_t)nCells + 1, nE1 = (size_t)nEdges + 1;
+        n_edge = (nel * nE1 + 1) & ~(size_t)1;
+        n_wd = (nel1 * nC1 + 1) & ~(size_t)1;
+        n_cell = (nel * nC1 + 1) & ~(size_t)1;
+        total = 2 * n_edge + n_wd + 3 * n_cell;
+    }
+};
 
 // Translate a pointer handed over the C ABI: a registered host address (anywhere inside a
 // registered range) maps to its device mirror; anything else is taken to be a device pointer.

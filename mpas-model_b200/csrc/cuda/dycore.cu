@@ -8,8 +8,8 @@
 
 #include "../host/decomp.h"
 
-namespace mpas {
-extern std::string g_last_error;
+namespace mpasb200 {
+extern std::string g_last_error;  // runtime.cu
 }
 
 namespace mpasb200 {
@@ -222,6 +222,39 @@ int dycore_p2p_setup(Dycore& m) {
 }
 
 namespace {
+struct ZeroTab {
+    real* p[16];
+    int n[16];
+};
+__global__ void zero_cols_kernel(ZeroTab t) {
+    real* p = t.p[blockIdx.x];
+    for (int i = threadIdx.x; i < t.n[blockIdx.x]; i += blockDim.x) p[i] = (real)0.0;
+}
+}  // namespace
+
+// The reference zero-fills the garbage column of its scratch arrays every time it allocates them (TI:593-605, 1029-1050);
+// views of the shared arena get the same at the start of their phase.  group 2 also covers the all-scalars workspace (4).
+int dycore_zero_garbage(DBlock& b, int group) {
+    if (b.views.empty()) return 0;
+    ZeroTab t;
+    int k = 0;
+    for (auto& v : b.views) {
+        if (v.group != group && !(group == 2 && v.group == 4)) continue;
+        t.p[k] = v.garbage; t.n[k] = v.inner;
+        if (++k == 16) {
+            zero_cols_kernel<<<k, 128, 0, stream()>>>(t);
+            count_launch();
+            k = 0;
+        }
+    }
+    if (k) {
+        zero_cols_kernel<<<k, 128, 0, stream()>>>(t);
+        count_launch();
+    }
+    return 0;
+}
+
+namespace {
 
 int add_field(DBlock& blk, const std::string& name, const void* host, int kind, int loc, const std::vector<long long>& dims) {
     DField df;
@@ -269,7 +302,7 @@ using namespace mpasb200;
 #define DY_CATCH                                 \
     }                                            \
     catch (const std::exception& e) {            \
-        mpas::g_last_error = e.what();           \
+        mpasb200::g_last_error = e.what();           \
         return 1;                                \
     }
 
@@ -290,8 +323,11 @@ void mpas_b200_dycore_destroy(void* h) {
     cudaStreamSynchronize(stream());
     dycore_p2p_teardown(*m);
     for (auto& b : m->blocks) {
-        auto sa = b.f.find("scale_arr");
-        if (sa != b.f.end()) release_keyed_workspace(sa->second.dev);  // the all-scalars mono workspace of this block
+        for (const char* key : {"scale_arr", "tend_u"}) {  // the library workspace keyed by this block's arrays (runtime.cu)
+            auto sa = b.f.find(key);
+            if (sa != b.f.end()) release_keyed_workspace(sa->second.dev);
+        }
+        if (b.arena) cudaFree(b.arena);
         for (auto& kv : b.f)
             if (kv.second.owned) cudaFree(kv.second.dev);
         for (auto& kv : b.halo.plans) halo_free_plan(kv.second);
@@ -311,21 +347,109 @@ int mpas_b200_dycore_attach_block(void* h, int iLocal, void* hostBlock) {
     mpas::Block* hb = (mpas::Block*)hostBlock;
     if (!hb) return fail_msg("mpas_b200_dycore_attach_block: null host block");
     DBlock& blk = m->blocks.at(iLocal);
+    // diet: (a) arrays only physics or output use -- every kernel takes them as optional arguments -- get no mirror;
+    // (b) phase-local scratch becomes views of one arena sized for the largest phase
+    static const char* kOptional[] = {"gradPVn", "gradPVt", "ke_edge", "tend_ru_physics", "rthdynten", "tend_rtheta_adv", "tend_rho_physics",
+                                      "tend_rtheta_physics", "rt_diabatic_tend"};
+    static const std::map<std::string, int> kGroup = {
+        {"delsq_u", 1}, {"delsq_theta", 1}, {"delsq_w", 1}, {"delsq_divergence", 1}, {"dpdz", 1}, {"delsq_vorticity", 1},
+        {"scalar_old", 2}, {"scalar_new", 2}, {"s_max", 2}, {"s_min", 2}, {"scale_arr", 2}, {"wdtn", 2}, {"flux_arr", 2}, {"flux_upwind_tmp", 2}, {"flux_tmp", 2},
+        {"horiz_flux_arr", 3}};
+    struct Pending { std::string name; int group; size_t off; DField df; };
+    std::vector<Pending> pend;
+    size_t gsize[4] = {0, 0, 0, 0};
+    auto place = [&](int g, size_t bytes) {  // 256-byte aligned, 64 bytes of slack behind (16-byte windows of the bulk column copies)
+        const size_t off = gsize[g];
+        gsize[g] = (off + bytes + 64 + 255) & ~(size_t)255;
+        return off;
+    };
     for (auto& kv : hb->pool.f) {
         const mpas::Field& fl = kv.second;
         std::vector<long long> dims(fl.dims.begin(), fl.dims.end());
+        if (m->diet && fl.kind == mpas::FK_REAL) {
+            bool skip = false;
+            for (const char* o : kOptional) skip = skip || kv.first == o;
+            if (skip) continue;
+            auto g = kGroup.find(kv.first);
+            if (g != kGroup.end()) {
+                Pending pd;
+                pd.name = kv.first; pd.group = g->second;
+                pd.df.kind = 0; pd.df.loc = (int)fl.loc; pd.df.dims = dims; pd.df.owned = false;
+                size_t n = 1;
+                for (auto d : dims) n *= (size_t)d;
+                pd.df.inner = 1;
+                for (size_t k = 0; k + 1 < dims.size(); ++k) pd.df.inner *= (int)dims[k];
+                pd.df.bytes = n * sizeof(real);
+                pd.off = place(pd.group, pd.df.bytes);
+                pend.push_back(pd);
+                continue;
+            }
+        }
         const void* src = fl.kind == mpas::FK_REAL ? (const void*)fl.r.data() : (const void*)fl.i.data();
         if (fl.kind == mpas::FK_REAL && fl.zero && fl.r.empty()) src = nullptr;  // lean block: zero-filled mirror from the metadata alone
         int rc = add_field(blk, kv.first, src, fl.kind == mpas::FK_REAL ? 0 : 1, (int)fl.loc, dims);
         if (rc) return rc;
     }
     for (auto& kv : hb->pool.cfg) blk.cfg[kv.first] = kv.second;
+    if (m->diet && !pend.empty()) {
+        const int L = (int)blk.c("nVertLevels"), ns = (int)blk.c("num_scalars"), nC = (int)blk.c("nCells"), nE = (int)blk.c("nEdges");
+        // library workspace of the same phases, as views too: the three per-edge flux arrays of dyn_tend (group 1, behind the rk 1
+        // scratch) and the all-scalars mono workspace (group 2, OVER the per-scalar scratch: a call takes one path or the other)
+        const size_t nELp = ((size_t)(nE + 1) * L + 1) & ~(size_t)1;
+        const size_t off_flux = place(1, 3 * nELp * sizeof(real));
+        const MonoWsLayout lay(L, ns, nC, nE);
+        gsize[2] = std::max(gsize[2], (lay.total * sizeof(real) + 64 + 255) & ~(size_t)255);
+        blk.arena_bytes = std::max(gsize[1], std::max(gsize[2], gsize[3]));
+        cudaError_t e = cudaMalloc(&blk.arena, blk.arena_bytes);
+        if (e != cudaSuccess) return fail("cudaMalloc scratch arena", e);
+        cudaMemset(blk.arena, 0, blk.arena_bytes);
+        for (auto& pd : pend) {
+            pd.df.dev = blk.arena + pd.off;
+            blk.f[pd.name] = pd.df;
+            ArenaView v;
+            v.name = pd.name; v.group = pd.group; v.inner = pd.df.inner;
+            v.garbage = (real*)pd.df.dev + (size_t)pd.df.inner * (size_t)(pd.df.dims.back() - 1);
+            blk.views.push_back(v);
+        }
+        // garbage columns of the all-scalars workspace pieces (group 2)
+        {
+            real* ws = (real*)blk.arena;
+            const int nel = L * ns, nel1 = (L + 1) * ns;
+            real* base[5] = {ws, ws + lay.n_edge, ws + 2 * lay.n_edge, ws + 2 * lay.n_edge + lay.n_wd, ws + 2 * lay.n_edge + lay.n_wd + lay.n_cell};
+            const int inner[5] = {nel, nel, nel1, nel, 2 * nel};
+            const int last[5] = {nE, nE, nC, nC, nC};
+            const char* nm[5] = {"mono_ws_flux", "mono_ws_upwind", "mono_ws_wdtn", "mono_ws_snew", "mono_ws_scale"};
+            for (int i = 0; i < 5; ++i) blk.views.push_back({nm[i], 4, base[i] + (size_t)inner[i] * last[i], inner[i]});
+        }
+        provide_keyed_workspace(blk.f.at("tend_u").dev, 1, (real*)(blk.arena + off_flux), 3 * nELp);
+        provide_keyed_workspace(blk.f.at("scale_arr").dev, 0, (real*)blk.arena, lay.total);
+    }
     blk.halo.blockID = hb->blockID;
     copy_lists(hb->cellExch.send, blk.halo.send[1]); copy_lists(hb->cellExch.recv, blk.halo.recv[1]);
     copy_lists(hb->edgeExch.send, blk.halo.send[2]); copy_lists(hb->edgeExch.recv, blk.halo.recv[2]);
     copy_lists(hb->vertexExch.send, blk.halo.send[3]); copy_lists(hb->vertexExch.recv, blk.halo.recv[3]);
     return 0;
     DY_CATCH
+}
+
+// 1 when `name` of block iLocal is a view of the scratch arena (valid only inside its phase), 0 when it has its own storage, -1 when absent
+int mpas_b200_dycore_field_is_scratch_view(void* h, int iLocal, const char* name) {
+    DBlock& b = ((Dycore*)h)->blocks.at(iLocal);
+    auto it = b.f.find(name);
+    if (it == b.f.end()) return -1;
+    for (auto& v : b.views)
+        if (v.name == name) return 1;
+    return 0;
+}
+
+long long mpas_b200_dycore_device_bytes(void* h) {
+    long long n = 0;
+    for (auto& b : ((Dycore*)h)->blocks) {
+        n += (long long)b.arena_bytes;
+        for (auto& kv : b.f)
+            if (kv.second.owned) n += (long long)kv.second.bytes + 64;
+    }
+    return n;
 }
 
 int mpas_b200_dycore_set_cfg(void* h, int iLocal, const char* name, double value) {
@@ -436,6 +560,7 @@ int mpas_b200_dycore_set_option(void* h, const char* name, int value) {
     if (n == "timing") m->timing = value != 0;
     else if (n == "graph") m->use_graph = value != 0;
     else if (n == "aggregate") m->aggregate = value != 0;
+    else if (n == "diet") m->diet = value != 0;  // before attach_block
     else return fail_msg("unknown option " + n);
     return 0;
 }

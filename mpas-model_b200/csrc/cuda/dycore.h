@@ -21,8 +21,20 @@ struct DField {
     std::vector<long long> dims;
 };
 
+// A view of the block's scratch arena: phase-local work arrays of different phases share storage (the reference
+// allocates and frees them around each phase for the same reason, TI:592-626, 1029-1099).
+struct ArenaView {
+    std::string name;
+    int group;  // 1 = dyn_tend rk 1 scratch, 2 = monotonic transport scratch, 3 = advance_scalars flux
+    real* garbage;      // first element of the trailing "garbage" column (zero-filled at the start of the phase, as TI:593-605)
+    int inner;
+};
+
 struct DBlock {
     std::map<std::string, DField> f;
+    char* arena = nullptr;
+    size_t arena_bytes = 0;
+    std::vector<ArenaView> views;
     std::map<std::string, double> cfg;
     HaloBlock halo;
     real* R(const std::string& n);
@@ -61,6 +73,7 @@ struct Dycore {
     bool timing = false;
     bool aggregate = true;
     bool use_graph = false;
+    bool diet = true;  // phase-local scratch shares one arena; optional (physics / output-only) arrays get no mirror
     std::map<std::string, PhaseTimer> timers;
     std::vector<std::string> timer_order;
     std::vector<cudaEvent_t> event_pool;
@@ -87,5 +100,6 @@ void dycore_p2p_teardown(Dycore& m);
 int dycore_init(Dycore& m);
 int dycore_step(Dycore& m);
 int dycore_call(Dycore& m, const std::string& routine, const double* prm, int nprm);
+int dycore_zero_garbage(DBlock& b, int group);  // zero the garbage columns of the arena views of one phase
 
 }  // namespace mpasb200

@@ -852,10 +852,12 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     }
     if (maxEdges > 8 || maxEdges2 > 16) return fail_msg("mpas_b200_compute_dyn_tend_work: maxEdges > 8 or maxEdges2 > 16 not supported");
     const size_t nEL = (size_t)(nEdges + 1) * L;
-    real* ft = workspace(0, nEL);
-    real* fw = workspace(1, nEL);
-    real* ft2 = workspace(2, nEL);
-    if (!ft || !fw || !ft2) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace");
+    // per-edge high-order fluxes of theta and w: per-block workspace keyed by the block's tend_u (runtime.cu)
+    const size_t nELp = (nEL + 1) & ~(size_t)1;
+    real* ft = keyed_workspace(p.tend_u, 3 * nELp, 1);
+    if (!ft) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace (the first call must be outside stream capture)");
+    real* fw = ft + nELp;
+    real* ft2 = fw + nELp;
     static const int flux_minb = tune("dt_flux_minb", 6);
     if (rk_step == 1) WLAUNCH((dt_edge_flux_kernel<true, 0>), p.nEdgesLoop, 0, p, ft, fw, ft2);
     else if (flux_minb == 5) WLAUNCH((dt_edge_flux_kernel<false, 5>), p.nEdgesLoop, 0, p, ft, fw, ft2);

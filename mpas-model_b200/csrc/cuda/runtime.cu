@@ -15,11 +15,10 @@
 
 #include <cstdlib>
 
-namespace mpas {
-extern std::string g_last_error;  // host_api.cpp
-}
 
 namespace mpasb200 {
+
+std::string g_last_error;  // message behind a non-zero return code (mpas_b200_last_error)
 
 namespace {
 struct Mirror {
@@ -46,51 +45,38 @@ void set_stream(cudaStream_t s) {
     g_own_stream = false;
 }
 int fail(const char* where, cudaError_t e) {
-    mpas::g_last_error = std::string(where) + ": " + cudaGetErrorString(e);
+    g_last_error = std::string(where) + ": " + cudaGetErrorString(e);
     return 1000 + (int)e;
 }
 int fail_msg(const std::string& msg) {
-    mpas::g_last_error = msg;
+    g_last_error = msg;
     return 1;
 }
 long long launches() { return g_launches; }
 void count_launch(int n) { g_launches += n; }
 
+// Library workspace keyed by a device address that identifies the block (an array of that block the routine is handed
+// anyway).  It replaces the reference's per-phase allocate/deallocate (TI:592-626, 1029-1099) for scratch the reference
+// argument lists have no room for: the three per-edge flux arrays of dyn_tend and the num_scalars-wide scratch of the
+// all-scalars monotonic transport.  Keyed, not global: captured step graphs of one Dycore bake these addresses in, so a
+// second (larger) Dycore in the same process must never make the first one's workspace move; several blocks of one
+// process run the mono routine concurrently (one host thread per block).  A device-resident Dycore provides the storage
+// itself (provide_keyed_workspace: a view of its scratch arena); for a host that calls the work routines directly the
+// library allocates on first use -- never inside a stream capture.
 namespace {
 struct Ws {
     real* p = nullptr;
     size_t count = 0;
+    bool owned = true;
 };
-Ws g_ws[16];
-}  // namespace
-real* workspace(int slot, size_t count) {
-    Ws& w = g_ws[slot];
-    if (w.count < count) {
-        if (w.p) {
-            cudaStreamSynchronize(stream());
-            cudaFree(w.p);
-        }
-        if (cudaMalloc(&w.p, count * sizeof(real) + 64) != cudaSuccess) {
-            w.p = nullptr;
-            w.count = 0;
-            return nullptr;
-        }
-        w.count = count;
-    }
-    return w.p;
-}
-
-// Per-block workspace (keyed by an address that identifies the block, e.g. its scale_arr): the all-scalars monotonic
-// transport needs num_scalars-wide scratch the reference argument list has no room for, and several blocks of one
-// process run the routine concurrently (one host thread per block), so the slots above cannot be shared.
-namespace {
 std::mutex g_kws_mu;
-std::map<const void*, Ws> g_kws;
+std::map<std::pair<const void*, int>, Ws> g_kws;
 }  // namespace
-real* keyed_workspace(const void* key, size_t count) {
+real* keyed_workspace(const void* key, size_t count, int slot) {
     std::lock_guard<std::mutex> lk(g_kws_mu);
-    Ws& w = g_kws[key];
+    Ws& w = g_kws[{key, slot}];
     if (w.count < count) {
+        if (!w.owned) return nullptr;  // the provider sized it; it does not grow behind the provider's back
         cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
         if (cudaStreamIsCapturing(stream(), &st) == cudaSuccess && st != cudaStreamCaptureStatusNone) return nullptr;  // never allocate inside a capture
         if (w.p) {
@@ -100,7 +86,7 @@ real* keyed_workspace(const void* key, size_t count) {
             w.count = 0;
         }
         if (cudaMalloc(&w.p, count * sizeof(real) + 64) != cudaSuccess) {
-            cudaGetLastError();  // clear the sticky-free allocation error: the caller falls back to the per-scalar path
+            cudaGetLastError();  // clear the sticky-free allocation error: the caller reports it
             w.p = nullptr;
             w.count = 0;
             return nullptr;
@@ -110,12 +96,24 @@ real* keyed_workspace(const void* key, size_t count) {
     }
     return w.p;
 }
+void provide_keyed_workspace(const void* key, int slot, real* p, size_t count) {
+    std::lock_guard<std::mutex> lk(g_kws_mu);
+    Ws& w = g_kws[{key, slot}];
+    if (w.p && w.owned) cudaFree(w.p);
+    w.p = p;
+    w.count = count;
+    w.owned = false;
+}
 void release_keyed_workspace(const void* key) {
     std::lock_guard<std::mutex> lk(g_kws_mu);
-    auto it = g_kws.find(key);
-    if (it == g_kws.end()) return;
-    if (it->second.p) cudaFree(it->second.p);
-    g_kws.erase(it);
+    for (auto it = g_kws.begin(); it != g_kws.end();) {
+        if (it->first.first == key) {
+            if (it->second.p && it->second.owned) cudaFree(it->second.p);
+            it = g_kws.erase(it);
+        } else {
+            ++it;
+        }
+    }
 }
 
 namespace {
@@ -270,6 +268,7 @@ int mpas_b200_synchronize() {
     return 0;
 }
 
+const char* mpas_b200_last_error() { return g_last_error.c_str(); }
 long long mpas_b200_launch_count() { return launches(); }
 int mpas_b200_real_size() { return (int)sizeof(real); }
 
@@ -319,15 +318,10 @@ int mpas_b200_finalize() {
     std::lock_guard<std::mutex> lk(g_mu);
     for (auto& kv : g_reg) cudaFree(kv.second.dev);
     g_reg.clear();
-    for (auto& w : g_ws) {
-        if (w.p) cudaFree(w.p);
-        w.p = nullptr;
-        w.count = 0;
-    }
     {
         std::lock_guard<std::mutex> lk2(g_kws_mu);
         for (auto& kv : g_kws)
-            if (kv.second.p) cudaFree(kv.second.p);
+            if (kv.second.p && kv.second.owned) cudaFree(kv.second.p);
         g_kws.clear();
     }
     return 0;

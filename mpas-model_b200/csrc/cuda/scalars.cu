@@ -919,8 +919,9 @@ extern "C" int mpas_b200_advance_scalars_mono_work(MPAS_MONO_ARGS) {
     }
     // ---- all scalars at once (default): needs the per-block workspace and the 6/8-slot edge tables
     if (tune("mono_fused", 1) && maxEdges <= 8 && p.nCellsLoop > 0) {
-        const size_t nel = (size_t)L * p.ns, nel1 = (size_t)(L + 1) * p.ns, nC1 = (size_t)nCells + 1, nE1 = (size_t)nEdges + 1;
-        const size_t n_edge = (nel * nE1 + 1) & ~(size_t)1, n_wd = (nel1 * nC1 + 1) & ~(size_t)1, n_cell = (nel * nC1 + 1) & ~(size_t)1;
+        const size_t nel = (size_t)L * p.ns, nel1 = (size_t)(L + 1) * p.ns;
+        const MonoWsLayout lay(L, p.ns, nCells, nEdges);
+        const size_t n_edge = lay.n_edge, n_wd = lay.n_wd, n_cell = lay.n_cell;
         const size_t shm = (size_t)WPB * (2 * tma_slot((int)nel) + tma_slot(L + 1) + (((int)nel1 + 3) & ~3)) * sizeof(real);
         static const int cell_minb = tune("monoN_cell_minb", 4), edge_minb = tune("monoN_edge_minb", 5);
         const void* cell_fn = cell_minb == 2 ? (const void*)monoN_cell_kernel<2> : cell_minb == 3 ? (const void*)monoN_cell_kernel<3> : (const void*)monoN_cell_kernel<4>;

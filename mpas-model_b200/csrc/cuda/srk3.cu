@@ -388,7 +388,10 @@ static int srk3_body(Dycore& m) {
             }
             {
                 Phase ph(m, "atm_compute_dyn_tend");
-                for (auto& b : m.blocks) CK(call_dyn_tend(b, rk_step, dt));  // TI:609
+                for (auto& b : m.blocks) {
+                    if (rk_step == 1) CK(dycore_zero_garbage(b, 1));  // TI:593-605
+                    CK(call_dyn_tend(b, rk_step, dt));  // TI:609
+                }
             }
             CK(xchg(m, {{"tend_u", 1}}));  // TI:642
             {
@@ -416,9 +419,13 @@ static int srk3_body(Dycore& m) {
             if (scalar_advection && !split) {  // TI:993-1099
                 if (rk_step < 3 || (!monotonic && !positive_definite)) {
                     Phase ph(m, "atm_advance_scalars");
-                    for (auto& b : m.blocks) CK(call_advance_scalars(b, rk_timestep[rk_step], rk_step, order, 0));
+                    for (auto& b : m.blocks) {
+                        CK(dycore_zero_garbage(b, 3));  // TI:1044-1045
+                        CK(call_advance_scalars(b, rk_timestep[rk_step], rk_step, order, 0));
+                    }
                 } else {
                     Phase ph(m, "atm_advance_scalars_mono");
+                    for (auto& b : m.blocks) CK(dycore_zero_garbage(b, 2));  // TI:1029-1050
                     CK(run_mono_all(m, rk_timestep[rk_step], 0));
                 }
             }
@@ -441,9 +448,13 @@ static int srk3_body(Dycore& m) {
         for (int rk_step = 1; rk_step <= 3; ++rk_step) {
             if (rk_step < 3 || (!monotonic && !positive_definite)) {
                 Phase ph(m, "atm_advance_scalars");
-                for (auto& b : m.blocks) CK(call_advance_scalars(b, rk_t[rk_step], rk_step, order, 1));
+                for (auto& b : m.blocks) {
+                    CK(dycore_zero_garbage(b, 3));  // TI:1417-1418
+                    CK(call_advance_scalars(b, rk_t[rk_step], rk_step, order, 1));
+                }
             } else {
                 Phase ph(m, "atm_advance_scalars_mono");
+                for (auto& b : m.blocks) CK(dycore_zero_garbage(b, 2));  // TI:1402-1423
                 CK(run_mono_all(m, rk_t[rk_step], 1));
             }
             if (rk_step < 3) CK(xchg(m, {{"scalars@2", 0}}));  // TI:1569-1572
@@ -533,13 +544,17 @@ int dycore_step(Dycore& m) {
 // solve_diagnostics (time_lev, dt, rk_step) | vert_imp_coefs (dts) | substep_finish (substep, split)
 int dycore_call(Dycore& m, const std::string& rt, const double* q, int nq) {
     auto need = [&](int n) { if (nq < n) throw std::runtime_error("dycore_call: too few parameters for " + rt); };
-    if (rt == "mono") { need(2); return run_mono_all(m, (real)q[0], (int)q[1]); }
+    if (rt == "mono") {
+        need(2);
+        for (auto& b : m.blocks) CK(dycore_zero_garbage(b, 2));
+        return run_mono_all(m, (real)q[0], (int)q[1]);
+    }
     for (auto& b : m.blocks) {
         if (rt == "acoustic") { need(2); CK(call_acoustic(b, (real)q[0], (int)q[1])); }
         else if (rt == "divdamp") { need(1); CK(call_divdamp(b, (real)q[0])); }
         else if (rt == "recover") { need(3); CK(call_recover(b, (real)q[0], (int)q[1], (int)q[2])); }
-        else if (rt == "dyn_tend") { need(2); CK(call_dyn_tend(b, (int)q[0], (real)q[1])); }
-        else if (rt == "advance_scalars") { need(4); CK(call_advance_scalars(b, (real)q[0], (int)q[1], (int)q[2], (int)q[3])); }
+        else if (rt == "dyn_tend") { need(2); if ((int)q[0] == 1) CK(dycore_zero_garbage(b, 1)); CK(call_dyn_tend(b, (int)q[0], (real)q[1])); }
+        else if (rt == "advance_scalars") { need(4); CK(dycore_zero_garbage(b, 3)); CK(call_advance_scalars(b, (real)q[0], (int)q[1], (int)q[2], (int)q[3])); }
         else if (rt == "solve_diagnostics") { need(3); CK(call_solve_diagnostics(b, (int)q[0], (real)q[1], (int)q[2])); }
         else if (rt == "vert_imp_coefs") { need(1); CK(call_vert_imp_coefs(b, (real)q[0])); }
         else if (rt == "smlstep") CK(call_smlstep(b));
@@ -672,7 +687,53 @@ int dycore_global_minmax(Dycore& m, const std::string& name, long long offset, l
     return 0;
 }
 
+// Order-independent checksum of the owned elements of a field: the sum (mod 2^64) of their bit patterns.  Owned-element
+// arithmetic does not depend on the partition, so the sum over all ranks is the same number for 1, 2, 4, 8 GPUs -- the
+// decomposition test of the reference (COMPASS decomp_test: P ranks == 1 rank, bitwise) as one printable integer.
+namespace {
+__global__ void checksum_kernel(const real* a, long long n, unsigned long long* out) {
+    unsigned long long v = 0;
+    for (long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x; t < n; t += (long long)gridDim.x * blockDim.x) {
+        real x = a[t];
+        if (x == (real)0.0) x = (real)0.0;  // -0 and +0 are the same value
+        if (sizeof(real) == 8) v += (unsigned long long)__double_as_longlong((double)x);
+        else v += (unsigned long long)__float_as_uint((float)x);
+    }
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(out, v);
+}
+}  // namespace
+
+int dycore_checksum(Dycore& m, const std::string& name, unsigned long long* out) {
+    unsigned long long* d = nullptr;
+    cudaError_t e = cudaMalloc(&d, sizeof(unsigned long long));
+    if (e != cudaSuccess) return fail("cudaMalloc checksum", e);
+    cudaMemsetAsync(d, 0, sizeof(unsigned long long), stream());
+    for (auto& b : m.blocks) {
+        auto it = b.f.find(name);
+        if (it == b.f.end() || it->second.kind != 0 || it->second.loc < 1 || it->second.loc > 3) {
+            cudaFree(d);
+            return fail_msg("mpas_b200_dycore_checksum: no decomposed real field " + name);
+        }
+        const DField& f = it->second;
+        const long long nOwned = f.loc == 1 ? (long long)b.c("nCellsSolve") : f.loc == 2 ? (long long)b.c("nEdgesSolve") : (long long)b.c("nVerticesSolve");
+        checksum_kernel<<<592, 256, 0, stream()>>>((const real*)f.dev, nOwned * f.inner, d);
+        count_launch();
+    }
+    cudaMemcpyAsync(out, d, sizeof(unsigned long long), cudaMemcpyDeviceToHost, stream());
+    e = cudaStreamSynchronize(stream());
+    cudaFree(d);
+    if (e != cudaSuccess) return fail("mpas_b200_dycore_checksum", e);
+    return 0;
+}
+
 }  // namespace mpasb200
+
+extern "C" int mpas_b200_dycore_checksum(void* h, const char* name, unsigned long long* out) {
+    try {
+        return mpasb200::dycore_checksum(*(mpasb200::Dycore*)h, name, out);
+    } catch (const std::exception& e) { return mpasb200::fail_msg(e.what()); }
+}
 
 extern "C" int mpas_b200_dycore_global_minmax(void* h, const char* name, long long offset, long long stride, double* mn, double* mx) {
     try {

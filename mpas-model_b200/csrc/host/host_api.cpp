@@ -1,6 +1,7 @@
 // C ABI of the host-side harness (mesh generation, decomposition, initial conditions).
 // Declared in include/mpas_b200.h.  Handles are opaque pointers; errors return non-zero /
 // NULL and leave a message retrievable through mpas_b200_last_error().
+#include <omp.h>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -41,7 +42,14 @@ struct HostCase {
 
 extern "C" {
 
-const char* mpas_b200_last_error() { return mpas::g_last_error.c_str(); }
+// OpenMP threads of the harness (mesh generation, initial state); n < 1 = all processors.  torch.distributed.run exports
+// OMP_NUM_THREADS=1 to its workers, which would make the set-up of a large mesh single-threaded.
+int mpas_host_set_num_threads(int n) {
+    if (n < 1) n = omp_get_num_procs();
+    omp_set_num_threads(n);
+    return n;
+}
+const char* mpas_host_last_error() { return mpas::g_last_error.c_str(); }
 
 // Create a global icosahedral mesh (unit sphere -> radius a), optionally SFC-reordered.
 void* mpas_host_case_create(int level, int lloyd_iters, int sfc) {

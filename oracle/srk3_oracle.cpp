@@ -6,6 +6,9 @@
 // exchanges follow mpas_dmpar_exch_halo_field (src/framework/mpas_dmpar.F:5386-5552, 5565-5748):
 // pack buffer((destList-1)*dim1+j) = array(j,srcList), unpack array(j,destList) = buffer((srcList-1)*dim1+j),
 // with a memcpy between blocks in place of MPI (the reference's own no-MPI path, :5481-5504).
+#include <omp.h>
+
+#include <chrono>
 #include <condition_variable>
 #include <cstdio>
 #include <cstring>
@@ -97,6 +100,9 @@ struct OModel {
     Barrier bar;
     std::string err;
     long nExchanges = 0;
+    // wall-clock per phase under the reference's own timer names (mpas_timer_start calls at TI:341...1369, src/framework/mpas_timer.F:88)
+    std::map<std::string, std::pair<double, long>> timers;
+    std::vector<std::string> timer_order;
 
     // exchange one field over the given halo layers (empty = all)
     void exchange_ptr(const std::vector<real*>& arrays, int loc, int inner, const std::vector<int>& layers) {
@@ -309,6 +315,23 @@ void model_init(OModel& m) {
     m.exchange("rw");
 }
 
+struct OPhase {  // mpas_timer_start / mpas_timer_stop of the reference, same names
+    OModel& m;
+    const char* name;
+    std::chrono::steady_clock::time_point t0;
+    OPhase(OModel& m_, const char* n) : m(m_), name(n), t0(std::chrono::steady_clock::now()) {}
+    ~OPhase() {
+        const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        auto it = m.timers.find(name);
+        if (it == m.timers.end()) {
+            m.timer_order.push_back(name);
+            it = m.timers.emplace(name, std::make_pair(0.0, 0L)).first;
+        }
+        it->second.first += ms;
+        it->second.second += 1;
+    }
+};
+
 // atm_srk3, TI:142-1796 (config_apply_lbcs = false, physics off, IAU off)
 // mpas_reconstruct at the end of atm_srk3 (TI:1594): u time level 2, owned cells
 void call_reconstruct(OBlock& b) {
@@ -347,23 +370,38 @@ void srk3_step(OModel& m) {
     m.exchange("scalars@1");
     m.exchange("pressure_p");
     m.exchange("rtheta_p");
-    for (auto& b : m.blocks) {  // TI:369, 410
+    for (auto& b : m.blocks) {  // TI:369
+        OPhase ph(m, "atm_rk_integration_setup");
         Dims d = dims(b);
         Ranges r = ranges(b);
         oracle_rk_integration_setup(d.L, d.ns, d.nC, d.nE, RANGES, b.R("ru"), b.R("ru_save"), b.R("rw"), b.R("rw_save"), b.R("rtheta_p"), b.R("rtheta_p_save"),
                                     b.R("rho_p"), b.R("rho_p_save"), b.R("rho_zz_old_split"), b.R("u@1"), b.R("u@2"), b.R("w@1"), b.R("w@2"), b.R("theta_m@1"),
                                     b.R("theta_m@2"), b.R("rho_zz@1"), b.R("rho_zz@2"), b.R("scalars@1"), b.R("scalars@2"));
+    }
+    for (auto& b : m.blocks) {  // TI:410
+        OPhase ph(m, "atm_compute_moist_coefficients");
+        Dims d = dims(b);
+        Ranges r = ranges(b);
         oracle_compute_moist_coefficients(d.L, d.ns, d.nC, d.nE, d.nCS, d.ms, d.me, RANGES, b.I("cellsOnEdge"), b.R("scalars@2"), b.R("cqw"), b.R("cqu"), b.R("qtot"));
     }
     for (int dynamics_substep = 1; dynamics_substep <= dynamics_split; ++dynamics_substep) {
-        for (auto& b : m.blocks) call_vert_imp_coefs(b, rk_sub_timestep[1]);  // TI:501
+        {
+            OPhase ph(m, "atm_compute_vert_imp_coefs");
+            for (auto& b : m.blocks) call_vert_imp_coefs(b, rk_sub_timestep[1]);  // TI:501
+        }
         m.exchange("exner");                                                  // TI:513
         for (int rk_step = 1; rk_step <= 3; ++rk_step) {
-            if (order == 3 && rk_step == 2)
+            if (order == 3 && rk_step == 2) {
+                OPhase ph(m, "atm_compute_vert_imp_coefs");
                 for (auto& b : m.blocks) call_vert_imp_coefs(b, rk_sub_timestep[rk_step]);  // TI:550
-            for (auto& b : m.blocks) call_dyn_tend(b, rk_step, dt);                          // TI:609
+            }
+            {
+                OPhase ph(m, "atm_compute_dyn_tend");
+                for (auto& b : m.blocks) call_dyn_tend(b, rk_step, dt);  // TI:609
+            }
             m.exchange("tend_u", {1});                                                       // TI:642
             for (auto& b : m.blocks) {                                                       // TI:669
+                OPhase ph(m, "small_step_prep");
                 Dims d = dims(b);
                 Ranges r = ranges(b);
                 oracle_set_smlstep_pert_variables_work(d.L, d.mE, d.nC, d.nE, d.nCS, b.I("nEdgesOnCell"), b.I("cellsOnEdge"), b.I("edgesOnCell"), b.R("fzm"),
@@ -372,9 +410,13 @@ void srk3_step(OModel& m) {
             }
             for (int small_step = 1; small_step <= number_sub_steps[rk_step]; ++small_step) {
                 m.exchange("rho_pp", {1});  // TI:792
-                for (auto& b : m.blocks) call_acoustic(b, rk_sub_timestep[rk_step], small_step);  // TI:824
+                {
+                    OPhase ph(m, "atm_advance_acoustic_step");
+                    for (auto& b : m.blocks) call_acoustic(b, rk_sub_timestep[rk_step], small_step);  // TI:824
+                }
                 m.exchange("rtheta_pp", {1});  // TI:845
                 for (auto& b : m.blocks) {     // TI:862
+                    OPhase ph(m, "atm_divergence_damping_3d");
                     Dims d = dims(b);
                     oracle_divergence_damping_3d(d.L, d.nC, d.nE, d.nCS, 1, d.nE, b.R("theta_m@1"), b.R("ru_p"), b.R("rtheta_pp"), b.R("rtheta_pp_old"),
                                                  b.I("cellsOnEdge"), b.R("specZoneMaskEdge"), rk_sub_timestep[rk_step], b.c("config_smdiv", 0.1), b.c("config_len_disp"));
@@ -384,16 +426,24 @@ void srk3_step(OModel& m) {
             m.exchange("ru_p");
             m.exchange("rho_pp");
             m.exchange("rtheta_pp", {2});
-            for (auto& b : m.blocks) call_recover(b, rk_timestep[rk_step], number_sub_steps[rk_step], rk_step);  // TI:917
+            {
+                OPhase ph(m, "atm_recover_large_step_variables");
+                for (auto& b : m.blocks) call_recover(b, rk_timestep[rk_step], number_sub_steps[rk_step], rk_step);  // TI:917
+            }
             m.exchange("u@2");                                                                                   // TI:988
             if (scalar_advection && !split) {                                                                    // TI:993-1099
                 if (rk_step < 3 || (!monotonic && !positive_definite)) {
+                    OPhase ph(m, "atm_advance_scalars");
                     for (auto& b : m.blocks) call_advance_scalars(b, rk_timestep[rk_step], rk_step, order, 0);
                 } else {
+                    OPhase ph(m, "atm_advance_scalars_mono");
                     run_mono_all(m, rk_timestep[rk_step], 0);
                 }
             }
-            for (auto& b : m.blocks) call_solve_diagnostics(b, 2, dt, rk_step);  // TI:1216
+            {
+                OPhase ph(m, "atm_compute_solve_diagnostics");
+                for (auto& b : m.blocks) call_solve_diagnostics(b, 2, dt, rk_step);  // TI:1216
+            }
             m.exchange("w@2");                                                   // TI:1234-1249
             m.exchange("pv_edge");
             m.exchange("rho_edge");
@@ -405,6 +455,7 @@ void srk3_step(OModel& m) {
             m.exchange("rtheta_p");
         }
         for (auto& b : m.blocks) {  // TI:1329
+            OPhase ph(m, "atm_rk_dynamics_substep_finish");
             Dims d = dims(b);
             Ranges r = ranges(b);
             oracle_rk_dynamics_substep_finish(d.L, d.nC, d.nE, dynamics_substep, dynamics_split, RANGES, b.R("ru"), b.R("ru_save"), b.R("rw"), b.R("rw_save"),
@@ -418,8 +469,10 @@ void srk3_step(OModel& m) {
         if (order == 2) rk_t[1] = dt / 2.;
         for (int rk_step = 1; rk_step <= 3; ++rk_step) {
             if (rk_step < 3 || (!monotonic && !positive_definite)) {
+                OPhase ph(m, "atm_advance_scalars");
                 for (auto& b : m.blocks) call_advance_scalars(b, rk_t[rk_step], rk_step, order, 1);
             } else {
+                OPhase ph(m, "atm_advance_scalars_mono");
                 run_mono_all(m, rk_t[rk_step], 1);
             }
             if (rk_step < 3) m.exchange("scalars@2");
@@ -433,7 +486,10 @@ void srk3_step(OModel& m) {
         for (size_t i = 0; i < n; ++i)
             if (s2[i] < 0.0) s2[i] = 0.0;
     }
-    for (auto& b : m.blocks) call_reconstruct(b);  // TI:1594
+    {
+        OPhase ph(m, "mpas_reconstruct");
+        for (auto& b : m.blocks) call_reconstruct(b);  // TI:1594
+    }
     // mpas_pool_shift_time_levels(state), mpas_atm_core.F:671
     for (auto& b : m.blocks)
         for (const char* n : {"u", "w", "theta_m", "rho_zz", "scalars"}) b.swap_levels(n);
@@ -569,5 +625,28 @@ int oracle_model_call(void* h, const char* routine, const double* q, int nq) {
     } catch (const std::exception& e) { g_oracle_err = e.what(); return 1; }
 }
 long oracle_model_exchange_count(void* h) { return ((OModel*)h)->nExchanges; }
+
+// per-phase wall-clock of the steps taken so far, reference timer names
+int oracle_model_timer_count(void* h) { return (int)((OModel*)h)->timer_order.size(); }
+int oracle_model_timer_get(void* h, int idx, char* name, int cap, double* ms, long* calls) {
+    OModel* m = (OModel*)h;
+    if (idx < 0 || idx >= (int)m->timer_order.size()) return 1;
+    const std::string& n = m->timer_order[idx];
+    std::strncpy(name, n.c_str(), cap - 1);
+    name[cap - 1] = 0;
+    *ms = m->timers[n].first;
+    *calls = m->timers[n].second;
+    return 0;
+}
+void oracle_model_timer_reset(void* h) {
+    for (auto& kv : ((OModel*)h)->timers) kv.second = {0.0, 0L};
+}
+// OpenMP threads of every later call (torch.distributed.run exports OMP_NUM_THREADS=1 to its workers)
+int oracle_set_num_threads(int n) {
+    if (n < 1) n = omp_get_num_procs();
+    omp_set_num_threads(n);
+    return n;
+}
+int oracle_get_max_threads() { return omp_get_max_threads(); }
 
 }  // extern "C"

@@ -85,6 +85,10 @@ def _bind_oracle(L):
         L.oracle_model_get_field.restype = C.c_void_p
         L.oracle_model_get_field.argtypes = [C.c_void_p, C.c_int, C.c_char_p]
         L.oracle_model_set_field_f64.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_void_p, C.c_longlong, C.c_int, C.c_int]
+        L.oracle_model_timer_count.argtypes = [C.c_void_p]
+        L.oracle_model_timer_get.argtypes = [C.c_void_p, C.c_int, C.c_char_p, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_long)]
+        L.oracle_model_timer_reset.argtypes = [C.c_void_p]
+        L.oracle_set_num_threads.argtypes = [C.c_int]
     return L
 
 
@@ -103,7 +107,7 @@ class OracleModel:
             for name in b.names():
                 kind, loc, dims = b.info(name)
                 inner = int(np.prod(dims[:-1])) if len(dims) > 1 else 1
-                ptr = host.lib().mpas_host_block_field_ptr(b.h, name.encode())
+                ptr = host.hostlib().mpas_host_block_field_ptr(b.h, name.encode())
                 if kind == 0:
                     self.L.oracle_model_set_field_f64(self.h, ib, name.encode(), ptr, int(np.prod(dims)), inner, loc)
                 else:
@@ -148,6 +152,19 @@ class OracleModel:
 
     def exchange_count(self):
         return self.L.oracle_model_exchange_count(self.h)
+
+    def timers(self):
+        """{reference timer name: (ms, calls)} of the steps taken since reset_timers (mpas_timer names, TI:341...1369)"""
+        out = {}
+        name = C.create_string_buffer(128)
+        ms, calls = C.c_double(), C.c_long()
+        for i in range(self.L.oracle_model_timer_count(self.h)):
+            self.L.oracle_model_timer_get(self.h, i, name, 128, C.byref(ms), C.byref(calls))
+            out[name.value.decode()] = (ms.value, calls.value)
+        return out
+
+    def reset_timers(self):
+        self.L.oracle_model_timer_reset(self.h)
 
     def __del__(self):
         try:

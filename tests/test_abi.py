@@ -9,18 +9,33 @@ import common
 ROOT = common.ROOT
 
 
-def _declared():
-    src = open(os.path.join(ROOT, "include", "mpas_b200.h")).read()
+def _declared(header="mpas_b200.h"):
+    src = open(os.path.join(ROOT, "include", header)).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    return sorted(set(re.findall(r"\b(mpas_(?:b200|host)_\w+)\s*\(", src)))
+    return sorted(set(re.findall(r"\b(mpas_(?:b200|host|nc)_\w+)\s*\(", src)))
 
 
 def test_library_loads_and_exports_every_declared_symbol():
     L = common.host.lib()
     names = _declared()
-    assert len(names) > 50
+    assert len(names) > 45
     missing = [n for n in names if not hasattr(L, n)]
     assert not missing, missing
+
+
+def test_host_harness_library_has_no_cuda_and_exports_its_header():
+    """libmpas_host.so (include/mpas_host.h) is what the CPU oracle and bench.py --impl reference load: it must not pull in
+    the CUDA product library."""
+    H = common.host.hostlib()
+    names = _declared("mpas_host.h")
+    assert len(names) > 35
+    missing = [n for n in names if not hasattr(H, n)]
+    assert not missing, missing
+    import subprocess
+    needed = subprocess.run(["objdump", "-p", common.host.HOSTLIB_PATH], capture_output=True, text=True).stdout
+    assert "libmpas_b200" not in needed and "libcuda" not in needed, needed
+    syms = subprocess.run(["nm", "-D", "--defined-only", common.host.HOSTLIB_PATH], capture_output=True, text=True).stdout
+    assert "mpas_b200_" not in syms
 
 
 def test_single_precision_library_exports_the_same_abi_with_4_byte_reals():

@@ -46,7 +46,7 @@ def test_sfc_mesh_equals_generator_mesh_up_to_permutation():
 def test_local_ordering_rules(case4):
     case, blocks = case4
     part = np.zeros(case.nCells, dtype=np.int32)
-    common.host.lib().mpas_host_case_get_partition(case.h, part.ctypes.data)
+    common.host.hostlib().mpas_host_case_get_partition(case.h, part.ctypes.data)
     for ib, b in enumerate(blocks):
         cfg = b.cfg()
         ids = b.field("indexToCellID")[:-1]

@@ -203,3 +203,50 @@ def test_seven_sided_cells_and_long_edge_lists(cr_pow, monkeypatch):
     for _ in range(2):
         gpu.step(1); ora.step(1)
         _compare(gpu, ora, blocks, STATE + DIAG, TOL)
+
+
+@pytest.mark.parametrize("nblocks", [1, 3])
+def test_memory_diet_is_bitwise_neutral_and_smaller(nblocks):
+    """diet (default): optional physics / output-only arrays without a mirror, phase-local scratch as views of one arena per
+    block with the garbage columns zero-filled at the start of each phase (TI:593-605, 1029-1050).  Every STATE / DIAG field
+    stays bitwise equal to the run in which every pool array has its own mirror; eager and graph replay."""
+    case, blocks = common.make_case(4, nblocks, nVertLevels=26, num_scalars=3)
+    _tracers(blocks, 3)
+    cfg = common.level_config(4)
+    a = common.GpuModel(blocks, cfg)
+    b = common.GpuModel(blocks, cfg, diet=False)
+    a.set_option("graph", 1)
+    assert a.is_scratch_view(0, "delsq_u") and a.is_scratch_view(0, "scale_arr") and a.is_scratch_view(0, "horiz_flux_arr")
+    assert a.is_scratch_view(0, "gradPVn") is None and a.is_scratch_view(0, "tend_ru_physics") is None
+    assert b.is_scratch_view(0, "delsq_u") is False and b.is_scratch_view(0, "gradPVn") is False
+    assert a.is_scratch_view(0, "u@1") is False
+    print("device bytes: diet %.1f MB, full %.1f MB" % (a.device_bytes() / 1e6, b.device_bytes() / 1e6))
+    assert a.device_bytes() < 0.85 * b.device_bytes()
+    a.init(); b.init()
+    a.step(4); b.step(4)
+    for ib in range(nblocks):
+        for n in STATE + DIAG:
+            assert np.array_equal(a.field(ib, n), b.field(ib, n)), (ib, n)
+
+
+def test_state_checksum_is_partition_independent():
+    """the owned-state checksum bench.py prints at every N (sum mod 2^64 of the bit patterns of the owned elements): 1 block ==
+    4 blocks, and it equals the same sum taken with numpy"""
+    sums = []
+    for nblocks in (1, 4):
+        case, blocks = common.make_case(4, nblocks, nVertLevels=26, num_scalars=2)
+        _tracers(blocks, 2)
+        gpu = common.GpuModel(blocks, common.level_config(4))
+        gpu.init()
+        gpu.step(3)
+        s = {n: gpu.checksum(n) for n in STATE}
+        for n in STATE:
+            tot = 0
+            for ib, b in enumerate(blocks):
+                loc = b.info(n)[1]
+                nown = int(b.cfg()[{1: "nCellsSolve", 2: "nEdgesSolve", 3: "nVerticesSolve"}[loc]])
+                x = gpu.field(ib, n)[:nown] + 0.0  # -0 -> +0
+                tot = (tot + int(np.ascontiguousarray(x).view(np.uint64).sum(dtype=np.uint64))) & ((1 << 64) - 1)
+            assert tot == s[n], n
+        sums.append(s)
+    assert sums[0] == sums[1]

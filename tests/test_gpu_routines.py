@@ -31,7 +31,7 @@ def state():
     ora.call("dyn_tend", 1, cfg["config_dt"]); ora.call("smlstep")
     dts = cfg["config_dt"] / 6
     ora.call("acoustic", dts, 1); ora.call("divdamp", dts); ora.call("acoustic", dts, 2)
-    gpu = common.GpuModel(blocks, cfg)  # uploads the host pools = the oracle's current state
+    gpu = common.GpuModel(blocks, cfg, diet=False)  # uploads the host pools = the oracle's current state; diet off: every pool array has its own mirror and is compared
     return blocks, cfg, gpu, ora
 
 
