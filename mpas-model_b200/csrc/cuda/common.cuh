@@ -165,6 +165,11 @@ __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity) {
 }
 // Element shift of a column inside its slot (every lane), and the copy itself (issuing lane only; adds its size to total).
 __device__ __forceinline__ int tma_shift(const real* gcol) { return (int)(((unsigned)(unsigned long long)gcol & 15u) / (unsigned)sizeof(real)); }
+// size of that copy, for callers that post the expected byte count before they issue it
+__device__ __forceinline__ unsigned tma_col_bytes(const real* gcol, int n) {
+    const unsigned sh = (unsigned)(unsigned long long)gcol & 15u;
+    return (sh + (unsigned)n * (unsigned)sizeof(real) + 15u) & ~15u;
+}
 __device__ __forceinline__ void tma_issue_col(unsigned sslot, const real* gcol, int n, unsigned mbar, unsigned& total) {
     const unsigned long long a = (unsigned long long)gcol;
     const unsigned sh = (unsigned)a & 15u;
@@ -208,6 +213,20 @@ struct MonoWsLayout {
         total = 2 * n_edge + n_wd + 3 * n_cell;
     }
 };
+
+// Edge tiles for the shared-memory staged stencil gathers (tiles.cu): consecutive edges [first[t], first[t+1]) (offsets
+// from the first edge of the plan's range) need the nc[t] <= ncmax distinct cells cells[t*ncmax ...] (1-based ids);
+// lidx[16*e + j] is the position of advCellsForEdge(j+1, e) in its tile's list.
+struct EdgeTilePlan {
+    int nTiles, ncmax;
+    const int* first;
+    const int* nc;
+    const int* cells;
+    const unsigned char* lidx;
+};
+// nullptr when the plan cannot be built now (inside a stream capture, out of memory): callers take the direct-gather kernel
+const EdgeTilePlan* edge_tile_plan(const int* d_advCellsForEdge, const int* d_nAdvCellsForEdge, int edgeStart, int nEdgesLoop, int nCells, int ncmax, int temax);
+void release_edge_tile_plans(const void* d_advCellsForEdge);  // nullptr: all
 
 // Translate a pointer handed over the C ABI: a registered host address (anywhere inside a
 // registered range) maps to its device mirror; anything else is taken to be a device pointer.

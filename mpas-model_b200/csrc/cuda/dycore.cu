@@ -76,8 +76,9 @@ int dycore_exchange(Dycore& m, const std::vector<XField>& fields) {
         if (p->send.nbr != p->recv.nbr || halo_p2p_tab(m.p2p, p->send, true, snd) || halo_p2p_tab(m.p2p, p->recv, false, rcv))
             return fail_msg("dycore_exchange: exchange '" + key + "' does not fit the peer-to-peer protocol (message larger than the window, or it does not "
                             "send to exactly the ranks it receives from); run with MPAS_B200_TUNE_p2p=0");
-        int rc = halo_pack_p2p(p, snd, m.p2p);
-        if (!rc) rc = halo_signal_p2p(snd, rcv, m.p2p);
+        bool signalled = false;
+        int rc = halo_pack_p2p(p, snd, rcv, m.p2p, signalled);
+        if (!rc && !signalled) rc = halo_signal_p2p(snd, rcv, m.p2p);
         if (!rc) rc = halo_unpack_p2p(p, rcv, m.p2p);
         return rc;
     }
@@ -121,6 +122,15 @@ int dycore_exchange(Dycore& m, const std::vector<XField>& fields) {
     return 0;
 }
 
+// A peer-to-peer wait that gave up leaves the halo columns of that exchange stale: every entry point that has just
+// synchronised (or is about to start new work) turns the raised flag into an error instead of carrying on.
+int dycore_check_p2p(Dycore& m) {
+    if (m.p2p.on && m.p2p.h_timeout && *(volatile int*)m.p2p.h_timeout)
+        return fail_msg("peer-to-peer halo exchange timed out waiting for a neighbour rank (MPAS_B200_TUNE_p2p_timeout_s, default 60 s): the state of this "
+                        "rank is no longer valid; a rank died or the ranks disagree about the exchange sequence");
+    return 0;
+}
+
 // ---- peer-to-peer windows ------------------------------------------------------------------------------------------------
 void dycore_p2p_teardown(Dycore& m) {
     P2P& pp = m.p2p;
@@ -130,8 +140,9 @@ void dycore_p2p_teardown(Dycore& m) {
     if (pp.win) cudaFree(pp.win);
     if (pp.seq_send) cudaFree(pp.seq_send);
     if (pp.seq_recv) cudaFree(pp.seq_recv);
-    if (pp.d_timeout) cudaFree(pp.d_timeout);
-    pp.win = nullptr; pp.seq_send = pp.seq_recv = nullptr; pp.d_timeout = nullptr;
+    if (pp.h_timeout) cudaFreeHost(pp.h_timeout);
+    if (pp.ticket) cudaFree(pp.ticket);
+    pp.win = nullptr; pp.seq_send = pp.seq_recv = nullptr; pp.d_timeout = pp.h_timeout = nullptr; pp.ticket = nullptr;
     pp.on = false;
 }
 
@@ -177,11 +188,17 @@ int dycore_p2p_setup(Dycore& m) {
     if (ok) ok = cudaMemsetAsync(pp.win, 0, wbytes, stream()) == cudaSuccess;
     if (ok) ok = cudaIpcGetMemHandle(&mine, pp.win) == cudaSuccess;
     if (ok) ok = cudaMalloc(&pp.seq_send, m.nranks * sizeof(unsigned long long)) == cudaSuccess && cudaMalloc(&pp.seq_recv, m.nranks * sizeof(unsigned long long)) == cudaSuccess &&
-                 cudaMalloc(&pp.d_timeout, sizeof(int)) == cudaSuccess;
+                 cudaMalloc(&pp.ticket, sizeof(unsigned)) == cudaSuccess && cudaHostAlloc(&pp.h_timeout, sizeof(int), cudaHostAllocMapped) == cudaSuccess;
+    if (ok) {
+        *pp.h_timeout = 0;
+        ok = cudaHostGetDevicePointer(&pp.d_timeout, pp.h_timeout, 0) == cudaSuccess;
+        pp.timeout_ns = (unsigned long long)std::max(1, tune("p2p_timeout_s", 60)) * 1000000000ULL;
+        if (!tune("p2p_fold_signal", 1)) { cudaFree(pp.ticket); pp.ticket = nullptr; }
+    }
     if (ok) {
         cudaMemsetAsync(pp.seq_send, 0, m.nranks * sizeof(unsigned long long), stream());
         cudaMemsetAsync(pp.seq_recv, 0, m.nranks * sizeof(unsigned long long), stream());
-        cudaMemsetAsync(pp.d_timeout, 0, sizeof(int), stream());
+        if (pp.ticket) cudaMemsetAsync(pp.ticket, 0, sizeof(unsigned), stream());
     }
     cudaGetLastError();
     // every rank's handle to every rank (a failed rank still takes part, with a zero handle)
@@ -328,6 +345,8 @@ void mpas_b200_dycore_destroy(void* h) {
             if (sa != b.f.end()) release_keyed_workspace(sa->second.dev);
         }
         if (b.arena) cudaFree(b.arena);
+        auto adv = b.f.find("advCellsForEdge");
+        if (adv != b.f.end()) release_edge_tile_plans(adv->second.dev);  // cached by the device address of this array (tiles.cu)
         for (auto& kv : b.f)
             if (kv.second.owned) cudaFree(kv.second.dev);
         for (auto& kv : b.halo.plans) halo_free_plan(kv.second);
@@ -485,7 +504,8 @@ int mpas_b200_dycore_step(void* h, int nsteps) {
     DY_TRY
     Dycore& m = *(Dycore*)h;
     for (int i = 0; i < nsteps; ++i) {
-        int rc = dycore_step(m);
+        int rc = dycore_check_p2p(m);
+        if (!rc) rc = dycore_step(m);
         if (rc) return rc;
     }
     return 0;
@@ -502,7 +522,7 @@ int mpas_b200_dycore_get_field(void* h, int iLocal, const char* name, void* host
     if (e != cudaSuccess) return fail("mpas_b200_dycore_get_field", e);
     e = cudaStreamSynchronize(stream());
     if (e != cudaSuccess) return fail("mpas_b200_dycore_get_field sync", e);
-    return 0;
+    return dycore_check_p2p(*(Dycore*)h);
     DY_CATCH
 }
 
@@ -544,13 +564,8 @@ int mpas_b200_dycore_halo_transport(void* h) {
     Dycore* m = (Dycore*)h;
     if (m->nranks < 2) return 0;
     if (!m->p2p.on) return 1;
-    int t = 0;
-    cudaMemcpyAsync(&t, m->p2p.d_timeout, sizeof(int), cudaMemcpyDeviceToHost, stream());
     cudaStreamSynchronize(stream());
-    if (t) {
-        cudaMemsetAsync(m->p2p.d_timeout, 0, sizeof(int), stream());
-        return -2;
-    }
+    if (*(volatile int*)m->p2p.h_timeout) return -2;
     return 2;
 }
 

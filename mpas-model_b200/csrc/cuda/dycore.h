@@ -97,6 +97,7 @@ struct XField {
 int dycore_exchange(Dycore& m, const std::vector<XField>& fields);
 int dycore_p2p_setup(Dycore& m);   // collective; leaves m.p2p.on false (NCCL path) when any rank cannot
 void dycore_p2p_teardown(Dycore& m);
+int dycore_check_p2p(Dycore& m);   // non-zero (with a message) once a peer-to-peer wait has given up
 int dycore_init(Dycore& m);
 int dycore_step(Dycore& m);
 int dycore_call(Dycore& m, const std::string& routine, const double* prm, int nprm);

@@ -326,6 +326,135 @@ __global__ void __launch_bounds__(WPB * 32, MINB) dt_edge_flux_kernel(DtP p, rea
     }
 }
 
+// The same fluxes with the stencil columns staged in shared memory (tiles.cu): one block per tile of consecutive edges.
+// Every thread below nc issues the bulk (TMA) copies of ONE cell's theta_m and w columns (16-byte window around the
+// column, as everywhere) and posts their byte count on the block's mbarrier; the block waits once, then each warp takes
+// every WPB-th edge of the tile and evaluates exactly the sums of dt_edge_flux_kernel with shared-memory reads in place
+// of the 2 x 10 gathered global loads per level pair.  About 1.1 columns per edge and array cross the L1/L2 boundary
+// instead of 10, coalesced and without a register or scoreboard.  Identical arithmetic, identical results.
+// dynamic shared memory: 2 * ncmax * tma_slot(L + 1) reals.
+#define FT_NCMAX 112
+#define FT_TEMAX 64
+template <bool RK1>
+__global__ void __launch_bounds__(WPB * 32, 2) dt_edge_flux_tile_kernel(DtP p, EdgeTilePlan tp, real* __restrict__ ft, real* __restrict__ fw, real* __restrict__ ft2) {
+    extern __shared__ __align__(16) real s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar;
+    __shared__ unsigned short s_base_t[FT_NCMAX], s_base_w[FT_NCMAX];  // element offset of level 1 of each staged column
+    __shared__ unsigned short s_ot[WPB][20], s_ow[WPB][20];
+    __shared__ real s_cp[WPB][20], s_cm[WPB][20];
+    const int L = p.L, L1 = L + 1, LS = tma_slot(L1);
+    const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int e0 = tp.first[tile], e1 = tp.first[tile + 1], nc = tp.nc[tile];
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar);
+    if (tid == 0) mbar_init(mbar, (unsigned)nc);
+    __syncthreads();
+    if (tid < nc) {
+        const int c = tp.cells[(size_t)tile * tp.ncmax + tid];
+        const real* gt = p.theta_m + (size_t)(c - 1) * L;
+        const real* gw = p.w + (size_t)(c - 1) * L1;
+        const unsigned s0 = (unsigned)__cvta_generic_to_shared(s_dyn), cs = (unsigned)(LS * sizeof(real));
+        mbar_arrive_expect_tx(mbar, tma_col_bytes(gt, L) + tma_col_bytes(gw, L1));
+        unsigned dummy = 0;
+        tma_issue_col(s0 + (unsigned)tid * cs, gt, L, mbar, dummy);
+        tma_issue_col(s0 + (unsigned)(tp.ncmax + tid) * cs, gw, L1, mbar, dummy);
+        s_base_t[tid] = (unsigned short)(tid * LS + tma_shift(gt));
+        s_base_w[tid] = (unsigned short)((tp.ncmax + tid) * LS + tma_shift(gw));
+    }
+    __syncthreads();
+    mbar_wait(mbar, 0);
+    for (int er = e0 + warp; er < e1; er += WPB) {
+        const int iEdge = p.edgeStart + er;
+        const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+        if (!(cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve)) continue;
+        const int n = p.nAdvCellsForEdge[iEdge - 1];
+        const int npad = (n + FUNR - 1) / FUNR * FUNR;
+        __syncwarp();
+        if (lane < npad) {
+            const bool in = lane < n;
+            const int li = in ? (int)tp.lidx[(size_t)er * 16 + lane] : 0;
+            const real a = in ? p.adv_coefs[IX2(lane + 1, iEdge, 15)] : (real)0.0, a3 = in ? p.adv_coefs_3rd[IX2(lane + 1, iEdge, 15)] : (real)0.0;
+            s_ot[warp][lane] = s_base_t[li];
+            s_ow[warp][lane] = s_base_w[li];
+            s_cp[warp][lane] = a + a3;
+            s_cm[warp][lane] = a - a3;
+        }
+        __syncwarp();
+        const real dv = p.dvEdge[iEdge - 1];
+        const unsigned eoff = (unsigned)(iEdge - 1) * (unsigned)L;
+        const unsigned c1off = (unsigned)(cell1 - 1) * (unsigned)L, c2off = (unsigned)(cell2 - 1) * (unsigned)L;
+        for (int ka = lane; ka < L; ka += 64) {  // 0-based levels ka and ka + 32
+            const bool vb = ka + 32 < L;
+            const int bo = vb ? 32 : 0;
+            const real* __restrict__ rup = elem_ptr(p.ru + ka, eoff);
+            const real rue_a = rup[0], rue_b = rup[bo];
+            const int mo = ka > 0 ? -1 : 0;
+            const real rum_a = rup[mo], rum_b = rup[bo - 1 + (vb ? 0 : 1 + mo)];
+            real rs_a = 0, rs_b = 0, t1_a = 0, t1_b = 0, t2_a = 0, t2_b = 0;
+            if (!RK1) {
+                const real* __restrict__ rs = elem_ptr(p.ru_save + ka, eoff);
+                const real* __restrict__ t1 = elem_ptr(p.theta_m_save + ka, c1off);
+                const real* __restrict__ t2 = elem_ptr(p.theta_m_save + ka, c2off);
+                rs_a = rs[0]; rs_b = rs[bo];
+                t1_a = t1[0]; t1_b = t1[bo];
+                t2_a = t2[0]; t2_b = t2[bo];
+            }
+            {
+                const real* tab_a = signbit(rue_a) ? s_cm[warp] : s_cp[warp];
+                const real* tab_b = signbit(rue_b) ? s_cm[warp] : s_cp[warp];
+                const real* th = s_dyn + ka;
+                real f_a = 0.0, f_b = 0.0;
+                for (int j = 0; j < npad; j += FUNR) {
+                    real xa[FUNR], xb[FUNR];
+#pragma unroll
+                    for (int t = 0; t < FUNR; ++t) {
+                        const real* q = th + s_ot[warp][j + t];
+                        xa[t] = q[0];
+                        xb[t] = q[bo];
+                    }
+#pragma unroll
+                    for (int t = 0; t < FUNR; ++t) {
+                        f_a = f_a + tab_a[j + t] * xa[t];
+                        f_b = f_b + tab_b[j + t] * xb[t];
+                    }
+                }
+                real* o = ft + (size_t)eoff + ka;
+                o[0] = rue_a * f_a;
+                if (vb) o[32] = rue_b * f_b;
+            }
+            {
+                const real ruw_a = p.fzm[ka] * rue_a + p.fzp[ka] * rum_a;
+                const real ruw_b = p.fzm[ka + bo] * rue_b + p.fzp[ka + bo] * rum_b;
+                const real* tab_a = signbit(ruw_a) ? s_cm[warp] : s_cp[warp];
+                const real* tab_b = signbit(ruw_b) ? s_cm[warp] : s_cp[warp];
+                const real* wp = s_dyn + ka;
+                real f_a = 0.0, f_b = 0.0;
+                for (int j = 0; j < npad; j += FUNR) {
+                    real xa[FUNR], xb[FUNR];
+#pragma unroll
+                    for (int t = 0; t < FUNR; ++t) {
+                        const real* q = wp + s_ow[warp][j + t];
+                        xa[t] = q[0];
+                        xb[t] = q[bo];
+                    }
+#pragma unroll
+                    for (int t = 0; t < FUNR; ++t) {
+                        f_a = f_a + tab_a[j + t] * xa[t];
+                        f_b = f_b + tab_b[j + t] * xb[t];
+                    }
+                }
+                real* o = fw + (size_t)eoff + ka;
+                if (ka > 0) o[0] = ruw_a * f_a;
+                if (vb) o[32] = ruw_b * f_b;
+            }
+            if (!RK1) {
+                real* o = ft2 + (size_t)eoff + ka;
+                o[0] = dv * (rs_a - rue_a) * (real)0.5 * (t2_a + t1_a);
+                if (vb) o[32] = dv * (rs_b - rue_b) * (real)0.5 * (t2_b + t1_b);
+            }
+        }
+    }
+}
+
 // vertical mixing of u (TI:4949-5006), off by default: kept out of line so that it costs the common path no registers
 __device__ __noinline__ real u_vmix_term(const DtP& p, int k, int iEdge, int cell1, int cell2, real rho_e) {
     const int L = p.L, L1 = L + 1;
@@ -858,8 +987,20 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     if (!ft) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace (the first call must be outside stream capture)");
     real* fw = ft + nELp;
     real* ft2 = fw + nELp;
-    static const int flux_minb = tune("dt_flux_minb", 6);
-    if (rk_step == 1) WLAUNCH((dt_edge_flux_kernel<true, 0>), p.nEdgesLoop, 0, p, ft, fw, ft2);
+    static const int flux_minb = tune("dt_flux_minb", 6), flux_tile = tune("dt_flux_tile", 0);
+    // shared-memory staged stencil (tiles.cu) when the plan exists and two column sets of ncmax cells fit; else direct gathers
+    const EdgeTilePlan* tp = nullptr;
+    const size_t tile_shm = (size_t)2 * FT_NCMAX * tma_slot(L + 1) * sizeof(real);
+    if (flux_tile && 2 * FT_NCMAX * tma_slot(L + 1) < 65536 && p.nEdgesLoop > 0 &&
+        ensure_dyn_smem(rk_step == 1 ? (const void*)dt_edge_flux_tile_kernel<true> : (const void*)dt_edge_flux_tile_kernel<false>, tile_shm))
+        tp = edge_tile_plan(p.advCellsForEdge, p.nAdvCellsForEdge, p.edgeStart, p.nEdgesLoop, nCells, FT_NCMAX, FT_TEMAX);
+    if (tp) {
+        ktime_begin(rk_step == 1 ? "dt_edge_flux_tile_kernel<true>" : "dt_edge_flux_tile_kernel<false>");
+        if (rk_step == 1) dt_edge_flux_tile_kernel<true><<<tp->nTiles, WPB * 32, tile_shm, stream()>>>(p, *tp, ft, fw, ft2);
+        else dt_edge_flux_tile_kernel<false><<<tp->nTiles, WPB * 32, tile_shm, stream()>>>(p, *tp, ft, fw, ft2);
+        ktime_end();
+        count_launch();
+    } else if (rk_step == 1) WLAUNCH((dt_edge_flux_kernel<true, 0>), p.nEdgesLoop, 0, p, ft, fw, ft2);
     else if (flux_minb == 5) WLAUNCH((dt_edge_flux_kernel<false, 5>), p.nEdgesLoop, 0, p, ft, fw, ft2);
     else if (flux_minb == 6) WLAUNCH((dt_edge_flux_kernel<false, 6>), p.nEdgesLoop, 0, p, ft, fw, ft2);
     else WLAUNCH((dt_edge_flux_kernel<false, 0>), p.nEdgesLoop, 0, p, ft, fw, ft2);

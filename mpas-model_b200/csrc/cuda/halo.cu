@@ -54,8 +54,30 @@ __device__ __forceinline__ int p2p_find_item(const P2PItems& it, long long t) {
     return i;
 }
 
-// window[dst][me][parity][pos - off + j] = array[(idx-1)*inner + j]; parity = (messages sent to dst so far + 1) & 1
-__global__ void __launch_bounds__(256) halo_pack_p2p_kernel(P2PItems it, P2PSideTab tab, const unsigned long long* __restrict__ seq_send) {
+__device__ __forceinline__ unsigned long long global_timer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    return t;
+}
+
+// one thread per neighbour: count the message and publish its number to the receiver; count the messages about to be received
+__device__ __forceinline__ void p2p_signal(int t, const P2PSideTab& snd, const P2PSideTab& rcv, unsigned long long* seq_send, unsigned long long* seq_recv) {
+    if (t < snd.n) {
+        const unsigned long long m = seq_send[snd.rank[t]] + 1ULL;
+        seq_send[snd.rank[t]] = m;
+        __threadfence_system();
+        st_release_sys(snd.flag[t], m);
+    } else if (t >= MPAS_P2P_MAXN && t - MPAS_P2P_MAXN < rcv.n) {
+        seq_recv[rcv.rank[t - MPAS_P2P_MAXN]] += 1ULL;
+    }
+}
+
+// window[dst][me][parity][pos - off + j] = array[(idx-1)*inner + j]; parity = (messages sent to dst so far + 1) & 1.
+// SIGNAL: the block that finishes last (a ticket counter, reset for the next exchange) publishes the message numbers, so an
+// exchange is two graph nodes (pack + signal, wait + unpack) instead of three.
+template <bool SIGNAL>
+__global__ void __launch_bounds__(256) halo_pack_p2p_kernel(P2PItems it, P2PSideTab tab, P2PSideTab rcv, unsigned long long* seq_send, unsigned long long* seq_recv,
+                                                            unsigned* ticket) {
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t < it.start[it.n]) {
         const int i = p2p_find_item(it, t);
@@ -68,37 +90,54 @@ __global__ void __launch_bounds__(256) halo_pack_p2p_kernel(P2PItems it, P2PSide
         real* dst = tab.slot[s] + (size_t)(m & 1ULL) * (size_t)tab.cap;
         dst[(size_t)(it.pos[i][e] - tab.off[s]) + j] = it.array[i][(size_t)(it.idx[i][e] - 1) * inner + j];
     }
-    __threadfence_system();  // the peer stores of this thread are performed before the grid ends (the signal kernel follows)
+    __threadfence_system();  // the peer stores of this thread are performed before the message number is published
+    if (SIGNAL) {
+        __shared__ unsigned s_last;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const unsigned k = atomicAdd(ticket, 1u);
+            s_last = (k == gridDim.x - 1) ? 1u : 0u;
+            if (s_last) *ticket = 0u;  // every other block has taken its ticket: ready for the next exchange
+        }
+        __syncthreads();
+        if (s_last) {
+            __threadfence();  // acquire side of the ticket: all blocks' seq_send reads and peer stores precede the signal
+            p2p_signal((int)threadIdx.x, tab, rcv, seq_send, seq_recv);
+        }
+    }
 }
 
-// one thread per neighbour: count the message and publish its number to the receiver; count the messages about to be received
 __global__ void halo_signal_p2p_kernel(P2PSideTab snd, P2PSideTab rcv, unsigned long long* seq_send, unsigned long long* seq_recv) {
-    const int t = threadIdx.x;
-    if (t < snd.n) {
-        const unsigned long long m = seq_send[snd.rank[t]] + 1ULL;
-        seq_send[snd.rank[t]] = m;
-        __threadfence_system();
-        st_release_sys(snd.flag[t], m);
-    } else if (t >= MPAS_P2P_MAXN && t - MPAS_P2P_MAXN < rcv.n) {
-        seq_recv[rcv.rank[t - MPAS_P2P_MAXN]] += 1ULL;
-    }
+    p2p_signal((int)threadIdx.x, snd, rcv, seq_send, seq_recv);
 }
 
 // waits until every source of the plan has published the message expected now, then
-// array[(idx-1)*inner + j] = window[me][src][parity][pos - off + j]
-__global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(P2PItems it, P2PSideTab tab, const unsigned long long* __restrict__ seq_recv, int* timeout_flag) {
+// array[(idx-1)*inner + j] = window[me][src][parity][pos - off + j].
+// A wait that gives up (timeout_ns of wall time: a peer died, or the ranks disagree about the exchange sequence) raises
+// *timeout_flag -- host-mapped memory the library checks wherever it synchronises -- and the block does NOT scatter the
+// stale window contents.
+__global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(P2PItems it, P2PSideTab tab, const unsigned long long* __restrict__ seq_recv, volatile int* timeout_flag,
+                                                              unsigned long long timeout_ns) {
+    __shared__ int s_fail;
+    if (threadIdx.x == 0) s_fail = 0;
+    __syncthreads();
     if ((int)threadIdx.x < tab.n) {
         const unsigned long long want = seq_recv[tab.rank[threadIdx.x]];
-        const long long t0 = clock64();
-        while (ld_acquire_sys(tab.flag[threadIdx.x]) < want) {
-            if (clock64() - t0 > 8000000000LL) {  // ~4 s: a peer died or the ranks disagree about the exchange sequence
-                *timeout_flag = 1;
-                break;
+        if (ld_acquire_sys(tab.flag[threadIdx.x]) < want) {
+            const unsigned long long t0 = global_timer_ns();
+            while (ld_acquire_sys(tab.flag[threadIdx.x]) < want) {
+                if (*timeout_flag || global_timer_ns() - t0 > timeout_ns) {
+                    *timeout_flag = 1;
+                    __threadfence_system();
+                    s_fail = 1;
+                    break;
+                }
+                __nanosleep(100);
             }
-            __nanosleep(100);
         }
     }
     __syncthreads();
+    if (s_fail) return;
     const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= it.start[it.n]) return;
     const int i = p2p_find_item(it, t);
@@ -261,9 +300,16 @@ int p2p_for_chunks(HaloPlan* p, const HaloSide& side, F&& launch) {
 }
 }  // namespace
 
-int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2P& pp) {
+// pack (+ signal when the group is one launch: always, exchange groups have <= 8 fields); returns through `signalled`
+// whether the message numbers have been published by the pack launch itself
+int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp, bool& signalled) {
+    int nsel = 0;
+    for (size_t i = 0; i < p->items.size(); ++i) nsel += p->send.n[i] != 0;
+    signalled = pp.ticket != nullptr && nsel > 0 && nsel <= MPAS_P2P_MAXITEMS;
+    const bool fold = signalled;
     return p2p_for_chunks(p, p->send, [&](const P2PItems& it) {
-        halo_pack_p2p_kernel<<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, snd, pp.seq_send);
+        if (fold) halo_pack_p2p_kernel<true><<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, snd, rcv, pp.seq_send, pp.seq_recv, pp.ticket);
+        else halo_pack_p2p_kernel<false><<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, snd, rcv, pp.seq_send, pp.seq_recv, nullptr);
         count_launch();
     });
 }
@@ -279,7 +325,7 @@ int halo_signal_p2p(const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp)
 
 int halo_unpack_p2p(HaloPlan* p, const P2PSideTab& rcv, const P2P& pp) {
     return p2p_for_chunks(p, p->recv, [&](const P2PItems& it) {
-        halo_unpack_p2p_kernel<<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, rcv, pp.seq_recv, pp.d_timeout);
+        halo_unpack_p2p_kernel<<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, rcv, pp.seq_recv, pp.d_timeout, pp.timeout_ns);
         count_launch();
     });
 }

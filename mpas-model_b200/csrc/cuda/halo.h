@@ -71,7 +71,8 @@ struct Nccl {
 // The NCCL send/recv pair of an exchange costs ~40 us for these few-hundred-kilobyte messages: latency, not bandwidth.
 // With the peers' receive windows mapped into this process (CUDA IPC) the pack kernel stores straight into the
 // neighbour's window, one thread then publishes a sequence number per neighbour (st.release.sys) and the neighbour's
-// unpack kernel waits for it (ld.acquire.sys): three plain kernels per exchange, graph-capturable, no proxy thread.
+// unpack kernel waits for it (ld.acquire.sys): plain kernels, graph-capturable, no proxy thread.  The block of the pack
+// kernel that finishes last publishes the numbers itself, so an exchange is two launches: pack + signal, wait + unpack.
 // Window of a rank: [nranks flags (u64) padded to 256 B][nranks sources x 2 parities x cap reals].  Message m of the
 // pair (src -> dst) goes to parity m & 1: src cannot send message m + 2 before it has unpacked dst's message m + 1,
 // which dst sends only after unpacking m, so two slots per pair suffice.  The per-pair message counters live in device
@@ -92,13 +93,16 @@ struct P2P {
     char* win = nullptr;          // this rank's window
     std::vector<char*> peer;      // every rank's window as mapped here (peer[rank] == win)
     unsigned long long *seq_send = nullptr, *seq_recv = nullptr;  // device, nranks each
-    int* d_timeout = nullptr;     // device: set when a wait gave up (the exchange then delivered stale data)
+    int* h_timeout = nullptr;     // pinned host word, mapped: raised by a wait that gave up (that block then skipped its scatter)
+    int* d_timeout = nullptr;     // the device alias of h_timeout
+    unsigned* ticket = nullptr;   // device: block ticket of the pack kernel (the last block publishes the message numbers)
+    unsigned long long timeout_ns = 60000000000ULL;  // MPAS_B200_TUNE_p2p_timeout_s (wall time, %globaltimer)
     static size_t flag_bytes(int nranks) { return ((size_t)nranks * 8 + 255) & ~(size_t)255; }
     real* slot(char* w, int src, int par) const { return (real*)(w + flag_bytes(nranks)) + ((size_t)src * 2 + par) * (size_t)cap; }
     unsigned long long* flag(char* w, int src) const { return (unsigned long long*)w + src; }
 };
 int halo_p2p_tab(const P2P& pp, const HaloSide& side, bool is_send, P2PSideTab& tab);  // non-zero: a message exceeds cap
-int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2P& pp);
+int halo_pack_p2p(HaloPlan* p, const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp, bool& signalled);
 int halo_signal_p2p(const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp);
 int halo_unpack_p2p(HaloPlan* p, const P2PSideTab& rcv, const P2P& pp);
 

@@ -237,6 +237,7 @@ int mpas_b200_unregister_field(const void* host) {
     std::lock_guard<std::mutex> lk(g_mu);
     auto it = g_reg.find((uintptr_t)host);
     if (it == g_reg.end()) return fail_msg("mpas_b200_unregister_field: address not registered");
+    release_edge_tile_plans(it->second.dev);
     cudaFree(it->second.dev);
     g_reg.erase(it);
     return 0;
@@ -316,6 +317,7 @@ int mpas_b200_ktime_report(char* buf, int cap) {
 
 int mpas_b200_finalize() {
     std::lock_guard<std::mutex> lk(g_mu);
+    release_edge_tile_plans(nullptr);
     for (auto& kv : g_reg) cudaFree(kv.second.dev);
     g_reg.clear();
     {

@@ -684,7 +684,7 @@ int dycore_global_minmax(Dycore& m, const std::string& name, long long offset, l
     }
     *mn = lo;
     *mx = hi;
-    return 0;
+    return dycore_check_p2p(m);
 }
 
 // Order-independent checksum of the owned elements of a field: the sum (mod 2^64) of their bit patterns.  Owned-element
@@ -724,7 +724,7 @@ int dycore_checksum(Dycore& m, const std::string& name, unsigned long long* out)
     e = cudaStreamSynchronize(stream());
     cudaFree(d);
     if (e != cudaSuccess) return fail("mpas_b200_dycore_checksum", e);
-    return 0;
+    return dycore_check_p2p(m);
 }
 
 }  // namespace mpasb200
