@@ -173,12 +173,12 @@ def cpu_model(a, level, ns, threads):
 
 def cpu_sample_level(a, ns, threads, nsteps, budget_s, max_level):
     """largest icosahedral level <= max_level whose `nsteps` steps fit `budget_s` of CPU time, from a one-step probe on level 5"""
-    case, block, m = cpu_model(a, 5, ns, threads)
+    level = min(5, max_level)
+    case, block, m = cpu_model(a, level, ns, threads)
     m.step(1)
     t0 = time.perf_counter()
     m.step(1)
     per_cell = (time.perf_counter() - t0) / case.nCells
-    level = 5
     while level < max_level and per_cell * LEVEL_CELLS[level + 1] * nsteps <= budget_s:
         level += 1
     return level

@@ -62,6 +62,24 @@ int mpas_b200_rk_dynamics_substep_finish(MPAS_SUBSTEPFINISH_ARGS);         /* TI
 int mpas_b200_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS);             /* TI:5825 */
 int mpas_b200_reconstruct_2d(MPAS_RECONSTRUCT_ARGS);                       /* mpas_vector_reconstruction.F:195, called TI:1594 */
 
+/* ---- Layer 1: halo exchange for a host that keeps its own blocks and exchange lists (the bodies of
+ * mpas_dmpar_exch_halo_field2d_real / 3d_real, src/framework/mpas_dmpar.F:5386-5552, 5565-5748).
+ * kind: 1 cell, 2 edge, 3 vertex (the decomposed, LAST dimension); which: 0 send lists, 1 recv lists;
+ * layer_mask: bit (l-1) selects halo layer l, 0 = all layers (the optional haloLayersIn of the reference).
+ * Lists are the host's own, as mpas_dmpar_get_exch_list built them (mpas_dmpar.F:1483-2038): per list endPointID (rank),
+ * halo layer, nList and the 1-based srcList / destList (all lists of a side concatenated).  endPoint == own rank is the
+ * reference's copyList.  Arrays: registered host addresses or device pointers, extent includes the +1 garbage column. ---- */
+int mpas_b200_halo_comm_init(int rank, int nranks, const void* id128);  /* id from mpas_b200_nccl_unique_id, broadcast by the host */
+int mpas_b200_halo_register_lists(int kind, int which, int nLists, const int* endPoint, const int* haloLayer, const int* nList, const int* srcList,
+                                  const int* destList);
+int mpas_b200_exch_halo_field1d(mpas_real* array, int kind, int layer_mask);                    /* mpas_dmpar.F:5253 */
+int mpas_b200_exch_halo_field2d(mpas_real* array, int dim1, int kind, int layer_mask);          /* mpas_dmpar.F:5386 */
+int mpas_b200_exch_halo_field3d(mpas_real* array, int dim1, int dim2, int kind, int layer_mask); /* mpas_dmpar.F:5565 */
+long mpas_b200_halo_exchange_count(void);
+/* the halo_fn of mpas_b200_advance_scalars_mono_work for such a host (TI:3757, 4098): ctx -> int[2] = {nVertLevels, num_scalars} */
+int mpas_b200_mono_halo_default(void* ctx, int which, mpas_real* array);
+int mpas_b200_halo_finalize(void);
+
 /* ---- Layer 2: device-resident dycore ---- */
 void* mpas_b200_dycore_create(int nLocalBlocks, int rank, int nranks);
 void mpas_b200_dycore_destroy(void* h);

@@ -65,11 +65,27 @@ int dycore_exchange(Dycore& m, const std::vector<XField>& fields) {
             HaloPlan* p = halo_build_plan(blk.halo, items);
             blk.halo.plans[k2] = p;
             plans[b] = p;
+            if (m.nranks > 1 && m.p2p.on && P == 1) {
+                // a plan first seen after the switch to peer stores (every rank builds it at the same call): all ranks agree
+                // whether it fits the two-slot protocol; if it does not on ANY rank it goes over NCCL on all of them
+                P2PSideTab a, c;
+                const bool fits = p->send.nbr == p->recv.nbr && !halo_p2p_tab(m.p2p, p->send, true, a) && !halo_p2p_tab(m.p2p, p->recv, false, c);
+                real hv = fits ? (real)0.0 : (real)1.0;
+                real* d_tmp = nullptr;
+                if (cudaMalloc(&d_tmp, 2 * sizeof(real)) != cudaSuccess) return fail_msg("dycore_exchange: cudaMalloc");
+                cudaMemcpyAsync(d_tmp, &hv, sizeof(real), cudaMemcpyHostToDevice, stream());
+                const int nrc = m.nccl.allreduce_max(d_tmp, d_tmp + 1, 1, stream());
+                cudaMemcpyAsync(&hv, d_tmp + 1, sizeof(real), cudaMemcpyDeviceToHost, stream());
+                const cudaError_t se = cudaStreamSynchronize(stream());
+                cudaFree(d_tmp);
+                if (nrc || se != cudaSuccess) return fail_msg("dycore_exchange: collective check of a new exchange plan failed (a plan cannot be built inside a stream capture)");
+                p->p2p_ok = hv == (real)0.0;
+            }
         } else {
             plans[b] = it->second;
         }
     }
-    if (m.nranks > 1 && m.p2p.on && P == 1) {
+    if (m.nranks > 1 && m.p2p.on && P == 1 && plans[0]->p2p_ok) {
         // peer-to-peer: pack straight into the neighbours' windows, publish, wait + unpack (halo.h)
         HaloPlan* p = plans[0];
         P2PSideTab snd, rcv;

@@ -42,6 +42,9 @@ struct HaloSide {                      // send or recv side of a plan
 struct HaloPlan {
     std::vector<HaloItem> items;
     HaloSide send, recv;
+    // false: some rank's plan of this exchange does not send to exactly the ranks it receives from (or exceeds the window):
+    // agreed collectively when the plan is built after the peer-to-peer switch; such an exchange travels over NCCL on every rank
+    bool p2p_ok = true;
 };
 
 struct HaloBlock {  // exchange lists of one block, by location (index 1..3)

@@ -47,9 +47,22 @@ def main():
     same = np.array_equal(dy.field(0, "u@1")[:nE], d1.field(0, "u@1")[inv[eids - 1]])
     ok &= same
     transport = dy.halo_transport()  # raises after a peer-to-peer timeout
+    # the reference's halo test idiom across processes (mpas_test_core_halo_exch.F:631 fill, :1010 validate) over whatever
+    # transport the steps have switched to
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", "tests"))
+    from test_gpu_halo import FIELDS, fill_exchange_validate
+    halo_ok = True
+    try:
+        for name, kind in FIELDS:
+            for layer in (0, 1, 2):
+                fill_exchange_validate(dy, [blk], name, kind, layer, dy.field, dy.set_field, dy.exchange)
+    except AssertionError as e:
+        halo_ok = False
+        print("rank", rank, "halo idiom failed:", str(e)[:300], flush=True)
+    ok &= halo_ok
     t = torch.tensor([1 if ok else 0], device="cuda"); dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print("MULTIGPU_CHECK world=%d level=%d steps=%d graph=%d transport=%s exchanges/step=%.0f -> %s" % (world, level, steps, graph, transport, dy.exchange_count() / steps, "BITWISE EQUAL" if t.item() == 1 else "MISMATCH"), flush=True)
+        print("MULTIGPU_CHECK world=%d level=%d steps=%d graph=%d transport=%s exchanges/step=%.0f -> %s" % (world, level, steps, graph, transport, dy.exchange_count() / steps, "BITWISE EQUAL, HALO IDIOM OK" if t.item() == 1 else "MISMATCH"), flush=True)
     dy.close(); d1.close()
     dist.destroy_process_group()
     sys.exit(0 if t.item() == 1 else 1)
