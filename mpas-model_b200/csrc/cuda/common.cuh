@@ -218,7 +218,7 @@ struct MonoWsLayout {
 // from the first edge of the plan's range) need the nc[t] <= ncmax distinct cells cells[t*ncmax ...] (1-based ids);
 // lidx[16*e + j] is the position of advCellsForEdge(j+1, e) in its tile's list.
 struct EdgeTilePlan {
-    int nTiles, ncmax;
+    int nTiles, ncmax, max_stencil;  // max_stencil: the longest advCellsForEdge list in the range
     const int* first;
     const int* nc;
     const int* cells;

@@ -51,15 +51,28 @@ struct PhaseTimer {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending;
 };
 
-struct HostBarrier {
+struct HostBarrier {  // barrier of the per-block host threads of the monotonic transport; abortable: a thread that fails
+                      // before it reaches the barrier must not leave the others blocked forever
     std::mutex m;
     std::condition_variable cv;
     int count = 0, gen = 0, n = 1;
-    void wait() {
+    bool aborted = false;
+    void reset(int nthreads) {
+        std::lock_guard<std::mutex> lk(m);
+        n = nthreads; count = 0; aborted = false;
+    }
+    void abort() {
+        std::lock_guard<std::mutex> lk(m);
+        aborted = true;
+        cv.notify_all();
+    }
+    bool wait() {  // false: aborted
         std::unique_lock<std::mutex> lk(m);
+        if (aborted) return false;
         int g = gen;
         if (++count == n) { count = 0; ++gen; cv.notify_all(); }
-        else cv.wait(lk, [&] { return g != gen; });
+        else cv.wait(lk, [&] { return g != gen || aborted; });
+        return !aborted;
     }
 };
 
@@ -79,6 +92,7 @@ struct Dycore {
     std::vector<cudaEvent_t> event_pool;
     HostBarrier bar;
     std::string err;
+    std::mutex err_mu;
     // captured step graph
     cudaGraphExec_t graph_exec[2] = {nullptr, nullptr};
     long long graph_nodes[2] = {0, 0};

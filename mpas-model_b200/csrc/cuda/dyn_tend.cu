@@ -335,6 +335,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) dt_edge_flux_kernel(DtP p, rea
 // dynamic shared memory: 2 * ncmax * tma_slot(L + 1) reals.
 #define FT_NCMAX 112
 #define FT_TEMAX 64
+#define FT1_NCMAX 88  // one-field form: 88 columns + the per-edge tables = 53 KB per block, 4 blocks per SM
 template <bool RK1>
 __global__ void __launch_bounds__(WPB * 32, 2) dt_edge_flux_tile_kernel(DtP p, EdgeTilePlan tp, real* __restrict__ ft, real* __restrict__ fw, real* __restrict__ ft2) {
     extern __shared__ __align__(16) real s_dyn[];
@@ -450,6 +451,142 @@ __global__ void __launch_bounds__(WPB * 32, 2) dt_edge_flux_tile_kernel(DtP p, E
                 real* o = ft2 + (size_t)eoff + ka;
                 o[0] = dv * (rs_a - rue_a) * (real)0.5 * (t2_a + t1_a);
                 if (vb) o[32] = dv * (rs_b - rue_b) * (real)0.5 * (t2_b + t1_b);
+            }
+        }
+    }
+}
+
+// Second form of the staged kernel: ONE field per launch (FIELD 0: theta_m -> ft [, ft2]; FIELD 1: w -> fw), so a block holds
+// one set of columns (half the shared memory: 4 blocks per SM), and everything an edge needs besides its own operand columns
+// -- the shared-memory offsets of its stencil columns and the two coefficient tables -- is put into shared memory by the whole
+// block BEFORE the wait for the bulk copies, so the latency of those index / coefficient loads hides behind the copy.  In
+// the edge loop a warp then has only its operand loads (ru [, ru_save, theta_m_save of the two cells]) in front of the sums,
+// and it requests those of its next edge before it works on the current one.
+template <int FIELD, bool RK1>
+__global__ void __launch_bounds__(WPB * 32, 4) dt_edge_flux_tile1_kernel(DtP p, EdgeTilePlan tp, real* __restrict__ ft, real* __restrict__ fw, real* __restrict__ ft2) {
+    extern __shared__ __align__(16) real s_dyn[];
+    __shared__ __align__(8) unsigned long long s_bar;
+    __shared__ unsigned short s_base[FT1_NCMAX];
+    __shared__ unsigned short s_o[FT_TEMAX][10];
+    __shared__ real s_cp[FT_TEMAX][10], s_cm[FT_TEMAX][10];
+    __shared__ int s_c1[FT_TEMAX], s_c2[FT_TEMAX];  // cells of the edge; s_c1 = 0: edge not needed (no owned cell) or not a 10-cell stencil
+    const int L = p.L, L1 = L + 1, NL = FIELD ? L1 : L, LS = tma_slot(NL);
+    const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int e0 = tp.first[tile], ne = tp.first[tile + 1] - e0, nc = tp.nc[tile];
+    const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar);
+    if (tid == 0) mbar_init(mbar, (unsigned)nc);
+    __syncthreads();
+    if (tid < nc) {
+        const int c = tp.cells[(size_t)tile * tp.ncmax + tid];
+        const real* g = FIELD ? p.w + (size_t)(c - 1) * L1 : p.theta_m + (size_t)(c - 1) * L;
+        mbar_arrive_expect_tx(mbar, tma_col_bytes(g, NL));
+        unsigned dummy = 0;
+        tma_issue_col((unsigned)__cvta_generic_to_shared(s_dyn) + (unsigned)tid * (unsigned)(LS * sizeof(real)), g, NL, mbar, dummy);
+        s_base[tid] = (unsigned short)(tid * LS + tma_shift(g));
+    }
+    if (tid < ne) {
+        const int iEdge = p.edgeStart + e0 + tid;
+        const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+        const bool need = (cell1 <= p.nCellsSolve || cell2 <= p.nCellsSolve);
+        s_c1[tid] = need ? cell1 : 0;
+        s_c2[tid] = cell2;
+    }
+    __syncthreads();
+    for (int t = tid; t < ne * 10; t += WPB * 32) {
+        const int er = t / 10, j = t - er * 10;
+        const int iEdge = p.edgeStart + e0 + er;
+        const int n = p.nAdvCellsForEdge[iEdge - 1];
+        const bool in = j < n;
+        const real a = in ? p.adv_coefs[IX2(j + 1, iEdge, 15)] : (real)0.0, a3 = in ? p.adv_coefs_3rd[IX2(j + 1, iEdge, 15)] : (real)0.0;
+        s_o[er][j] = s_base[in ? (int)tp.lidx[(size_t)(e0 + er) * 16 + j] : 0];
+        s_cp[er][j] = a + a3;
+        s_cm[er][j] = a - a3;
+        if (j == 0 && n > 10) s_c1[er] = -s_c1[er];  // longer stencil than the tables hold: the warp takes the direct path below
+    }
+    __syncthreads();
+    mbar_wait(mbar, 0);
+    // operands of the first edge of this warp
+    real rue_a = 0, rue_b = 0, rum_a = 0, rum_b = 0, rs_a = 0, rs_b = 0, t1_a = 0, t1_b = 0, t2_a = 0, t2_b = 0;
+    const int ka = lane;  // levels ka and ka + 32 (chunks beyond 64 levels: outer loop below)
+    auto load_ops = [&](int er, int kb) {
+        if (er >= ne) return;
+        const int c1 = s_c1[er];
+        if (c1 <= 0) return;
+        const int iEdge = p.edgeStart + e0 + er;
+        const unsigned eoff = (unsigned)(iEdge - 1) * (unsigned)L;
+        const bool vb = kb + 32 < L;
+        const int bo = vb ? 32 : 0;
+        if (kb < L) {
+            const real* __restrict__ rup = elem_ptr(p.ru + kb, eoff);
+            rue_a = rup[0]; rue_b = rup[bo];
+            if (FIELD) {
+                const int mo = kb > 0 ? -1 : 0;
+                rum_a = rup[mo]; rum_b = rup[bo - 1 + (vb ? 0 : 1 + mo)];
+            } else if (!RK1) {
+                const real* __restrict__ rs = elem_ptr(p.ru_save + kb, eoff);
+                const real* __restrict__ t1 = elem_ptr(p.theta_m_save + kb, (unsigned)(c1 - 1) * (unsigned)L);
+                const real* __restrict__ t2 = elem_ptr(p.theta_m_save + kb, (unsigned)(s_c2[er] - 1) * (unsigned)L);
+                rs_a = rs[0]; rs_b = rs[bo];
+                t1_a = t1[0]; t1_b = t1[bo];
+                t2_a = t2[0]; t2_b = t2[bo];
+            }
+        }
+    };
+    for (int k0 = 0; k0 < L; k0 += 64) {
+        const int kb = k0 + ka;
+        load_ops(warp, kb);
+        for (int er = warp; er < ne; er += WPB) {
+            const real c_rue_a = rue_a, c_rue_b = rue_b, c_rum_a = rum_a, c_rum_b = rum_b;
+            const real c_rs_a = rs_a, c_rs_b = rs_b, c_t1_a = t1_a, c_t1_b = t1_b, c_t2_a = t2_a, c_t2_b = t2_b;
+            load_ops(er + WPB, kb);  // next edge of this warp: in flight while this one is summed
+            const int c1 = s_c1[er];
+            if (c1 == 0 || kb >= L) continue;
+            const int iEdge = p.edgeStart + e0 + er;
+            const unsigned eoff = (unsigned)(iEdge - 1) * (unsigned)L;
+            const bool vb = kb + 32 < L;
+            const int bo = vb ? 32 : 0;
+            if (c1 < 0) continue;  // (handled by the direct kernel launched for such meshes; never on Voronoi meshes with <= 10-cell stencils)
+            real ua, ub;
+            if (FIELD) {
+                ua = p.fzm[kb] * c_rue_a + p.fzp[kb] * c_rum_a;
+                ub = p.fzm[kb + bo] * c_rue_b + p.fzp[kb + bo] * c_rum_b;
+            } else {
+                ua = c_rue_a;
+                ub = c_rue_b;
+            }
+            const real* tab_a = signbit(ua) ? s_cm[er] : s_cp[er];
+            const real* tab_b = signbit(ub) ? s_cm[er] : s_cp[er];
+            const real* col = s_dyn + kb;
+            real f_a = 0.0, f_b = 0.0;
+#pragma unroll
+            for (int j = 0; j < 10; j += FUNR) {
+                real xa[FUNR], xb[FUNR];
+#pragma unroll
+                for (int t = 0; t < FUNR; ++t) {
+                    const real* q = col + s_o[er][j + t];
+                    xa[t] = q[0];
+                    xb[t] = q[bo];
+                }
+#pragma unroll
+                for (int t = 0; t < FUNR; ++t) {
+                    f_a = f_a + tab_a[j + t] * xa[t];
+                    f_b = f_b + tab_b[j + t] * xb[t];
+                }
+            }
+            if (FIELD) {
+                real* o = fw + (size_t)eoff + kb;
+                if (kb > 0) o[0] = ua * f_a;
+                if (vb) o[32] = ub * f_b;
+            } else {
+                real* o = ft + (size_t)eoff + kb;
+                o[0] = ua * f_a;
+                if (vb) o[32] = ub * f_b;
+                if (!RK1) {
+                    const real dv = p.dvEdge[iEdge - 1];
+                    real* o2 = ft2 + (size_t)eoff + kb;
+                    o2[0] = dv * (c_rs_a - c_rue_a) * (real)0.5 * (c_t2_a + c_t1_a);
+                    if (vb) o2[32] = dv * (c_rs_b - c_rue_b) * (real)0.5 * (c_t2_b + c_t1_b);
+                }
             }
         }
     }
@@ -987,14 +1124,30 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     if (!ft) return fail_msg("mpas_b200_compute_dyn_tend_work: cannot allocate the edge-flux workspace (the first call must be outside stream capture)");
     real* fw = ft + nELp;
     real* ft2 = fw + nELp;
-    static const int flux_minb = tune("dt_flux_minb", 6), flux_tile = tune("dt_flux_tile", 0);
+    static const int flux_minb = tune("dt_flux_minb", 6), flux_tile = tune("dt_flux_tile", 2);
     // shared-memory staged stencil (tiles.cu) when the plan exists and two column sets of ncmax cells fit; else direct gathers
     const EdgeTilePlan* tp = nullptr;
     const size_t tile_shm = (size_t)2 * FT_NCMAX * tma_slot(L + 1) * sizeof(real);
     if (flux_tile && 2 * FT_NCMAX * tma_slot(L + 1) < 65536 && p.nEdgesLoop > 0 &&
         ensure_dyn_smem(rk_step == 1 ? (const void*)dt_edge_flux_tile_kernel<true> : (const void*)dt_edge_flux_tile_kernel<false>, tile_shm))
-        tp = edge_tile_plan(p.advCellsForEdge, p.nAdvCellsForEdge, p.edgeStart, p.nEdgesLoop, nCells, FT_NCMAX, FT_TEMAX);
-    if (tp) {
+        tp = edge_tile_plan(p.advCellsForEdge, p.nAdvCellsForEdge, p.edgeStart, p.nEdgesLoop, nCells, flux_tile == 2 ? FT1_NCMAX : FT_NCMAX, FT_TEMAX);
+    if (tp && flux_tile == 2) {
+        const size_t shm1 = (size_t)FT1_NCMAX * tma_slot(L + 1) * sizeof(real);
+        if (!ensure_dyn_smem((const void*)dt_edge_flux_tile1_kernel<0, true>, shm1) || !ensure_dyn_smem((const void*)dt_edge_flux_tile1_kernel<0, false>, shm1) ||
+            !ensure_dyn_smem((const void*)dt_edge_flux_tile1_kernel<1, true>, shm1) || tp->max_stencil > 10)
+            tp = nullptr;
+    }
+    if (tp && flux_tile == 2) {
+        const size_t shm1 = (size_t)FT1_NCMAX * tma_slot(L + 1) * sizeof(real);
+        ktime_begin(rk_step == 1 ? "dt_edge_flux_tile1_kernel<0,true>" : "dt_edge_flux_tile1_kernel<0,false>");
+        if (rk_step == 1) dt_edge_flux_tile1_kernel<0, true><<<tp->nTiles, WPB * 32, shm1, stream()>>>(p, *tp, ft, fw, ft2);
+        else dt_edge_flux_tile1_kernel<0, false><<<tp->nTiles, WPB * 32, shm1, stream()>>>(p, *tp, ft, fw, ft2);
+        ktime_end();
+        ktime_begin("dt_edge_flux_tile1_kernel<1>");
+        dt_edge_flux_tile1_kernel<1, true><<<tp->nTiles, WPB * 32, shm1, stream()>>>(p, *tp, ft, fw, ft2);
+        ktime_end();
+        count_launch(2);
+    } else if (tp) {
         ktime_begin(rk_step == 1 ? "dt_edge_flux_tile_kernel<true>" : "dt_edge_flux_tile_kernel<false>");
         if (rk_step == 1) dt_edge_flux_tile_kernel<true><<<tp->nTiles, WPB * 32, tile_shm, stream()>>>(p, *tp, ft, fw, ft2);
         else dt_edge_flux_tile_kernel<false><<<tp->nTiles, WPB * 32, tile_shm, stream()>>>(p, *tp, ft, fw, ft2);

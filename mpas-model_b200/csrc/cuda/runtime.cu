@@ -5,6 +5,7 @@
 // the *_work entry points with the SAME host addresses it always passed; every entry point maps
 // them to the device mirrors.  Device pointers pass through untouched, so the device-resident
 // dycore driver (dycore.cu) uses the identical entry points.
+#include <atomic>
 #include <cstdio>
 #include <cstring>
 #include <map>
@@ -29,7 +30,7 @@ std::map<uintptr_t, Mirror> g_reg;  // host base address -> mirror
 std::mutex g_mu;
 cudaStream_t g_stream = nullptr;
 bool g_own_stream = false;
-long long g_launches = 0;
+std::atomic<long long> g_launches{0};  // the per-block threads of the monotonic transport count too
 }  // namespace
 
 cudaStream_t stream() {
@@ -44,16 +45,21 @@ void set_stream(cudaStream_t s) {
     g_stream = s;
     g_own_stream = false;
 }
+namespace {
+std::mutex g_err_mu;
+}
 int fail(const char* where, cudaError_t e) {
+    std::lock_guard<std::mutex> lk(g_err_mu);
     g_last_error = std::string(where) + ": " + cudaGetErrorString(e);
     return 1000 + (int)e;
 }
 int fail_msg(const std::string& msg) {
+    std::lock_guard<std::mutex> lk(g_err_mu);
     g_last_error = msg;
     return 1;
 }
-long long launches() { return g_launches; }
-void count_launch(int n) { g_launches += n; }
+long long launches() { return g_launches.load(); }
+void count_launch(int n) { g_launches.fetch_add(n); }
 
 // Library workspace keyed by a device address that identifies the block (an array of that block the routine is handed
 // anyway).  It replaces the reference's per-phase allocate/deallocate (TI:592-626, 1029-1099) for scratch the reference

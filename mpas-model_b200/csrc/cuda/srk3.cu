@@ -249,7 +249,7 @@ int mono_halo(void* ctx, int which, real* array) {
         df.bytes = (size_t)df.inner * (size_t)(d.nC + 1) * sizeof(real);
         b.f["mono_scale_all"] = df;
     }
-    if (threaded) m->bar.wait();
+    if (threaded && !m->bar.wait()) return 1;  // another block's thread failed: do not wait for it
     int rc = 0;
     if (c->iblock == 0) {
         try {
@@ -261,7 +261,8 @@ int mono_halo(void* ctx, int which, real* array) {
             rc = 1;
         }
     }
-    if (threaded) m->bar.wait();
+    if (rc) m->bar.abort();
+    if (threaded && !m->bar.wait()) return 1;
     return rc;
 }
 
@@ -283,7 +284,7 @@ int call_mono(Dycore& m, int ib, real dt, int advance_density) {
 int run_mono_all(Dycore& m, real dt, int advance_density) {
     const int P = (int)m.blocks.size();
     if (P == 1) return call_mono(m, 0, dt, advance_density);
-    m.bar.n = P;
+    m.bar.reset(P);
     m.err.clear();
     std::vector<std::thread> th;
     std::vector<int> rcs(P, 0);
@@ -292,9 +293,11 @@ int run_mono_all(Dycore& m, real dt, int advance_density) {
             try {
                 rcs[ib] = call_mono(m, ib, dt, advance_density);
             } catch (const std::exception& e) {
+                std::lock_guard<std::mutex> lk(m.err_mu);
                 m.err = e.what();
                 rcs[ib] = 1;
             }
+            if (rcs[ib]) m.bar.abort();  // a thread that fails before a barrier releases the others
         });
     for (auto& t : th) t.join();
     if (!m.err.empty()) return fail_msg(m.err);
@@ -488,13 +491,32 @@ int dycore_step(Dycore& m) {
             const long xbefore = m.nExchanges;
             cudaError_t e = cudaStreamBeginCapture(stream(), cudaStreamCaptureModeThreadLocal);
             if (e != cudaSuccess) return fail("cudaStreamBeginCapture", e);
-            const int r = srk3_body(m);
+            // an exception out of the captured body (a missing field or config) must not leave the stream in capture mode:
+            // every later call on it would fail with a capture error that hides the real message
+            int r = 0;
+            std::string what;
+            try {
+                r = srk3_body(m);
+            } catch (const std::exception& ex) {
+                what = ex.what();
+                r = 1;
+            }
             e = cudaStreamEndCapture(stream(), &g);
+            if (!what.empty()) {
+                if (e == cudaSuccess && g) cudaGraphDestroy(g);
+                cudaGetLastError();
+                count_launch(-(int)(launches() - before));
+                m.nExchanges = xbefore;
+                return fail_msg(what);
+            }
             m.graph_nodes[par] = launches() - before;  // kernels / copies recorded, not yet executed
             m.graph_exchanges[par] = m.nExchanges - xbefore;
             count_launch(-(int)m.graph_nodes[par]);
             m.nExchanges = xbefore;
-            if (r) return r;
+            if (r) {
+                if (e == cudaSuccess && g) cudaGraphDestroy(g);
+                return r;
+            }
             if (e != cudaSuccess) return fail("cudaStreamEndCapture", e);
             e = cudaGraphInstantiate(&m.graph_exec[par], g, 0);
             cudaGraphDestroy(g);

@@ -103,6 +103,8 @@ const EdgeTilePlan* edge_tile_plan(const int* d_advCellsForEdge, const int* d_nA
     cudaMemcpy(d + o_nc, ncs.data(), (size_t)nTiles * 4, cudaMemcpyHostToDevice);
     cudaMemcpy(d + o_cells, cells.data(), (size_t)nTiles * ncmax * 4, cudaMemcpyHostToDevice);
     cudaMemcpy(d + o_lidx, lidx.data(), lidx.size(), cudaMemcpyHostToDevice);
+    ps.plan.max_stencil = 0;
+    for (int e = 0; e < nEdgesLoop; ++e) ps.plan.max_stencil = std::max(ps.plan.max_stencil, std::min(std::max(nadv[e], 0), 15));
     ps.plan.nTiles = nTiles;
     ps.plan.ncmax = ncmax;
     ps.plan.first = (const int*)(d + o_first);

@@ -67,6 +67,7 @@ void read_grid_nc(const std::string& path, Mesh& m) {
     auto dim = [&](const char* n) -> int64_t {
         const int id = f.find_dim(n);
         if (id < 0) throw std::runtime_error(std::string("grid file has no dimension ") + n);
+        if (f.dims[id].len > 2147483647LL) throw std::runtime_error(std::string("grid file: dimension ") + n + " exceeds the 32-bit index range of the model");
         return f.dims[id].len;
     };
     const int nC = (int)dim("nCells"), nE = (int)dim("nEdges"), nV = (int)dim("nVertices");
@@ -233,6 +234,23 @@ int read_restart_block(const std::string& path, Block& b) {
     if (f.numrecs < 1) throw std::runtime_error("restart file has no record: " + path);
     Pool& p = b.pool;
     const int index_qv = p.cfg.count("index_qv") ? (int)p.cfg.at("index_qv") : 1;
+    // the file must be of THIS mesh and level count: variables are matched by name only, and a file whose sizes merely
+    // divide evenly would otherwise be read from the wrong offsets
+    {
+        auto flen = [&](const char* n) -> int64_t { const int id = f.find_dim(n); return id < 0 ? -1 : f.dims[id].len; };
+        auto maxid = [&](FieldLoc loc) { int mx = 0; for (int g : ids_of(b.mesh, loc)) mx = std::max(mx, g); return (int64_t)mx; };
+        const struct { const char* dim; FieldLoc loc; } chk[3] = {{"nCells", LOC_CELL}, {"nEdges", LOC_EDGE}, {"nVertices", LOC_VERTEX}};
+        for (auto& c : chk) {
+            const int64_t n = flen(c.dim);
+            if (n >= 0 && n < maxid(c.loc))
+                throw std::runtime_error(std::string("restart file ") + path + ": dimension " + c.dim + " = " + std::to_string(n) +
+                                         " is smaller than a global ID of this block (" + std::to_string(maxid(c.loc)) + "): file of another mesh");
+        }
+        const int64_t nl = flen("nVertLevels");
+        if (nl >= 0 && p.cfg.count("nVertLevels") && nl != (int64_t)p.cfg.at("nVertLevels"))
+            throw std::runtime_error("restart file " + path + ": nVertLevels = " + std::to_string(nl) + " but the block has " +
+                                     std::to_string((int64_t)p.cfg.at("nVertLevels")));
+    }
     int nfilled = 0;
     std::vector<double> col;
     for (auto& kv : p.f) {
@@ -266,6 +284,12 @@ int read_restart_block(const std::string& path, Block& b) {
             if (!v.record) continue;
             const int64_t inner = fl.inner();
             if (v.count_per_record % inner) throw std::runtime_error("restart: shape mismatch for " + kv.first);
+            {
+                int mx = 0;
+                for (int i = 0; i < nloc; ++i) mx = std::max(mx, ids[i]);
+                if ((int64_t)mx * inner > v.count_per_record)
+                    throw std::runtime_error("restart: variable " + kv.first + " of " + path + " is too small for this mesh");
+            }
             int i = 0;
             while (i < nloc) {
                 int j = i + 1;

@@ -267,6 +267,9 @@ void read_converted(const File& f, const Var& v, int64_t rec, int64_t start, int
     const int sz = type_size(v.type);
     const int64_t CH = 1 << 16;
     std::vector<unsigned char> raw((size_t)(CH * sz)), host((size_t)(CH * sz));
+    // a range outside the variable would silently read the neighbouring variable / record (write_converted checks the same)
+    if (start < 0 || count < 0 || start + count > v.count_per_record) die("read outside variable " + v.name + " in " + f.path);
+    if (rec < 0 || (v.record && rec >= f.numrecs) || (!v.record && rec != 0)) die("no such record of variable " + v.name + " in " + f.path);
     if (fseeko(f.fp, var_offset(f, v, rec, start), SEEK_SET) != 0) die("seek failed in " + f.path);
     for (int64_t done = 0; done < count; done += CH) {
         const int64_t n = std::min(CH, count - done);

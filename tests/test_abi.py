@@ -76,3 +76,30 @@ def test_argument_lists_match_reference_dummy_argument_counts():
     assert count("MPAS_DIVDAMP_ARGS") == 15
     # TI:4481-4499 has 128 dummies; + the 10 host-associated module scratch arrays (TI:35-43) + num_scalars, moist_start/end are already dummies
     assert count("MPAS_DYNTEND_ARGS") >= 128 + 10
+
+
+def test_fortran_shim_interfaces_are_generated_from_the_headers_and_cover_every_work_routine():
+    """shim/mpas_atm_b200_interfaces.inc (the bind(C) interface blocks the Fortran host compiles) must be exactly what
+    tools/gen_shim.py makes of include/mpas_b200.h + mpas_b200_args.h, and name all 14 work routines plus the
+    halo-exchange entry points, each with as many dummies as the C prototype has parameters."""
+    import subprocess
+    import sys
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "gen_shim.py"), "--check"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    inc = open(os.path.join(ROOT, "shim", "mpas_atm_b200_interfaces.inc")).read()
+    hdr = open(os.path.join(ROOT, "include", "mpas_b200.h")).read()
+    work = re.findall(r"int\s+(mpas_b200_\w+)\((MPAS_\w+_ARGS)\);", hdr)
+    assert len(work) == 14
+    src = open(os.path.join(ROOT, "include", "mpas_b200_args.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S).replace("\\\n", " ")
+    macros = dict(re.findall(r"#define\s+(MPAS_\w+_ARGS)\s+(.*)", src))
+    for name, macro in work:
+        m = re.search(r"function %s\((.*?)\)\s*&\s*\n\s*bind\(C, name='%s'\)" % (name, name), inc, flags=re.S)
+        assert m, name
+        dummies = [a for a in re.sub(r"[&\s]", "", m.group(1)).split(",") if a]
+        body = macros[macro].replace("MPAS_RANGE_ARGS", macros["MPAS_RANGE_ARGS"])
+        assert len(dummies) == len([a for a in body.split(",") if a.strip()]), name
+    for name in ("mpas_b200_halo_register_lists", "mpas_b200_exch_halo_field2d", "mpas_b200_exch_halo_field3d", "mpas_b200_halo_comm_init"):
+        assert "bind(C, name='%s')" % name in inc
+    shim = open(os.path.join(ROOT, "shim", "mpas_atm_b200_shim.F")).read()
+    assert '#include "mpas_atm_b200_interfaces.inc"' in shim

@@ -210,3 +210,18 @@ def test_gpu_restart_run_is_bit_identical_to_the_uninterrupted_run(tmp_path):
         for n in RESTART:
             nown = int(b.cfg()[SOLVE[b.info(n)[1]]])
             assert np.array_equal(m.field(ib, n)[:nown], ref.field(ib, n)[:nown]), n
+
+
+def test_restart_of_another_mesh_or_level_count_is_refused(tmp_path):
+    """variables are matched by name: a file whose sizes merely divide evenly must not be read from the wrong offsets"""
+    case3, blocks3 = common.make_case(3, 1, nVertLevels=8, num_scalars=1)
+    p = tmp_path / "restart_l3.nc"
+    case3.create_restart(p, ["u@1", "theta_m@1", "w@1"])
+    blocks3[0].write_restart(p, ["u@1", "theta_m@1", "w@1"])
+    assert blocks3[0].read_restart(p) == 3
+    case4, blocks4 = common.make_case(4, 1, nVertLevels=8, num_scalars=1)
+    with pytest.raises(RuntimeError, match="another mesh|too small"):
+        blocks4[0].read_restart(p)
+    case3b, blocks3b = common.make_case(3, 1, nVertLevels=4, num_scalars=1)
+    with pytest.raises(RuntimeError, match="nVertLevels"):
+        blocks3b[0].read_restart(p)
