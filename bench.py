@@ -103,6 +103,9 @@ def parse():
     ap.add_argument("--levels", type=int, default=55)
     ap.add_argument("--scalars", type=int, default=None, help="num_scalars (default: 1 = qv at level >= 9 as configs[3], 4 = qv + 3 tracers below as configs[1])")
     ap.add_argument("--lloyd", type=int, default=5)
+    ap.add_argument("--case", default="jw", choices=["jw", "supercell"],
+                    help="supercell = BASELINE.json configs[2]: doubly periodic planar hex mesh, 2 km, --nx x --nx cells, qv qc qr transported (an extra line, not the metric)")
+    ap.add_argument("--nx", type=int, default=200, help="supercell: cells per side")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--ktime", action="store_true", help="also print per-kernel CUDA-event times of one eager step to stderr")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -110,6 +113,14 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=30.0, help="target CPU time of the bounded cpu_baseline sample")
     ap.add_argument("--precision", default=None, choices=["double", "single"], help="single = the PRECISION=single build (dtype f32), an extra line")
     a = ap.parse_args()
+    if a.case == "supercell":  # "level" 7 = the requested --nx, every level below halves the side (the bounded CPU sample)
+        a.auto_level = False
+        a.level = 7
+        a.auto_scalars = False
+        a.scalars = a.scalars or 3
+        if "--levels" not in sys.argv:
+            a.levels = 40
+        return a
     a.auto_level = a.level is None
     if a.level is None:
         a.level = DEFAULT_LEVEL
@@ -119,7 +130,36 @@ def parse():
     return a
 
 
-def workload_name(level, levels, ns, note=""):
+def side(a, level):
+    return max(8, (a.nx >> (7 - level)) & ~1)
+
+
+def n_cells(a, level):
+    return side(a, level) ** 2 if a.case == "supercell" else LEVEL_CELLS[level]
+
+
+def host_case(a, level):
+    import common
+    if a.case == "supercell":
+        return common.host.HostCase(0, planar=(side(a, level), side(a, level), 2000.0), sfc=True)
+    return common.host.HostCase(level, lloyd_iters=a.lloyd, sfc=True)
+
+
+def model_config(a, level):
+    import common
+    if a.case == "supercell":
+        return dict(config_dt=12.0, config_len_disp=2000.0)  # 2 km -> 12 s
+    return common.level_config(level)
+
+
+def init_case(a):
+    return 5 if a.case == "supercell" else 2
+
+
+def workload_name(level, levels, ns, note="", a=None):
+    if a is not None and a.case == "supercell":
+        return "idealised supercell, doubly periodic planar hex mesh %d x %d cells, 2 km, %d levels, %d moist scalars (qv, qc, qr) transported, physics off%s" % (
+            side(a, level), side(a, level), levels, ns, note)
     tr = "qv only" if ns == 1 else "qv + %d passive tracers" % (ns - 1)
     return "JW baroclinic wave, icosahedral level %d (x1.%d, %s km), %d levels, %d scalars (%s), dycore only%s" % (
         level, LEVEL_CELLS[level], LEVEL_KM.get(level, 0), levels, ns, tr, note)
@@ -128,8 +168,8 @@ def workload_name(level, levels, ns, note=""):
 def config_dict(a, level, ns, note=""):
     """identical in the b200 and the reference arm for the same command line"""
     import common
-    return {"workload": workload_name(level, a.levels, ns, note), "nCells": LEVEL_CELLS[level], "nVertLevels": a.levels, "num_scalars": ns,
-            "config_dt_s": common.level_config(level)["config_dt"],
+    return {"workload": workload_name(level, a.levels, ns, note, a), "nCells": n_cells(a, level), "nVertLevels": a.levels, "num_scalars": ns,
+            "config_dt_s": model_config(a, level)["config_dt"],
             "partition": "METIS k-way, %d blocks" % a.gpus if a.gpus > 1 else "single block", "l2_policy": "no flush needed: one step streams far more than the 126 MB L2"}
 
 
@@ -163,10 +203,11 @@ def cpu_model(a, level, ns, threads):
     """the CPU restatement (oracle perf build: -O3 -march=native, OpenMP) of the same case on `level`, initialised"""
     import common
     common.oracle(perf=True).oracle_set_num_threads(threads)
-    case = common.host.HostCase(level, lloyd_iters=a.lloyd, sfc=True)
-    block = case.build_block(0, nVertLevels=a.levels, init_case=2, num_scalars=ns, full_fields=True)
-    set_tracers(block, ns)
-    m = common.OracleModel([block], common.level_config(level), perf=True)
+    case = host_case(a, level)
+    block = case.build_block(0, nVertLevels=a.levels, init_case=init_case(a), num_scalars=ns, full_fields=True)
+    if a.case == "jw":
+        set_tracers(block, ns)
+    m = common.OracleModel([block], model_config(a, level), perf=True)
     m.init()
     return case, block, m
 
@@ -179,7 +220,7 @@ def cpu_sample_level(a, ns, threads, nsteps, budget_s, max_level):
     t0 = time.perf_counter()
     m.step(1)
     per_cell = (time.perf_counter() - t0) / case.nCells
-    while level < max_level and per_cell * LEVEL_CELLS[level + 1] * nsteps <= budget_s:
+    while level < max_level and per_cell * n_cells(a, level + 1) * nsteps <= budget_s:
         level += 1
     return level
 
@@ -206,10 +247,10 @@ def run_reference(a):
     t0 = time.perf_counter()
     m.step(a.steps)
     dt = time.perf_counter() - t0
-    scale = case.nCells / float(LEVEL_CELLS[a.level])
+    scale = case.nCells / float(n_cells(a, a.level))
     value = a.steps / dt * scale
     sample = "%d steps of the same case on icosahedral level %d (%d of %d cells) in %.1f s on %d OpenMP threads, steps/s scaled by the cell ratio %.5f" % (
-        a.steps, level, case.nCells, LEVEL_CELLS[a.level], dt, threads, scale)
+        a.steps, level, case.nCells, n_cells(a, a.level), dt, threads, scale)
     line = {
         "impl": "reference", "metric": "dycore timesteps/sec", "value": value, "unit": "steps/s", "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": 1000.0 / value, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -257,14 +298,15 @@ def run_b200(a):
     level, ns, note = a.level, a.scalars, ""
     while True:
         t_setup = time.perf_counter()
-        case = host.HostCase(level, lloyd_iters=a.lloyd, sfc=True)
+        case = host_case(a, level)
         if N > 1:
             case.partition(N, "metis")
         # "lean": the work / tendency arrays (all zero at start, 83 % of a block's words) get no host storage, their device mirrors
         # are created zero-filled from the metadata
-        block = case.build_block(rank, nVertLevels=a.levels, init_case=2, num_scalars=ns, full_fields="lean")
-        set_tracers(block, ns)
-        cfg = common.level_config(level)
+        block = case.build_block(rank, nVertLevels=a.levels, init_case=init_case(a), num_scalars=ns, full_fields="lean")
+        if a.case == "jw":
+            set_tracers(block, ns)
+        cfg = model_config(a, level)
         dy, err = None, ""
         try:
             dy = host.Dycore([block], cfg, rank=rank, nranks=N, device=local_rank)
@@ -391,8 +433,8 @@ def run_b200(a):
         tr = json.load(open(os.path.join(ROOT, "profiles", "r02_dram_traffic.json")))
         if tr.get("_kernel_source_sha") != kernel_source_sha():
             roofline["traffic_note"] = "committed ncu capture is of other kernel sources (%s, now %s): not used" % (tr.get("_kernel_source_sha"), kernel_source_sha())
-        elif N == 1 and a.levels == int(tr["_nVertLevels"]) and ns == int(tr["_num_scalars"]) and not host.SINGLE:
-            scale = LEVEL_CELLS[level] / float(tr["_nCells"])
+        elif N == 1 and a.case == "jw" and a.levels == int(tr["_nVertLevels"]) and ns == int(tr["_num_scalars"]) and not host.SINGLE:
+            scale = n_cells(a, level) / float(tr["_nCells"])
             roofline["traffic"] = tr[dom]["dram_GB_per_step"] / phases[dom]["calls_per_step"] * scale
             roofline["traffic_unit"] = "GB per call (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_dram_traffic.csv%s)" % (
                 "" if scale == 1.0 else ", captured on %d cells and scaled by the cell ratio" % int(tr["_nCells"]))
@@ -449,10 +491,10 @@ def run_b200(a):
         t0 = time.perf_counter()
         m.step(nst)
         dt_ = time.perf_counter() - t0
-        scale = ccase.nCells / float(LEVEL_CELLS[level])
+        scale = ccase.nCells / float(n_cells(a, level))
         cpu = {"value": nst / dt_ * scale, "unit": "steps/s", "cores": threads, "kind": "port",
                "sample": "%d steps (after 1 warm-up step) of the same case on icosahedral level %d (%d of %d cells) in %.1f s, scaled by the cell ratio; "
-                         "C++/OpenMP restatement, -O3 -march=native; the Fortran reference cannot be built on this box" % (nst, lvl, ccase.nCells, LEVEL_CELLS[level], dt_),
+                         "C++/OpenMP restatement, -O3 -march=native; the Fortran reference cannot be built on this box" % (nst, lvl, ccase.nCells, n_cells(a, level), dt_),
                "phases_ms_on_sample_mesh": phase_ms(m, nst)}
 
     if rank == 0:

@@ -15,6 +15,9 @@ int mpas_host_set_num_threads(int n); /* OpenMP threads of the harness; n < 1 = 
 
 /* ---- Layer 0: host harness (mesh, partition, JW initial state) ---- */
 void* mpas_host_case_create(int level, int lloyd_iters, int sfc);
+/* doubly periodic planar mesh of nx x ny regular hexagons, spacing dc (m); build blocks with init_case 4 (squall line) / 5 (supercell),
+ * src/core_init_atmosphere/mpas_init_atm_cases.F:1313-1895 */
+void* mpas_host_case_create_planar(int nx, int ny, double dc, int sfc);
 void mpas_host_case_destroy(void* h);
 int mpas_host_case_dims(void* h, int* nCells, int* nEdges, int* nVertices, int* maxEdges, int* maxEdges2);
 int mpas_host_case_permutation(void* h, int kind, int* out);

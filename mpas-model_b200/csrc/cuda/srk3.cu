@@ -124,9 +124,9 @@ int call_dyn_tend(DBlock& b, int rk_step, real dt) {
         b.R("pressure_p"), b.Ropt("pressure_base"), b.R("zz"), b.R("zxu"), b.R("cqu"), b.R("h_divergence"), b.R("kdiff"), b.R("edgesOnCell_sign"),
         b.R("edgesOnVertex_sign"), b.R("rw_save"), b.R("ru_save"), b.R("theta_m@1"), b.R("exner"), b.R("rho_p_save"), b.R("scalars@2"), b.R("tend_u_euler"),
         b.R("tend_w_euler"), b.R("tend_theta_euler"), b.Ropt("deriv_two"), b.I("cellsOnEdge"), b.I("verticesOnEdge"), b.I("edgesOnCell"), b.I("edgesOnEdge"),
-        b.I("cellsOnCell"), b.I("edgesOnVertex"), b.I("nEdgesOnCell"), b.I("nEdgesOnEdge"), b.Ropt("latCell"), b.Ropt("latEdge"), b.Ropt("angleEdge"), nullptr,
-        nullptr, b.I("advCellsForEdge"), b.I("nAdvCellsForEdge"), b.R("adv_coefs"), b.R("adv_coefs_3rd"), b.R("rdzu"), b.R("rdzw"), b.R("fzm"), b.R("fzp"),
-        nullptr, nullptr, (real)b.c("cf1"), (real)b.c("cf2"), (real)b.c("cf3"), (real)b.c("sphere_radius"), nullptr, nullptr, b.R("defc_a"), b.R("defc_b"),
+        b.I("cellsOnCell"), b.I("edgesOnVertex"), b.I("nEdgesOnCell"), b.I("nEdgesOnEdge"), b.Ropt("latCell"), b.Ropt("latEdge"), b.Ropt("angleEdge"), b.Ropt("u_init"),
+        b.Ropt("v_init"), b.I("advCellsForEdge"), b.I("nAdvCellsForEdge"), b.R("adv_coefs"), b.R("adv_coefs_3rd"), b.R("rdzu"), b.R("rdzw"), b.R("fzm"), b.R("fzp"),
+        b.Ropt("qv_init"), b.Ropt("t_init"), (real)b.c("cf1"), (real)b.c("cf2"), (real)b.c("cf3"), (real)b.c("sphere_radius"), nullptr, nullptr, b.R("defc_a"), b.R("defc_b"),
         nullptr, nullptr, (real)b.c("config_coef_3rd_order", 0.25), (real)b.c("config_smagorinsky_coef", 0.125), (int)b.c("config_mix_full", 1),
         (int)b.c("config_horiz_mixing", 1), (real)b.c("config_del4u_div_factor", 10.0), (real)b.c("config_h_mom_eddy_visc2", 0.0),
         (real)b.c("config_v_mom_eddy_visc2", 0.0), (real)b.c("config_h_theta_eddy_visc2", 0.0), (real)b.c("config_v_theta_eddy_visc2", 0.0),

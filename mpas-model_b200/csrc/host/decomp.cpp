@@ -231,6 +231,7 @@ void build_block(const Mesh& G, const std::vector<int>& part, int nBlocks, int i
     Mesh& m = out.mesh;
     m = Mesh();
     m.maxEdges = mE; m.maxEdges2 = mE2; m.on_a_sphere = G.on_a_sphere; m.sphere_radius = G.sphere_radius;
+    m.planar_xmax = G.planar_xmax; m.planar_ymax = G.planar_ymax;
     const int nc = (int)cells.size(), ne = (int)edges.size(), nv = (int)verts.size();
     m.alloc(nc, ne, nv);
     m.nCellsSolve = cellEnd[0]; m.nEdgesSolve = edgeEnd[0]; m.nVerticesSolve = vertEnd[0];

@@ -68,6 +68,23 @@ void* mpas_host_case_create(int level, int lloyd_iters, int sfc) {
     API_CATCH(nullptr)
 }
 
+// Doubly periodic planar mesh of nx x ny regular hexagons with spacing dc (m): the idealised squall-line / supercell cases
+// (BASELINE.json configs[2]); build blocks with init_case 4 (squall line) or 5 (supercell).
+void* mpas_host_case_create_planar(int nx, int ny, double dc, int sfc) {
+    API_TRY
+    auto* hc = new HostCase();
+    Mesh gen;
+    make_planar_hex_mesh(nx, ny, dc, gen);
+    if (sfc) {
+        sfc_reorder(gen, hc->global, hc->perm);
+        hc->has_perm = true;
+    } else {
+        hc->global = gen;
+    }
+    return hc;
+    API_CATCH(nullptr)
+}
+
 void mpas_host_case_destroy(void* h) { delete (HostCase*)h; }
 
 int mpas_host_case_dims(void* h, int* nCells, int* nEdges, int* nVertices, int* maxEdges, int* maxEdges2) {
@@ -144,8 +161,16 @@ int mpas_host_case_build_block(void* h, int iBlock, int nVertLevels, int init_ca
     lap("mesh_to_pool");
     init_advection_and_deformation(blk->mesh, p);
     lap("init_advection_and_deformation");
-    init_case_jw(blk->mesh, hc->cfg, p);
-    lap("init_case_jw");
+    if (init_case == 4 || init_case == 5) {
+        if (blk->mesh.on_a_sphere) throw std::runtime_error("init_case 4 / 5 (squall line / supercell) need a planar mesh (mpas_host_case_create_planar)");
+        hc->cfg.config_zd = 12000.0;  // no upper damping layer in the idealised convective cases (mpas_init_atm_cases.F:1483-1484)
+        hc->cfg.config_xnutr = 0.0;
+        init_case_squall_line(blk->mesh, hc->cfg, p);
+    } else {
+        if (!blk->mesh.on_a_sphere) throw std::runtime_error("the Jablonowski-Williamson cases need a spherical mesh");
+        init_case_jw(blk->mesh, hc->cfg, p);
+    }
+    lap("init_case");
     core_init_derived(blk->mesh, hc->cfg, p);
     lap("core_init_derived");
     init_reconstruct(blk->mesh, p);

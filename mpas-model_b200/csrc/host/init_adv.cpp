@@ -151,25 +151,39 @@ void init_advection_and_deformation(const Mesh& m, Pool& p) {
             if (cell_list[i] > nC) do_the_cell = false;
         if (!do_the_cell) continue;
 
-        // ---------------- deriv_two (:129-390), sphere branch
-        for (int i = 1; i <= n; ++i) {
-            int c = cell_list[i] - 1;
-            xc[i] = m.xCell[c] / R; yc[i] = m.yCell[c] / R; zc[i] = m.zCell[c] / R;
-        }
-        double theta_abs;
-        if (zc[1] == 1.0) theta_abs = pii / 2.;
-        else theta_abs = pii / 2. - sphere_angle(xc[1], yc[1], zc[1], xc[2], yc[2], zc[2], 0.0, 0.0, 1.0);
-        for (int i = 1; i <= n - 1; ++i) {
-            int ip2 = i + 2;
-            if (ip2 > n) ip2 = 2;
-            thetav[i] = sphere_angle(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1], xc[ip2], yc[ip2], zc[ip2]);
-            dl_sphere[i] = R * arc_length(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1]);
-        }
-        thetat[1] = theta_abs;
-        for (int i = 2; i <= n - 1; ++i) thetat[i] = thetat[i - 1] + thetav[i - 1];
-        for (int i = 1; i <= n - 1; ++i) {
-            xp[i] = std::cos(thetat[i]) * dl_sphere[i];
-            yp[i] = std::sin(thetat[i]) * dl_sphere[i];
+        // ---------------- deriv_two (:129-390)
+        double theta_abs = 0.0;
+        double angle_2d[26];
+        if (m.on_a_sphere) {
+            for (int i = 1; i <= n; ++i) {
+                int c = cell_list[i] - 1;
+                xc[i] = m.xCell[c] / R; yc[i] = m.yCell[c] / R; zc[i] = m.zCell[c] / R;
+            }
+            if (zc[1] == 1.0) theta_abs = pii / 2.;
+            else theta_abs = pii / 2. - sphere_angle(xc[1], yc[1], zc[1], xc[2], yc[2], zc[2], 0.0, 0.0, 1.0);
+            for (int i = 1; i <= n - 1; ++i) {
+                int ip2 = i + 2;
+                if (ip2 > n) ip2 = 2;
+                thetav[i] = sphere_angle(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1], xc[ip2], yc[ip2], zc[ip2]);
+                dl_sphere[i] = R * arc_length(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1]);
+            }
+            thetat[1] = theta_abs;
+            for (int i = 2; i <= n - 1; ++i) thetat[i] = thetat[i - 1] + thetav[i - 1];
+            for (int i = 1; i <= n - 1; ++i) {
+                xp[i] = std::cos(thetat[i]) * dl_sphere[i];
+                yp[i] = std::sin(thetat[i]) * dl_sphere[i];
+            }
+        } else {  // on an x-y plane (:184-200): neighbour positions from angleEdge / dcEdge, safe across periodic boundaries
+            bool edges_ok = true;
+            for (int i = 1; i <= n - 1; ++i) {
+                const int iEdge = EOC(i, iCell);
+                if (iEdge > nE) { edges_ok = false; break; }
+                angle_2d[i] = m.angleEdge[iEdge - 1];
+                if (iCell != m.cellsOnEdge[2 * (iEdge - 1)]) angle_2d[i] = angle_2d[i] - pii;
+                xp[i] = m.dcEdge[iEdge - 1] * std::cos(angle_2d[i]);
+                yp[i] = m.dcEdge[iEdge - 1] * std::sin(angle_2d[i]);
+            }
+            if (!edges_ok) continue;
         }
         int ma = n - 1;
         for (int i = 0; i < 25; ++i)
@@ -189,12 +203,17 @@ void init_advection_and_deformation(const Mesh& m, Pool& p) {
         for (int i = 1; i <= nEoC; ++i) {
             int iEdge = EOC(i, iCell);
             if (iEdge > nE) continue;
-            int v1 = m.verticesOnEdge[2 * (iEdge - 1)] - 1, v2 = m.verticesOnEdge[2 * (iEdge - 1) + 1] - 1;
-            double xec, yec, zec;
-            arc_bisect(m.xVertex[v1] / R, m.yVertex[v1] / R, m.zVertex[v1] / R, m.xVertex[v2] / R, m.yVertex[v2] / R,
-                       m.zVertex[v2] / R, xec, yec, zec);
-            double thetae = sphere_angle(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1], xec, yec, zec);
-            thetae = thetae + thetat[i];
+            double thetae;
+            if (m.on_a_sphere) {
+                int v1 = m.verticesOnEdge[2 * (iEdge - 1)] - 1, v2 = m.verticesOnEdge[2 * (iEdge - 1) + 1] - 1;
+                double xec, yec, zec;
+                arc_bisect(m.xVertex[v1] / R, m.yVertex[v1] / R, m.zVertex[v1] / R, m.xVertex[v2] / R, m.yVertex[v2] / R,
+                           m.zVertex[v2] / R, xec, yec, zec);
+                thetae = sphere_angle(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1], xec, yec, zec);
+                thetae = thetae + thetat[i];
+            } else {
+                thetae = angle_2d[i];  // :358-362
+            }
             double cos2t = std::cos(thetae), sin2t = std::sin(thetae);
             double costsint = cos2t * sin2t;
             cos2t = cos2t * cos2t;
@@ -205,28 +224,43 @@ void init_advection_and_deformation(const Mesh& m, Pool& p) {
                     2. * cos2t * bmatrix[3][j - 1] + 2. * costsint * bmatrix[4][j - 1] + 2. * sin2t * bmatrix[5][j - 1];
         }
 
-        // ---------------- deformation weights (:821-933), sphere branch
-        xc[1] = m.xCell[iCell - 1] / R; yc[1] = m.yCell[iCell - 1] / R; zc[1] = m.zCell[iCell - 1] / R;
+        // ---------------- deformation weights (:821-933)
         bool verts_ok = true;
-        for (int i = 2; i <= n; ++i) {
-            int iv = VOC(i - 1, iCell);
-            if (iv > m.nVertices) { verts_ok = false; break; }
-            xc[i] = m.xVertex[iv - 1] / R; yc[i] = m.yVertex[iv - 1] / R; zc[i] = m.zVertex[iv - 1] / R;
-        }
+        for (int i = 2; i <= n; ++i)
+            if (VOC(i - 1, iCell) > m.nVertices) verts_ok = false;
         if (!verts_ok) continue;
-        if (zc[1] == 1.0) theta_abs = pii / 2.;
-        else theta_abs = pii / 2. - sphere_angle(xc[1], yc[1], zc[1], xc[2], yc[2], zc[2], 0.0, 0.0, 1.0);
-        for (int i = 1; i <= n - 1; ++i) {
-            int ip2 = i + 2;
-            if (ip2 > n) ip2 = 2;
-            thetav[i] = sphere_angle(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1], xc[ip2], yc[ip2], zc[ip2]);
-            dl_sphere[i] = R * arc_length(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1]);
-        }
-        thetat[1] = 0.;
-        for (int i = 2; i <= n - 1; ++i) thetat[i] = thetat[i - 1] + thetav[i - 1];
-        for (int i = 1; i <= n - 1; ++i) {
-            xp[i] = std::cos(thetat[i]) * dl_sphere[i];
-            yp[i] = std::sin(thetat[i]) * dl_sphere[i];
+        if (m.on_a_sphere) {
+            xc[1] = m.xCell[iCell - 1] / R; yc[1] = m.yCell[iCell - 1] / R; zc[1] = m.zCell[iCell - 1] / R;
+            for (int i = 2; i <= n; ++i) {
+                int iv = VOC(i - 1, iCell);
+                xc[i] = m.xVertex[iv - 1] / R; yc[i] = m.yVertex[iv - 1] / R; zc[i] = m.zVertex[iv - 1] / R;
+            }
+            if (zc[1] == 1.0) theta_abs = pii / 2.;
+            else theta_abs = pii / 2. - sphere_angle(xc[1], yc[1], zc[1], xc[2], yc[2], zc[2], 0.0, 0.0, 1.0);
+            for (int i = 1; i <= n - 1; ++i) {
+                int ip2 = i + 2;
+                if (ip2 > n) ip2 = 2;
+                thetav[i] = sphere_angle(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1], xc[ip2], yc[ip2], zc[ip2]);
+                dl_sphere[i] = R * arc_length(xc[1], yc[1], zc[1], xc[i + 1], yc[i + 1], zc[i + 1]);
+            }
+            thetat[1] = 0.;
+            for (int i = 2; i <= n - 1; ++i) thetat[i] = thetat[i - 1] + thetav[i - 1];
+            for (int i = 1; i <= n - 1; ++i) {
+                xp[i] = std::cos(thetat[i]) * dl_sphere[i];
+                yp[i] = std::sin(thetat[i]) * dl_sphere[i];
+            }
+        } else {
+            // on an x-y plane, literally as the reference has it (:889-901): xp(1) is the CELL CENTRE and xp(2..n) the vertices in raw
+            // mesh coordinates, while the loops below use xp(1..n-1) as the polygon.  The reference's own planar cases run with
+            // config_horiz_mixing = '2d_fixed' (the supercell here too), which never reads defc_a / defc_b.
+            theta_abs = 0.0;
+            xp[1] = m.xCell[iCell - 1];
+            yp[1] = m.yCell[iCell - 1];
+            for (int i = 2; i <= n; ++i) {
+                int iv = VOC(i - 1, iCell);
+                xp[i] = m.xVertex[iv - 1];
+                yp[i] = m.yVertex[iv - 1];
+            }
         }
         thetat[1] = theta_abs;
         for (int i = 2; i <= n - 1; ++i) {

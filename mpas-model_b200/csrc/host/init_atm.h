@@ -22,7 +22,7 @@ struct Constants {
 
 struct InitConfig {
     int nVertLevels = 26;
-    int init_case = 2;          // 1 steady JW, 2 JW + perturbation, 3 normal-mode
+    int init_case = 2;          // 1 steady JW, 2 JW + perturbation, 3 normal-mode; 4 squall line, 5 supercell (planar mesh)
     int num_scalars = 1;        // qv + passive tracers
     int theta_adv_order = 3;
     double coef_3rd_order = 0.25;
@@ -42,6 +42,9 @@ void init_advection_and_deformation(const Mesh& m, Pool& p);
 
 // init_atm_case_jw (mpas_init_atm_cases.F:367-1160) on all local cells/edges of m
 void init_case_jw(const Mesh& m, const InitConfig& cfg, Pool& p);
+
+// init_atm_case_squall_line (mpas_init_atm_cases.F:1313-1895): test case 4 squall line, 5 supercell, planar periodic mesh
+void init_case_squall_line(const Mesh& m, const InitConfig& cfg, Pool& p);
 
 // core-init derived arrays (mpas_atm_core.F:311-360, 456-463, 927-1288)
 void core_init_derived(const Mesh& m, const InitConfig& cfg, Pool& p);

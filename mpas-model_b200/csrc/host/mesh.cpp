@@ -280,7 +280,12 @@ void compute_mesh_metrics(Mesh& m) {
         }
         m.areaCell[c] = a;
     }
-    // TRiSK weights
+    compute_trisk_weights(m);
+}
+
+// edgesOnEdge / weightsOnEdge from edgesOnCell, verticesOnCell, kiteAreasOnVertex, areaCell, dvEdge, dcEdge (any geometry)
+void compute_trisk_weights(Mesh& m) {
+    const int nc = m.nCells, ne = m.nEdges, nv = m.nVertices, mE = m.maxEdges, mE2 = m.maxEdges2;
 #pragma omp parallel for schedule(static)
     for (int e = 0; e < ne; ++e) {
         int k = 0;
@@ -321,6 +326,69 @@ void compute_mesh_metrics(Mesh& m) {
         m.nEdgesOnEdge[e] = std::min(k, mE2);
     }
     m.nEdgesOnEdge[ne] = 0;
+}
+
+// ---------------------------------------------------------------------------------------
+// Doubly periodic planar mesh of regular hexagons (the reference's idealised supercell / squall-line meshes are made by
+// its external periodic_hex tool; BASELINE.json configs[2]): nx x ny cells, cell spacing dc, rows offset by dc/2, ny even.
+// Connectivity comes from the same triangulation builder as the sphere (two CCW triangles per cell: (p, E, NE) and
+// (p, NE, NW)), so every ordering convention (CCW slots, vertex i precedes edge i, vertex 2 of an edge on the left of its
+// normal) is the sphere's; the metrics are analytic.  on_a_sphere = false, fEdge = fVertex = 0 (set by the initial case).
+// ---------------------------------------------------------------------------------------
+void make_planar_hex_mesh(int nx, int ny, double dc, Mesh& m) {
+    if (nx < 4 || ny < 4 || (ny % 2) != 0) throw std::runtime_error("planar hex mesh: need nx >= 4, ny >= 4, ny even");
+    const double h = dc * std::sqrt(3.0) / 2.0, Lx = nx * dc, Ly = ny * h;
+    const int nc = nx * ny;
+    auto id = [&](int i, int j) { return ((j + ny) % ny) * nx + ((i + nx) % nx); };
+    std::vector<V3> pts(nc);
+    std::vector<Tri> tris;
+    tris.reserve((size_t)2 * nc);
+    for (int j = 0; j < ny; ++j)
+        for (int i = 0; i < nx; ++i) {
+            pts[id(i, j)] = V3{dc * (i + 0.5 * (j % 2)), h * j, 0.0};
+            const int odd = j % 2;
+            const int pE = id(i + 1, j), pNE = id(i + odd, j + 1), pNW = id(i + odd - 1, j + 1), pp = id(i, j);
+            Tri t1, t2;
+            t1.v[0] = pp; t1.v[1] = pE; t1.v[2] = pNE;
+            t2.v[0] = pp; t2.v[1] = pNE; t2.v[2] = pNW;
+            tris.push_back(t1);
+            tris.push_back(t2);
+        }
+    build_from_triangulation(pts, tris, m);
+    m.on_a_sphere = false;
+    m.sphere_radius = 1.0;
+    m.planar_xmax = 0.0;
+    m.planar_ymax = 0.0;
+    const int ne = m.nEdges, nv = m.nVertices;
+    auto wrap = [](double d, double Lp) { return d - Lp * std::floor(d / Lp + 0.5); };
+    for (int c = 0; c < nc; ++c) {
+        m.zCell[c] = 0.0; m.latCell[c] = 0.0; m.lonCell[c] = 0.0;
+        m.areaCell[c] = dc * dc * std::sqrt(3.0) / 2.0;
+        m.meshDensity[c] = 1.0;
+        m.planar_xmax = std::max(m.planar_xmax, m.xCell[c]);
+        m.planar_ymax = std::max(m.planar_ymax, m.yCell[c]);
+    }
+    for (int v = 0; v < nv; ++v) {
+        const int a = m.cellsOnVertex[3 * v] - 1, b = m.cellsOnVertex[3 * v + 1] - 1, c = m.cellsOnVertex[3 * v + 2] - 1;
+        const double bx = wrap(m.xCell[b] - m.xCell[a], Lx), by = wrap(m.yCell[b] - m.yCell[a], Ly);
+        const double cx = wrap(m.xCell[c] - m.xCell[a], Lx), cy = wrap(m.yCell[c] - m.yCell[a], Ly);
+        m.xVertex[v] = m.xCell[a] + (bx + cx) / 3.0;  // equilateral triangle: centroid = circumcentre
+        m.yVertex[v] = m.yCell[a] + (by + cy) / 3.0;
+        m.zVertex[v] = 0.0; m.latVertex[v] = 0.0; m.lonVertex[v] = 0.0;
+        m.areaTriangle[v] = dc * dc * std::sqrt(3.0) / 4.0;
+        for (int j = 0; j < 3; ++j) m.kiteAreasOnVertex[3 * v + j] = m.areaTriangle[v] / 3.0;
+    }
+    for (int e = 0; e < ne; ++e) {
+        const int c1 = m.cellsOnEdge[2 * e] - 1, c2 = m.cellsOnEdge[2 * e + 1] - 1;
+        const double dx = wrap(m.xCell[c2] - m.xCell[c1], Lx), dy = wrap(m.yCell[c2] - m.yCell[c1], Ly);
+        m.xEdge[e] = m.xCell[c1] + 0.5 * dx;
+        m.yEdge[e] = m.yCell[c1] + 0.5 * dy;
+        m.zEdge[e] = 0.0; m.latEdge[e] = 0.0; m.lonEdge[e] = 0.0;
+        m.dcEdge[e] = std::sqrt(dx * dx + dy * dy);
+        m.dvEdge[e] = dc / std::sqrt(3.0);
+        m.angleEdge[e] = std::atan2(dy, dx);  // angle of the normal (cell 1 -> cell 2) from the x axis
+    }
+    compute_trisk_weights(m);
 }
 
 // ---------------------------------------------------------------------------------------
@@ -438,6 +506,7 @@ void apply_permutation(const Mesh& in, const MeshPermutation& p, Mesh& out) {
     out = Mesh();
     out.maxEdges = mE; out.maxEdges2 = mE2; out.vertexDegree = in.vertexDegree;
     out.on_a_sphere = in.on_a_sphere; out.sphere_radius = in.sphere_radius;
+    out.planar_xmax = in.planar_xmax; out.planar_ymax = in.planar_ymax;
     out.alloc(nc, ne, nv);
     out.nCellsSolve = in.nCellsSolve; out.nEdgesSolve = in.nEdgesSolve; out.nVerticesSolve = in.nVerticesSolve;
     out.nCellsHalo = in.nCellsHalo; out.nEdgesHalo = in.nEdgesHalo; out.nVerticesHalo = in.nVerticesHalo;

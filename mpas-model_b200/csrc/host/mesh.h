@@ -17,6 +17,7 @@ struct Mesh {
     int maxEdges = 6, maxEdges2 = 12, vertexDegree = 3;
     bool on_a_sphere = true;
     double sphere_radius = 1.0;
+    double planar_xmax = 0.0, planar_ymax = 0.0;  // planar meshes: GLOBAL maxima of xCell / yCell (the initial cases centre their bubble on them)
     // halo layer ends: cells: nCellsHalo[h] = count incl. halo layers <= h (h=0 owned)
     std::vector<int> nCellsHalo, nEdgesHalo, nVerticesHalo;
 
@@ -50,6 +51,10 @@ struct Mesh {
 // lloyd_iters > 0 applies fixed-topology centroidal relaxation.
 void make_icosahedral_mesh(int level, Mesh& m, int lloyd_iters = 0);
 
+
+// Doubly periodic planar mesh of nx x ny regular hexagons, cell spacing dc (m); ny even
+void make_planar_hex_mesh(int nx, int ny, double dc, Mesh& m);
+void compute_trisk_weights(Mesh& m);
 
 // Recompute all metric arrays (lat/lon, dc, dv, angle, areas, kites, TRiSK weights)
 // from positions + connectivity.

@@ -32,6 +32,8 @@ def hostlib():
         _hostlib.mpas_host_last_error.restype = C.c_char_p
         _hostlib.mpas_host_case_create.restype = C.c_void_p
         _hostlib.mpas_host_case_create.argtypes = [C.c_int, C.c_int, C.c_int]
+        _hostlib.mpas_host_case_create_planar.restype = C.c_void_p
+        _hostlib.mpas_host_case_create_planar.argtypes = [C.c_int, C.c_int, C.c_double, C.c_int]
         _hostlib.mpas_host_case_destroy.argtypes = [C.c_void_p]
         _hostlib.mpas_host_case_dims.argtypes = [C.c_void_p] + [C.POINTER(C.c_int)] * 5
         _hostlib.mpas_host_case_permutation.argtypes = [C.c_void_p, C.c_int, C.c_void_p]
@@ -225,9 +227,12 @@ class Block:
 class HostCase:
     """Global icosahedral mesh + partition + per-block JW initial state."""
 
-    def __init__(self, level, lloyd_iters=0, sfc=True, grid_file=None):
-        """level: icosahedral subdivision level of the built-in mesh generator; grid_file: read an MPAS grid.nc instead"""
-        if grid_file is not None:
+    def __init__(self, level, lloyd_iters=0, sfc=True, grid_file=None, planar=None):
+        """level: icosahedral subdivision level of the built-in mesh generator; grid_file: read an MPAS grid.nc instead;
+        planar = (nx, ny, dc): doubly periodic planar mesh of regular hexagons (squall line / supercell: build_block init_case 4 / 5)"""
+        if planar is not None:
+            self.h = hostlib().mpas_host_case_create_planar(int(planar[0]), int(planar[1]), float(planar[2]), 1 if sfc else 0)
+        elif grid_file is not None:
             self.h = hostlib().mpas_host_case_create_from_grid(str(grid_file).encode(), 1 if sfc else 0)
         else:
             self.h = hostlib().mpas_host_case_create(level, lloyd_iters, 1 if sfc else 0)
