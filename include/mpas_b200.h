@@ -60,6 +60,7 @@ int mpas_b200_rk_integration_setup(MPAS_RKSETUP_ARGS);                     /* TI
 int mpas_b200_compute_moist_coefficients(MPAS_MOIST_ARGS);                 /* TI:1862 */
 int mpas_b200_rk_dynamics_substep_finish(MPAS_SUBSTEPFINISH_ARGS);         /* TI:5993 */
 int mpas_b200_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS);             /* TI:5825 */
+int mpas_b200_compute_output_diagnostics(MPAS_OUTPUTDIAG_ARGS);           /* mpas_atm_core.F:753 */
 int mpas_b200_reconstruct_2d(MPAS_RECONSTRUCT_ARGS);                       /* mpas_vector_reconstruction.F:195, called TI:1594 */
 
 /* ---- Layer 1: halo exchange for a host that keeps its own blocks and exchange lists (the bodies of

@@ -213,6 +213,13 @@ typedef int (*mpas_halo_fn)(void *ctx, int which, mpas_real *array);
         int moist_end, MPAS_RANGE_ARGS, const int *cellsOnEdge, const mpas_real *scalars,          \
         mpas_real *cqw, mpas_real *cqu, mpas_real *qtot
 
+/* atm_compute_output_diagnostics, src/core_atmosphere/mpas_atm_core.F:753-802 (pool arguments resolved to arrays) */
+#define MPAS_OUTPUTDIAG_ARGS                                                                       \
+    int nVertLevels, int num_scalars, int index_qv, int nCells, const mpas_real *theta_m,          \
+        const mpas_real *rho_zz, const mpas_real *scalars, const mpas_real *zz,                    \
+        const mpas_real *pressure_base, const mpas_real *pressure_p, mpas_real *theta,             \
+        mpas_real *rho, mpas_real *pressure
+
 /* atm_rk_dynamics_substep_finish, TI:5993-6081 */
 #define MPAS_SUBSTEPFINISH_ARGS                                                                    \
     int nVertLevels, int nCells, int nEdges, int dynamics_substep, int dynamics_split,             \

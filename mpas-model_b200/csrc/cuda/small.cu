@@ -481,3 +481,31 @@ extern "C" int mpas_b200_init_coupled_diagnostics(MPAS_INITCOUPLED_ARGS) {
     KCHECK("icd_cell2_kernel");
     return 0;
 }
+
+// ---- atm_compute_output_diagnostics (src/core_atmosphere/mpas_atm_core.F:753-802): theta, rho, pressure for the history stream
+namespace {
+struct OutDiagP {
+    KMagic km;
+    int L, ns, iqv, nCells;
+    const real *theta_m, *rho_zz, *scalars, *zz, *pressure_base, *pressure_p;
+    real *theta, *rho, *pressure;
+};
+__global__ void __launch_bounds__(256) output_diag_kernel(OutDiagP p) {
+    const int L = p.L;
+    FLAT_KC(p.nCells, L);
+    const size_t ic = IX2(k, _c0 + 1, L);
+    p.theta[ic] = p.theta_m[ic] / ((real)1. + MPAS_RVORD * p.scalars[ic * (size_t)p.ns + (size_t)(p.iqv - 1)]);
+    p.rho[ic] = p.rho_zz[ic] * p.zz[ic];
+    p.pressure[ic] = p.pressure_base[ic] + p.pressure_p[ic];
+}
+}  // namespace
+
+extern "C" int mpas_b200_compute_output_diagnostics(MPAS_OUTPUTDIAG_ARGS) {
+    OutDiagP p;
+    p.L = nVertLevels; p.km.set(nVertLevels); p.ns = num_scalars; p.iqv = index_qv; p.nCells = nCells;
+    p.theta_m = X(theta_m); p.rho_zz = X(rho_zz); p.scalars = X(scalars); p.zz = X(zz); p.pressure_base = X(pressure_base); p.pressure_p = X(pressure_p);
+    p.theta = X(theta); p.rho = X(rho); p.pressure = X(pressure);
+    KLAUNCH(output_diag_kernel, (long long)nCells * nVertLevels, 256, p);
+    KCHECK("output_diag_kernel");
+    return 0;
+}

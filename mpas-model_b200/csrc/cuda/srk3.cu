@@ -585,6 +585,11 @@ int dycore_call(Dycore& m, const std::string& rt, const double* q, int nq) {
         else if (rt == "substep_finish") { need(2); CK(call_substep_finish(b, (int)q[0], (int)q[1])); }
         else if (rt == "init_coupled") CK(call_init_coupled(b));
         else if (rt == "reconstruct") CK(call_reconstruct(b));
+        else if (rt == "output_diagnostics") {  // time level 1 after a step, as atm_core_run calls it (mpas_atm_core.F:717)
+            Dims d = dims(b);
+            CK(mpas_b200_compute_output_diagnostics(d.L, d.ns, (int)b.c("index_qv", 1), d.nC, b.R("theta_m@1"), b.R("rho_zz@1"), b.R("scalars@1"), b.R("zz"),
+                                                    b.R("pressure_base"), b.R("pressure_p"), b.R("theta"), b.R("rho"), b.R("pressure")));
+        }
         else return fail_msg("dycore_call: unknown routine " + rt);
     }
     return 0;

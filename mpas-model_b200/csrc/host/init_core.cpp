@@ -221,7 +221,7 @@ void allocate_dycore_fields(const Mesh& m, const InitConfig& cfg, Pool& p, int f
                           "divergence", "ke", "pv_cell", "qtot", "dpdz", "delsq_theta", "delsq_w", "delsq_divergence", "tend_rtheta_adv",
                           "rthdynten", "tend_rho_physics", "tend_rtheta_physics", "tend_theta", "tend_theta_euler", "tend_rho",
                           "rt_diabatic_tend", "scalar_old", "scalar_new", "s_max", "s_min", "rho_zz_int", "uReconstructX", "uReconstructY",
-                          "uReconstructZ", "uReconstructZonal", "uReconstructMeridional"}) C(n);
+                          "uReconstructZ", "uReconstructZonal", "uReconstructMeridional", "pressure"}) C(n);
     for (const char* n : {"vorticity", "pv_vertex", "ke_vertex", "delsq_vorticity"}) V(n);
     add("scalars@2", LOC_CELL, {ns, L, nC});
     add("scalars_tend", LOC_CELL, {ns, L, nC});

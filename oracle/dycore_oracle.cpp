@@ -1283,4 +1283,16 @@ int oracle_advance_scalars_mono_work(MPAS_MONO_ARGS) {
     return 0;
 }
 
+// ------------------------------------------------------------------ src/core_atmosphere/mpas_atm_core.F:753-802
+int oracle_compute_output_diagnostics(MPAS_OUTPUTDIAG_ARGS) {
+    const int L = nVertLevels, ns = num_scalars;
+    for (int iCell = 1; iCell <= nCells; ++iCell)
+        for (int k = 1; k <= L; ++k) {
+            theta[IX2(k, iCell, L)] = theta_m[IX2(k, iCell, L)] / (1. + rvord * scalars[IX3(index_qv, k, iCell, ns, L)]);
+            rho[IX2(k, iCell, L)] = rho_zz[IX2(k, iCell, L)] * zz[IX2(k, iCell, L)];
+            pressure[IX2(k, iCell, L)] = pressure_base[IX2(k, iCell, L)] + pressure_p[IX2(k, iCell, L)];
+        }
+    return 0;
+}
+
 }  // extern "C"

@@ -25,6 +25,7 @@
 typedef mpas_real real;
 
 extern "C" {
+int oracle_compute_output_diagnostics(MPAS_OUTPUTDIAG_ARGS);
 int oracle_rk_integration_setup(MPAS_RKSETUP_ARGS);
 int oracle_compute_moist_coefficients(MPAS_MOIST_ARGS);
 int oracle_compute_vert_imp_coefs_work(MPAS_VERTIMP_ARGS);
@@ -612,6 +613,10 @@ int oracle_model_call(void* h, const char* routine, const double* q, int nq) {
                                                   b.R("theta_m@1"), b.R("theta_m@2"), b.R("rho_zz@1"), b.R("rho_zz@2"));
             }
             else if (rt == "reconstruct") call_reconstruct(b);
+            else if (rt == "output_diagnostics") {  // time level 1 after a step, as atm_core_run calls it (mpas_atm_core.F:717)
+                oracle_compute_output_diagnostics(d.L, d.ns, (int)b.c("index_qv", 1), d.nC, b.R("theta_m@1"), b.R("rho_zz@1"), b.R("scalars@1"), b.R("zz"),
+                                                  b.R("pressure_base"), b.R("pressure_p"), b.R("theta"), b.R("rho"), b.R("pressure"));
+            }
             else if (rt == "init_coupled") {
                 oracle_init_coupled_diagnostics(d.L, d.mE, d.ns, (int)b.c("index_qv", 1), d.nC, d.nE, RANGES, b.I("cellsOnEdge"), b.I("nEdgesOnCell"), b.I("edgesOnCell"),
                                                 b.R("edgesOnCell_sign"), b.R("theta_m@1"), b.R("theta"), b.R("rho_zz@1"), b.R("rho"), b.R("rho_p"), b.R("rho_base"),

@@ -63,3 +63,59 @@ def test_full_size_conservation_monotonicity_and_graph_replay():
     e.step(6)
     for n in STATE:
         assert np.array_equal(e.field(0, n), m.field(0, n)), n
+
+
+DIAG = ["ru", "rw", "rho_p", "rtheta_p", "exner", "pressure_p", "rho_edge", "pv_edge", "v", "ke", "divergence", "vorticity", "tend_u", "tend_w", "tend_theta",
+        "tend_rho", "ruAvg", "wwAvg", "kdiff", "h_divergence", "uReconstructX", "uReconstructY", "uReconstructZ", "uReconstructZonal", "uReconstructMeridional"]
+# against the oracle with libm pow (the reference's arithmetic) the residual fields carry the last-place noise of exner
+# amplified (BASELINE.md section 4 "deviations"); against the correctly rounded pow everything is 1e-12
+RESIDUAL = {"w@1", "rw", "tend_w", "tend_rho", "tend_theta", "tend_u", "wwAvg", "h_divergence", "divergence"}
+
+
+def _worst(gpu, ora, names):
+    out = {}
+    for n in names:
+        g, o = gpu.field(0, n), ora.field(0, n)
+        assert np.isfinite(g).all(), n
+        out[n] = common.rel_l2(g, o)
+    return out
+
+
+def test_benched_config_60km_L55_4_scalars_matches_oracle_after_1_and_10_steps():
+    """BASELINE.json configs[1] -- the level-7 workload bench.py --level 7 --scalars 4 times -- GPU against the CPU oracle on the
+    identical initial state: every STATE and DIAG field within 1e-12 relative L2 after 1 and after 10 steps (oracle with the
+    correctly rounded x**rcv, as on the device); against libm's pow the non-residual fields still meet 1e-12 after 10 steps."""
+    blocks = _blocks()
+    cfg = common.level_config(LEVEL)
+    gpu = common.GpuModel(blocks, cfg)
+    gpu.set_option("graph", 1)
+    common.oracle_set_option("cr_pow", 1)
+    try:
+        ora = common.OracleModel(blocks, cfg)
+        gpu.init(); ora.init()
+        gpu.step(1); ora.step(1)
+        w1 = _worst(gpu, ora, STATE + DIAG)
+        assert max(w1.values()) <= 1e-12, sorted(w1.items(), key=lambda kv: -kv[1])[:4]
+        gpu.step(9); ora.step(9)
+        w10 = _worst(gpu, ora, STATE + DIAG)
+        assert max(w10.values()) <= 1e-12, sorted(w10.items(), key=lambda kv: -kv[1])[:4]
+        print("60 km L55: worst rel L2 after 1 step %.2e (%s), after 10 steps %.2e (%s)" % (
+            max(w1.values()), max(w1, key=w1.get), max(w10.values()), max(w10, key=w10.get)))
+    finally:
+        common.oracle_set_option("cr_pow", 0)
+
+
+def test_30km_one_step_matches_oracle():
+    """icosahedral level 8 (655362 cells, 30 km), 55 levels: one step, all fields 1e-12 (cr_pow oracle)"""
+    case, blocks = common.make_case(8, 1, nVertLevels=L, num_scalars=1, lloyd=5)
+    cfg = common.level_config(8)
+    gpu = common.GpuModel(blocks, cfg)
+    common.oracle_set_option("cr_pow", 1)
+    try:
+        ora = common.OracleModel(blocks, cfg)
+        gpu.init(); ora.init()
+        gpu.step(1); ora.step(1)
+        w1 = _worst(gpu, ora, STATE + DIAG)
+        assert max(w1.values()) <= 1e-12, sorted(w1.items(), key=lambda kv: -kv[1])[:4]
+    finally:
+        common.oracle_set_option("cr_pow", 0)

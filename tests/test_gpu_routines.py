@@ -82,6 +82,7 @@ CASES = [
     ("substep_finish", lambda c: (2, 3)),
     ("substep_finish", lambda c: (3, 3)),
     ("rk_setup", lambda c: ()),
+    ("output_diagnostics", lambda c: ()),
 ]
 
 

@@ -127,7 +127,12 @@ def test_supercell_gpu_matches_oracle_after_1_and_10_steps(nblocks):
                     g, o = gpu.field(ib, n), ora.field(ib, n)
                     loc = b.info(n)[1]
                     nown = int(b.cfg()[{1: "nCellsSolve", 2: "nEdgesSolve", 3: "nVerticesSolve"}[loc]])
-                    e = common.rel_l2(g[:nown], o[:nown])
+                    if n in ("vorticity", "pv_edge", "divergence"):
+                        # f = 0 and the sheared flow is (nearly) irrotational and non-divergent: these fields are round-off-sized
+                        # residuals (1e-15 ... 1e-7 1/s); measured against the velocity gradient scale max|u| / dc instead
+                        e = float(np.abs(g[:nown] - o[:nown]).max()) / (15.0 / DC)
+                    else:
+                        e = common.rel_l2(g[:nown], o[:nown])
                     assert np.isfinite(g[:nown]).all() and e <= 1e-12, (nstep, ib, n, e)
         assert gpu.exchange_count() == ora.exchange_count()
     finally:
