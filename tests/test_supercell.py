@@ -122,18 +122,31 @@ def test_supercell_gpu_matches_oracle_after_1_and_10_steps(nblocks):
         gpu.init(); ora.init()
         for nstep in (1, 9):
             gpu.step(nstep); ora.step(nstep)
+            # norms over the owned elements of ALL blocks (what a one-block run measures): a block far from the bubble holds
+            # nothing but round-off in its tendencies, a per-block relative error would be noise over noise
+            num, den, dmax = {}, {}, {}
             for ib, b in enumerate(blocks):
                 for n in STATE + DIAG:
                     g, o = gpu.field(ib, n), ora.field(ib, n)
                     loc = b.info(n)[1]
                     nown = int(b.cfg()[{1: "nCellsSolve", 2: "nEdgesSolve", 3: "nVerticesSolve"}[loc]])
-                    if n in ("vorticity", "pv_edge", "divergence"):
-                        # f = 0 and the sheared flow is (nearly) irrotational and non-divergent: these fields are round-off-sized
-                        # residuals (1e-15 ... 1e-7 1/s); measured against the velocity gradient scale max|u| / dc instead
-                        e = float(np.abs(g[:nown] - o[:nown]).max()) / (15.0 / DC)
-                    else:
-                        e = common.rel_l2(g[:nown], o[:nown])
-                    assert np.isfinite(g[:nown]).all() and e <= 1e-12, (nstep, ib, n, e)
-        assert gpu.exchange_count() == ora.exchange_count()
+                    assert np.isfinite(g[:nown]).all(), (nstep, ib, n)
+                    num[n] = num.get(n, 0.0) + float(((g[:nown] - o[:nown]) ** 2).sum())
+                    den[n] = den.get(n, 0.0) + float((o[:nown] ** 2).sum())
+                    dmax[n] = max(dmax.get(n, 0.0), float(np.abs(g[:nown] - o[:nown]).max()))
+            for n in STATE + DIAG:
+                if n in ("vorticity", "pv_edge", "divergence"):
+                    # f = 0 and the sheared flow is (nearly) irrotational and non-divergent: these fields are round-off-sized
+                    # residuals (1e-15 ... 1e-7 1/s); measured against the velocity gradient scale max|u| / dc instead
+                    e = dmax[n] / (15.0 / DC)
+                else:
+                    e = np.sqrt(num[n] / den[n]) if den[n] > 0 else np.sqrt(num[n])
+                # tendencies / vertical velocity: small residuals of the hydrostatic balance of a convectively unstable column --
+                # the last-place difference of exner (pow_rcv) grows to a few 1e-12 within 10 steps
+                tol = 1e-11 if n in ("tend_u", "tend_w", "tend_theta", "tend_rho", "w@1", "rw", "wwAvg", "h_divergence") else 1e-12
+                assert e <= tol, (nstep, n, e)
+        # the reference sequence, except that the all-scalars monotonic transport sends the limiter scale factors of all
+        # scalars in ONE exchange where the reference's loop over scalars posts one each (TI:4098)
+        assert ora.exchange_count() - gpu.exchange_count() == (10 * (NS - 1) if nblocks > 1 else 0)
     finally:
         common.oracle_set_option("cr_pow", 0)
