@@ -158,6 +158,8 @@ void dycore_p2p_teardown(Dycore& m) {
     if (pp.seq_recv) cudaFree(pp.seq_recv);
     if (pp.h_timeout) cudaFreeHost(pp.h_timeout);
     if (pp.ticket) cudaFree(pp.ticket);
+    if (pp.d_timeout_dev) cudaFree(pp.d_timeout_dev);
+    pp.d_timeout_dev = nullptr;
     pp.win = nullptr; pp.seq_send = pp.seq_recv = nullptr; pp.d_timeout = pp.h_timeout = nullptr; pp.ticket = nullptr;
     pp.on = false;
 }
@@ -204,7 +206,8 @@ int dycore_p2p_setup(Dycore& m) {
     if (ok) ok = cudaMemsetAsync(pp.win, 0, wbytes, stream()) == cudaSuccess;
     if (ok) ok = cudaIpcGetMemHandle(&mine, pp.win) == cudaSuccess;
     if (ok) ok = cudaMalloc(&pp.seq_send, m.nranks * sizeof(unsigned long long)) == cudaSuccess && cudaMalloc(&pp.seq_recv, m.nranks * sizeof(unsigned long long)) == cudaSuccess &&
-                 cudaMalloc(&pp.ticket, sizeof(unsigned)) == cudaSuccess && cudaHostAlloc(&pp.h_timeout, sizeof(int), cudaHostAllocMapped) == cudaSuccess;
+                 cudaMalloc(&pp.ticket, sizeof(unsigned)) == cudaSuccess && cudaMalloc(&pp.d_timeout_dev, sizeof(int)) == cudaSuccess &&
+                 cudaHostAlloc(&pp.h_timeout, sizeof(int), cudaHostAllocMapped) == cudaSuccess;
     if (ok) {
         *pp.h_timeout = 0;
         ok = cudaHostGetDevicePointer(&pp.d_timeout, pp.h_timeout, 0) == cudaSuccess;
@@ -215,6 +218,7 @@ int dycore_p2p_setup(Dycore& m) {
         cudaMemsetAsync(pp.seq_send, 0, m.nranks * sizeof(unsigned long long), stream());
         cudaMemsetAsync(pp.seq_recv, 0, m.nranks * sizeof(unsigned long long), stream());
         if (pp.ticket) cudaMemsetAsync(pp.ticket, 0, sizeof(unsigned), stream());
+        cudaMemsetAsync(pp.d_timeout_dev, 0, sizeof(int), stream());
     }
     cudaGetLastError();
     // every rank's handle to every rank (a failed rank still takes part, with a zero handle)

@@ -90,11 +90,14 @@ __global__ void __launch_bounds__(256) halo_pack_p2p_kernel(P2PItems it, P2PSide
         real* dst = tab.slot[s] + (size_t)(m & 1ULL) * (size_t)tab.cap;
         dst[(size_t)(it.pos[i][e] - tab.off[s]) + j] = it.array[i][(size_t)(it.idx[i][e] - 1) * inner + j];
     }
-    __threadfence_system();  // the peer stores of this thread are performed before the message number is published
+    // One system-scope fence per BLOCK, not per thread: a fence.sys waits for the thread's peer stores to be acknowledged across
+    // NVLink, and hundreds of thousands of them made a 5 MB exchange cost 1 ms (NCCL: 40 us).  The block barrier orders every
+    // thread's stores before thread 0 (CTA scope), whose fence is cumulative: they are performed system-wide before its ticket.
     if (SIGNAL) {
         __shared__ unsigned s_last;
         __syncthreads();
         if (threadIdx.x == 0) {
+            __threadfence_system();
             const unsigned k = atomicAdd(ticket, 1u);
             s_last = (k == gridDim.x - 1) ? 1u : 0u;
             if (s_last) *ticket = 0u;  // every other block has taken its ticket: ready for the next exchange
@@ -117,7 +120,7 @@ __global__ void halo_signal_p2p_kernel(P2PSideTab snd, P2PSideTab rcv, unsigned 
 // *timeout_flag -- host-mapped memory the library checks wherever it synchronises -- and the block does NOT scatter the
 // stale window contents.
 __global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(P2PItems it, P2PSideTab tab, const unsigned long long* __restrict__ seq_recv, volatile int* timeout_flag,
-                                                              unsigned long long timeout_ns) {
+                                                              volatile int* timeout_dev, unsigned long long timeout_ns) {
     __shared__ int s_fail;
     if (threadIdx.x == 0) s_fail = 0;
     __syncthreads();
@@ -126,7 +129,10 @@ __global__ void __launch_bounds__(256) halo_unpack_p2p_kernel(P2PItems it, P2PSi
         if (ld_acquire_sys(tab.flag[threadIdx.x]) < want) {
             const unsigned long long t0 = global_timer_ns();
             while (ld_acquire_sys(tab.flag[threadIdx.x]) < want) {
-                if (*timeout_flag || global_timer_ns() - t0 > timeout_ns) {
+                // the spin loop polls the DEVICE copy of the flag: the host-mapped word is a PCIe read, and thousands of spinning
+                // threads polling it turned a 20 us exchange into 300 us
+                if (*timeout_dev || global_timer_ns() - t0 > timeout_ns) {
+                    *timeout_dev = 1;
                     *timeout_flag = 1;
                     __threadfence_system();
                     s_fail = 1;
@@ -325,7 +331,7 @@ int halo_signal_p2p(const P2PSideTab& snd, const P2PSideTab& rcv, const P2P& pp)
 
 int halo_unpack_p2p(HaloPlan* p, const P2PSideTab& rcv, const P2P& pp) {
     return p2p_for_chunks(p, p->recv, [&](const P2PItems& it) {
-        halo_unpack_p2p_kernel<<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, rcv, pp.seq_recv, pp.d_timeout, pp.timeout_ns);
+        halo_unpack_p2p_kernel<<<cdiv(it.start[it.n], 256), 256, 0, stream()>>>(it, rcv, pp.seq_recv, pp.d_timeout, pp.d_timeout_dev, pp.timeout_ns);
         count_launch();
     });
 }

@@ -98,6 +98,7 @@ struct P2P {
     unsigned long long *seq_send = nullptr, *seq_recv = nullptr;  // device, nranks each
     int* h_timeout = nullptr;     // pinned host word, mapped: raised by a wait that gave up (that block then skipped its scatter)
     int* d_timeout = nullptr;     // the device alias of h_timeout
+    int* d_timeout_dev = nullptr; // device-memory copy the spin loops poll (a host-mapped word would be a PCIe read per poll)
     unsigned* ticket = nullptr;   // device: block ticket of the pack kernel (the last block publishes the message numbers)
     unsigned long long timeout_ns = 60000000000ULL;  // MPAS_B200_TUNE_p2p_timeout_s (wall time, %globaltimer)
     static size_t flag_bytes(int nranks) { return ((size_t)nranks * 8 + 255) & ~(size_t)255; }
