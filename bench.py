@@ -267,6 +267,7 @@ def run_reference(a):
 E2E_FIELDS = ["u@1", "w@1", "theta_m@1", "rho_zz@1", "scalars@1", "ru", "rw", "rho_p", "rtheta_p", "exner", "pressure_p", "rho_edge", "pv_edge", "v", "ke",
               "divergence", "vorticity"]  # the restart set the step reads at a step boundary (Registry.xml restart stream)
 CHECKSUM_FIELDS = ["u@1", "w@1", "theta_m@1", "rho_zz@1", "scalars@1"]
+NS_DEPENDENT = ("atm_advance_scalars", "atm_advance_scalars_mono", "atm_rk_integration_setup", "atm_compute_moist_coefficients")
 
 
 def run_b200(a):
@@ -433,13 +434,15 @@ def run_b200(a):
         tr = json.load(open(os.path.join(ROOT, "profiles", "r02_dram_traffic.json")))
         if tr.get("_kernel_source_sha") != kernel_source_sha():
             roofline["traffic_note"] = "committed ncu capture is of other kernel sources (%s, now %s): not used" % (tr.get("_kernel_source_sha"), kernel_source_sha())
-        elif N == 1 and a.case == "jw" and a.levels == int(tr["_nVertLevels"]) and ns == int(tr["_num_scalars"]) and not host.SINGLE:
+        elif N == 1 and a.case == "jw" and a.levels == int(tr["_nVertLevels"]) and not host.SINGLE and (
+                ns == int(tr["_num_scalars"]) or dom not in NS_DEPENDENT):  # the dynamics routines move the same bytes for any num_scalars
             scale = n_cells(a, level) / float(tr["_nCells"])
             roofline["traffic"] = tr[dom]["dram_GB_per_step"] / phases[dom]["calls_per_step"] * scale
             roofline["traffic_unit"] = "GB per call (ncu dram__bytes_read.sum + dram__bytes_write.sum, profiles/r02_dram_traffic.csv%s)" % (
                 "" if scale == 1.0 else ", captured on %d cells and scaled by the cell ratio" % int(tr["_nCells"]))
             roofline["algorithmic_GB_per_call"] = phases[dom]["algorithmic_GB_per_call"]
-            roofline["whole_step_traffic_GB"] = tr["_whole_step"]["dram_GB_per_step"] * scale
+            if ns == int(tr["_num_scalars"]):
+                roofline["whole_step_traffic_GB"] = tr["_whole_step"]["dram_GB_per_step"] * scale
         else:
             roofline["traffic_note"] = "the committed ncu capture is 1 GPU, %s levels, %s scalars, f64" % (tr["_nVertLevels"], tr["_num_scalars"])
     except Exception as e:

@@ -153,3 +153,46 @@ def test_recover_rk3_pow_within_last_place(state):
     for ib in range(len(blocks)):
         for n in ("exner", "pressure_p"):
             gpu.set_field(ib, n, ora.field(ib, n))
+
+
+def test_routines_bit_exact_beyond_one_64_level_chunk():
+    """nVertLevels = 70: the second 64-level chunk of every warp-per-column kernel (k0 += 64 loops, the n > 64 tail of the column
+    staging, the non-preloaded Rayleigh operands of acoustic_cell) at routine level, bit for bit against the oracle."""
+    case, blocks = common.make_case(3, 2, nVertLevels=70, num_scalars=2)
+    for b in blocks:
+        s = b.field("scalars@1")
+        s[:-1, :, 1] = (np.sin(2 * b.field("latCell")) ** 2)[:-1, None]
+    cfg = common.level_config(3)
+    ora = common.OracleModel(blocks, cfg)
+    ora.init()
+    ora.step(2)
+    dts = cfg["config_dt"] / 6
+    ora.call("rk_setup"); ora.call("moist"); ora.call("vert_imp_coefs", dts)
+    ora.call("dyn_tend", 1, cfg["config_dt"]); ora.call("smlstep")
+    ora.call("acoustic", dts, 1); ora.call("divdamp", dts)
+    gpu = common.GpuModel(blocks, cfg, diet=False)
+    for routine, p in (("acoustic", (dts, 2)), ("divdamp", (dts,)), ("recover", (dts, 1, 1)), ("solve_diagnostics", (2, cfg["config_dt"], 1)),
+                       ("vert_imp_coefs", (dts,)), ("dyn_tend", (2, cfg["config_dt"])), ("dyn_tend", (1, cfg["config_dt"])), ("smlstep", ()),
+                       ("advance_scalars", (cfg["config_dt"] / 2, 1, 2, 1))):
+        gpu.call(routine, *p)
+        ora.call(routine, *p)
+        _check(blocks, gpu, ora)
+    gpu.call("mono", cfg["config_dt"], 1)
+    ora.call("mono", cfg["config_dt"], 1)
+    _check(blocks, gpu, ora, skip=("wdtn",) + MONO_SCRATCH)
+
+
+def test_too_many_levels_for_the_shared_memory_staging_is_a_clean_error():
+    """the warp-per-column kernels stage whole columns in shared memory: beyond ~220 levels the entry point must return an error
+    with a message, not a launch failure that poisons the context"""
+    case, blocks = common.make_case(3, 1, nVertLevels=400, num_scalars=1)
+    gpu = common.GpuModel(blocks, common.level_config(3))
+    with pytest.raises(RuntimeError, match="nVertLevels too large"):
+        gpu.init()
+        gpu.step(1)
+    # the library is still usable afterwards
+    case2, blocks2 = common.make_case(3, 1, nVertLevels=8, num_scalars=1)
+    g2 = common.GpuModel(blocks2, common.level_config(3))
+    g2.init()
+    g2.step(1)
+    assert np.isfinite(g2.field(0, "u@1")).all()
