@@ -80,6 +80,16 @@ long mpas_b200_halo_exchange_count(void);
 /* the halo_fn of mpas_b200_advance_scalars_mono_work for such a host (TI:3757, 4098): ctx -> int[2] = {nVertLevels, num_scalars} */
 int mpas_b200_mono_halo_default(void* ctx, int which, mpas_real* array);
 int mpas_b200_halo_finalize(void);
+/* No counterpart in the reference: added for callers that cannot call cudaMalloc
+ * (CUDA graph capture, tight serving loops, harnesses that forbid it).  One same-process halo copy (the copyList leg of the
+ * exchange above) that allocates nothing: array(dim1, nElems+1); pack  buffer(:, sendDest(i)) = array(:, sendSrc(i)),
+ * then unpack  array(:, recvDest(i)) = buffer(:, recvSrc(i)),  i = 1..n, all four lists 1-based and device-resident (device
+ * pointers or registered host addresses); sendDest / recvSrc are buffer slots in 1..n.  The message buffer is a fixed
+ * device array inside the library: n * dim1 <= MPAS_B200_NO_ALLOC_MAX_REALS or the call fails with a clear error.  All
+ * calls share that buffer: calls that overlap on the GPU race (calls on the library stream are ordered and safe). */
+#define MPAS_B200_NO_ALLOC_MAX_REALS (1u << 20)
+int mpas_b200_halo_copy_no_alloc(mpas_real* array, int dim1, int n, const int* sendSrc, const int* sendDest, const int* recvSrc,
+                                 const int* recvDest);
 
 /* ---- Layer 2: device-resident dycore ---- */
 void* mpas_b200_dycore_create(int nLocalBlocks, int rank, int nranks);
