@@ -104,7 +104,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
     __shared__ unsigned s_eo[WPB][8], s_c1[WPB][8], s_c2[WPB][8];
     __shared__ real s_coef[WPB][8];
     const int L = p.L, L1 = L + 1, mE = p.mE, LS = tma_slot(L1);
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);  // warp-uniform for the compiler
     __shared__ int s_tv[WPB][5];  // per warp: active flag and the s_dyn indices of its rwp, a, alpha, gamma columns (level 1)
     const int iCell0 = p.cellStart + blockIdx.x * WPB + warp;
     const bool exists = iCell0 <= p.cellEnd;

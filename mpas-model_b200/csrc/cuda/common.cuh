@@ -34,15 +34,16 @@ __device__ __forceinline__ real fsign(real a, real b) { return copysign(a, b); }
 // x / 12 without the generic division sequence: with r = RN(1/12), q0 = RN(x r), rem = x - 12 q0 (exact in one fma),
 // RN(q0 + rem r) is the correctly rounded quotient (Markstein's correction step; for the divisor 3 * 2^2 the exact
 // quotient is never closer than 1/6 ulp to a rounding tie, so the O(2^-53 ulp) error of the correction cannot change
-// the rounding).  Outside [1e-290, 1e290] (underflow / overflow of the intermediates, zeros, NaN) the plain division
+// the rounding).  Outside [2^-962, 2^963) (underflow / overflow of the intermediates, zeros, NaN) the plain division
 // is used, so the result equals x / 12.0 bit for bit for every input.  3 instructions instead of ~12.
 __device__ __forceinline__ real div12(real x) {
 #ifdef SINGLE_PRECISION
     return x / (real)12.0;
 #else
-    const double ax = fabs(x);
-    if (!(ax >= 1e-290 && ax <= 1e290)) {
-        if (ax == 0.0) return x;
+    // biased exponent in [61, 1985] <=> 2^-962 <= |x| < 2^963: an integer test (zeros, subnormals, inf and NaN fail it)
+    const unsigned ex = ((unsigned)__double2hiint(x) >> 20) & 0x7ffu;
+    if (ex - 61u > 1924u) {
+        if (x == 0.0) return x;
         return x / 12.0;
     }
     const double r = 1.0 / 12.0;
@@ -129,8 +130,10 @@ __device__ __forceinline__ void cp_async_s(unsigned sdst, const real* g) {
 __device__ __forceinline__ void stage_col_s(unsigned sdst_lane, const real* gsrc_lane, int n, int lane) {
     if (lane < n) cp_async_s(sdst_lane, gsrc_lane);
     if (lane + 32 < n) cp_async_s(sdst_lane + 32 * (unsigned)sizeof(real), gsrc_lane + 32);
-    if (n > 64)
+    if (n > 64) {
+#pragma unroll 1
         for (int d = 64; lane + d < n; d += 32) cp_async_s(sdst_lane + d * (unsigned)sizeof(real), gsrc_lane + d);
+    }
 }
 __device__ __forceinline__ void stage_wait() {
     asm volatile("cp.async.wait_all;" ::: "memory");
@@ -268,7 +271,7 @@ void ktime_end();
 // warp-per-column mapping: WPB warps per block, one mesh element (cell / edge / vertex) per warp, lanes along k
 #define WPB 8
 #define WARP_ENTITY(first, count)                                   \
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;     \
+    const int lane = threadIdx.x & 31, warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0); \
     const int _ent0 = blockIdx.x * WPB + warp;                      \
     if (_ent0 >= (count)) return;                                   \
     const int ent = (first) + _ent0

@@ -344,7 +344,7 @@ __global__ void __launch_bounds__(WPB * 32, 2) dt_edge_flux_tile_kernel(DtP p, E
     __shared__ unsigned short s_ot[WPB][20], s_ow[WPB][20];
     __shared__ real s_cp[WPB][20], s_cm[WPB][20];
     const int L = p.L, L1 = L + 1, LS = tma_slot(L1);
-    const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int e0 = tp.first[tile], e1 = tp.first[tile + 1], nc = tp.nc[tile];
     const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar);
     if (tid == 0) mbar_init(mbar, (unsigned)nc);
@@ -471,7 +471,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) dt_edge_flux_tile1_kernel(DtP p, 
     __shared__ real s_cp[FT_TEMAX][10], s_cm[FT_TEMAX][10];
     __shared__ int s_c1[FT_TEMAX], s_c2[FT_TEMAX];  // cells of the edge; s_c1 = 0: edge not needed (no owned cell) or not a 10-cell stencil
     const int L = p.L, L1 = L + 1, NL = FIELD ? L1 : L, LS = tma_slot(NL);
-    const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const int e0 = tp.first[tile], ne = tp.first[tile + 1] - e0, nc = tp.nc[tile];
     const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar);
     if (tid == 0) mbar_init(mbar, (unsigned)nc);

@@ -80,7 +80,7 @@ enum { VI_ZZ, VI_P, VI_T, VI_CQW, VI_WT, VI_WR, VI_TZ, VI_C, VI_NCOL, VI_WZ = VI
 __global__ void __launch_bounds__(WPB * 32) vert_imp_kernel(VicP p) {
     extern __shared__ real smem[];
     const int L = p.L, L1 = L + 1, LS = L + 2;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);
     real* sw = smem + (size_t)warp * VI_NCOL * LS;
     real *s_zz = sw + VI_ZZ * LS, *s_p = sw + VI_P * LS, *s_t = sw + VI_T * LS, *s_cqw = sw + VI_CQW * LS, *s_wt = sw + VI_WT * LS;
     real *s_wr = sw + VI_WR * LS, *s_tz = sw + VI_TZ * LS, *s_c = sw + VI_C * LS;
