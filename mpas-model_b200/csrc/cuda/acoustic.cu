@@ -143,7 +143,7 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
     const real *g_zz = p.zz + coff, *g_coftz = p.coftz + woff, *g_cofwt = p.cofwt + coff, *g_rhozz = p.rho_zz + coff;
     const real *g_a = p.a_tri + coff, *g_al = p.alpha_tri + coff, *g_ga = p.gamma_tri + coff;
     const real *g_rtpp = p.rtheta_pp + coff, *g_rhopp = p.rho_pp + coff, *g_rwp = p.rw_p + woff;
-    if (lane == 0) {
+    if (elect_one()) {
         mbar_init(mbar, 1);
         const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
         unsigned total = 0;

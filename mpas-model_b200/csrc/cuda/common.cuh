@@ -166,6 +166,14 @@ __device__ __forceinline__ void mbar_wait(unsigned mbar, unsigned parity) {
             : "memory");
     } while (!ok);
 }
+// One lane of a converged warp (elect.sync): the guard of the bulk-copy issue.  Unlike `lane == 0` it tells the compiler that
+// exactly one thread runs the block, so a bulk copy with warp-uniform operands is a single predicated instruction instead
+// of a loop over the active threads.
+__device__ __forceinline__ bool elect_one() {
+    unsigned pred;
+    asm volatile("{\n .reg .pred p;\n elect.sync _|p, 0xffffffff;\n selp.u32 %0, 1, 0, p;\n}" : "=r"(pred));
+    return pred != 0;
+}
 // Element shift of a column inside its slot (every lane), and the copy itself (issuing lane only; adds its size to total).
 __device__ __forceinline__ int tma_shift(const real* gcol) { return (int)(((unsigned)(unsigned long long)gcol & 15u) / (unsigned)sizeof(real)); }
 // size of that copy, for callers that post the expected byte count before they issue it

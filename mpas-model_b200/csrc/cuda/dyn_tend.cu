@@ -635,7 +635,6 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) 
     const int iEdge = ent;
     real* sc = s_dyn + (size_t)warp * (RK1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * LS;
     const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
-    if (lane == 0) mbar_init(mbar, 1);
     const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
     const bool del4 = (RK1 && p.h_mom_eddy_visc4 > (real)0.0);
     int vertex1 = 0, vertex2 = 0;
@@ -664,7 +663,8 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) 
         g_dv1 = p.delsq_vorticity + (size_t)(vertex1 - 1) * L;
         g_dv2 = p.delsq_vorticity + (size_t)(vertex2 - 1) * L;
     }
-    if (lane == 0) {  // one bulk copy per column, all in flight together
+    if (elect_one()) {  // one bulk copy per column, all in flight together
+        mbar_init(mbar, 1);
         const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
         unsigned total = 0;
         tma_issue_col(s0 + EC_U * cs, g_u, L, mbar, total);
@@ -722,7 +722,7 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) 
         wz[kk] = f;
     }
     __syncwarp();
-    if (del4 && lane == 0) {  // second copy phase into the rw slots (their last read is above)
+    if (del4 && elect_one()) {  // second copy phase into the rw slots (their last read is above)
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
         unsigned total = 0;
@@ -864,7 +864,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) dt_cell_kernel(DtP p, const re
     const real *g_w = p.w + woff, *g_rw = p.rw + woff, *g_th = p.theta_m + coff, *g_rws = p.rw_save + woff, *g_ths = p.theta_m_save + coff;
     const real *g_twe = p.tend_w_euler + woff, *g_tte = p.tend_theta_euler + coff, *g_rho = p.rho_zz + coff;
     const real *g_cqw = p.cqw + coff, *g_pp = p.pp + coff, *g_dpdz = p.dpdz + coff;
-    if (lane == 0) {
+    if (elect_one()) {
         mbar_init(mbar, 1);
         const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc), cs = (unsigned)(LS * sizeof(real));
         unsigned total = 0;

@@ -123,7 +123,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) as_cell_kernel(AsP p) {
     const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
     const real* g_scal = p.scalar_new + (size_t)(iCell - 1) * nel;
     const real* g_ww = p.wwAvg + (size_t)(iCell - 1) * L1;
-    if (lane == 0) {
+    if (elect_one()) {
         mbar_init(mbar, 1);
         const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc);
         unsigned total = 0;
@@ -685,7 +685,7 @@ __global__ void __launch_bounds__(WPB * 32, MINB) monoN_cell_kernel(MonoNP p) {
     const real* g_new = p.scalars_new + (size_t)(iCell - 1) * nel;
     const real* g_old = p.scalars_old + (size_t)(iCell - 1) * nel;
     const real* g_ww = p.wwAvg + (size_t)(iCell - 1) * L1;
-    if (lane == 0) {
+    if (elect_one()) {
         mbar_init(mbar, 1);
         const unsigned s0 = (unsigned)__cvta_generic_to_shared(sc);
         unsigned total = 0;
