@@ -215,6 +215,99 @@ __global__ void __launch_bounds__(256, MINB) dt_cell_mix_kernel(DtP p) {  // rk_
     p.tend_theta_euler[ic] = tte;
 }
 
+// dt_cell_mix_kernel as one cell per warp, two levels per lane: the edge metadata (offsets of the edge and of its two cells,
+// the sign * metric factors in the reference's multiplication order, meshScalingDel2) is staged once per cell instead of
+// once per level; cells with more than 6 edges and meshes with maxEdges > 8 take the flat kernel's path per slot count.
+// Padding slots carry zero factors (sum + 0 * x == sum: the sums start at +0 and are never -0).
+template <int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) dt_cell_mix_warp_kernel(DtP p) {  // rk_step == 1
+    __shared__ unsigned s_eo[WPB][8], s_c1[WPB][8], s_c2[WPB][8], s_w1[WPB][8], s_w2[WPB][8];
+    __shared__ real s_fd[WPB][8], s_fw[WPB][8], s_ft[WPB][8], s_ms2[WPB][8];
+    const int L = p.L, L1 = L + 1, mE = p.mE;
+    WARP_ENTITY(p.cellStart, p.nCellsLoop);
+    const int iCell = ent;
+    const int ne = p.nEdgesOnCell[iCell - 1];
+    const real r_areaCell = p.invAreaCell[iCell - 1];
+    const int npad = ne <= 6 ? 6 : 8;
+    if (lane < 8) {
+        const bool in = lane < ne;
+        const int iEdge = p.edgesOnCell[IX2(in ? lane + 1 : 1, iCell, mE)];
+        const real sgn = p.edgesOnCell_sign[IX2(in ? lane + 1 : 1, iCell, mE)];
+        const real dv = p.dvEdge[iEdge - 1], idc = p.invDcEdge[iEdge - 1];
+        const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
+        s_eo[warp][lane] = (unsigned)(iEdge - 1) * (unsigned)L;
+        s_c1[warp][lane] = (unsigned)(cell1 - 1) * (unsigned)L;
+        s_c2[warp][lane] = (unsigned)(cell2 - 1) * (unsigned)L;
+        s_w1[warp][lane] = (unsigned)(cell1 - 1) * (unsigned)L1;
+        s_w2[warp][lane] = (unsigned)(cell2 - 1) * (unsigned)L1;
+        s_fd[warp][lane] = in ? r_areaCell * dv * sgn : (real)0.0;
+        s_fw[warp][lane] = in ? (real)0.5 * r_areaCell * sgn * dv * idc : (real)0.0;
+        s_ft[warp][lane] = in ? r_areaCell * sgn * dv * idc : (real)0.0;
+        s_ms2[warp][lane] = p.meshScalingDel2[iEdge - 1];
+    }
+    __syncwarp();
+    const bool visc4 = p.h_mom_eddy_visc4 > (real)0.0;
+    const size_t coff = (size_t)(iCell - 1) * L, woff = (size_t)(iCell - 1) * L1;
+    if (lane == 0) p.tend_w_euler[woff + L] = 0.0;  // k = nVertLevels + 1
+    for (int ka = lane; ka < L; ka += 64) {  // 0-based levels ka and ka + 32
+        const bool vb = ka + 32 < L;
+        const int bo = vb ? 32 : 0;
+        const int ma = ka > 0 ? 1 : 0;  // distance to the level below (level 1 has none: the w terms are skipped there)
+        real dsq_div[2] = {0, 0}, dsq_w[2] = {0, 0}, twe[2] = {0, 0}, dsq_th[2] = {0, 0}, tte[2] = {0, 0};
+#pragma unroll 1
+        for (int t = 0; t < npad; ++t) {
+            const unsigned eo = s_eo[warp][t], c1 = s_c1[warp][t], c2 = s_c2[warp][t];
+            const real* __restrict__ re = elem_ptr(p.rho_edge + ka, eo);
+            const real* __restrict__ k1 = elem_ptr(p.kdiff + ka, c1);
+            const real* __restrict__ k2 = elem_ptr(p.kdiff + ka, c2);
+            const real* __restrict__ t1 = elem_ptr(p.theta_m + ka, c1);
+            const real* __restrict__ t2 = elem_ptr(p.theta_m + ka, c2);
+            const real* __restrict__ w1 = elem_ptr(p.w + ka, s_w1[warp][t]);
+            const real* __restrict__ w2 = elem_ptr(p.w + ka, s_w2[warp][t]);
+            real rho_e[2], rho_m[2], kd1[2], kd2[2], kd1m[2], kd2m[2], th1[2], th2[2], ww1[2], ww2[2], du[2] = {0, 0};
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int o = h ? bo : 0, m = h ? (bo ? 1 : ma) : ma;
+                rho_e[h] = re[o]; rho_m[h] = re[o - m];
+                kd1[h] = k1[o]; kd2[h] = k2[o]; kd1m[h] = k1[o - m]; kd2m[h] = k2[o - m];
+                th1[h] = t1[o]; th2[h] = t2[o];
+                ww1[h] = w1[o]; ww2[h] = w2[o];
+            }
+            if (visc4) {
+                const real* __restrict__ dq = elem_ptr(p.delsq_u + ka, eo);
+                du[0] = dq[0];
+                du[1] = dq[bo];
+            }
+            const real fd = s_fd[warp][t], fw = s_fw[warp][t], ft = s_ft[warp][t], ms2 = s_ms2[warp][t];
+            const real pr_scale = p.prandtl_inv * ms2;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                if (visc4) dsq_div[h] = dsq_div[h] + fd * du[h];
+                if (h == 1 || ka > 0) {  // k >= 2
+                    real w_turb_flux = fw * (rho_e[h] + rho_m[h]) * (ww2[h] - ww1[h]);
+                    dsq_w[h] = dsq_w[h] + w_turb_flux;
+                    w_turb_flux = w_turb_flux * ms2 * (real)0.25 * (kd1[h] + kd2[h] + kd1m[h] + kd2m[h]);
+                    twe[h] = twe[h] + w_turb_flux;
+                }
+                real theta_turb_flux = ft * (th2[h] - th1[h]) * rho_e[h];
+                dsq_th[h] = dsq_th[h] + theta_turb_flux;
+                theta_turb_flux = theta_turb_flux * (real)0.5 * (kd1[h] + kd2[h]) * pr_scale;
+                tte[h] = tte[h] + theta_turb_flux;
+            }
+        }
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            if (h == 1 && !vb) break;
+            const int k0 = ka + 32 * h;
+            if (visc4) p.delsq_divergence[coff + k0] = dsq_div[h];
+            p.delsq_w[coff + k0] = dsq_w[h];
+            p.tend_w_euler[woff + k0] = twe[h];
+            p.delsq_theta[coff + k0] = dsq_th[h];
+            p.tend_theta_euler[coff + k0] = tte[h];
+        }
+    }
+}
+
 // ---- warp-per-column kernels: one mesh element per warp, lanes along k.  The k-independent stencil metadata
 // (neighbour indices, weights, signs) is fetched ONCE per warp into shared memory instead of once per level. ----
 
@@ -1111,7 +1204,12 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
             KLAUNCH(dt_vertex_mix_kernel, (long long)p.nVerticesLoop * L, 256, p);
             KCHECK("dt_vertex_mix_kernel");
         }
-        if (cmix_minb == 5) KLAUNCH(dt_cell_mix_kernel<5>, (long long)p.nCellsLoop * (L + 1), 256, p);
+        static const int cmix_warp = tune("dt_cmix_warp", 3);  // blocks per SM of the warp form, 0 = flat kernel
+        if (cmix_warp == 3 && maxEdges <= 8) WLAUNCH(dt_cell_mix_warp_kernel<3>, p.nCellsLoop, 0, p);
+        else if (cmix_warp == 4 && maxEdges <= 8) WLAUNCH(dt_cell_mix_warp_kernel<4>, p.nCellsLoop, 0, p);
+        else if (cmix_warp == 5 && maxEdges <= 8) WLAUNCH(dt_cell_mix_warp_kernel<5>, p.nCellsLoop, 0, p);
+        else if (cmix_warp && maxEdges <= 8) WLAUNCH(dt_cell_mix_warp_kernel<6>, p.nCellsLoop, 0, p);
+        else if (cmix_minb == 5) KLAUNCH(dt_cell_mix_kernel<5>, (long long)p.nCellsLoop * (L + 1), 256, p);
         else if (cmix_minb == 6) KLAUNCH(dt_cell_mix_kernel<6>, (long long)p.nCellsLoop * (L + 1), 256, p);
         else KLAUNCH(dt_cell_mix_kernel<0>, (long long)p.nCellsLoop * (L + 1), 256, p);
         KCHECK("dt_cell_mix_kernel");
