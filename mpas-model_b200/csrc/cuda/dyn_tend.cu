@@ -717,8 +717,8 @@ enum { EC_RW1, EC_RW2, EC_U, EC_PV, EC_RHO, EC_TE, EC_KE1, EC_KE2, EC_HD1, EC_HD
 // references to a multiple of UNR (q + 0*x == q exactly, q is never -0), and the unrolled body issues 4*UNR
 // independent loads before the first dependent add.
 // dynamic shared memory: WPB * ncol * tma_slot(L + 1) reals.
-template <int UNR, bool RK1, bool VMIX>
-__global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : 4) dt_edge_kernel(DtP p) {
+template <int UNR, bool RK1, bool VMIX, int MINB = 4>
+__global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : MINB) dt_edge_kernel(DtP p) {
     extern __shared__ __align__(16) real s_dyn[];
     __shared__ __align__(8) unsigned long long s_bar[WPB];
     __shared__ unsigned s_off[WPB][20];
@@ -1258,7 +1258,10 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     KCHECK("dt_edge_flux_kernel");
     {
         const size_t shm = (size_t)WPB * (rk_step == 1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * tma_slot(L + 1) * sizeof(real);
-        if (rk_step != 1) WLAUNCH((dt_edge_kernel<5, false, false>), p.nEdgesSolveLoop, shm, p);
+        static const int de_minb = tune("dt_edge_minb", 5);
+        if (rk_step != 1 && de_minb == 5) WLAUNCH((dt_edge_kernel<5, false, false, 5>), p.nEdgesSolveLoop, shm, p);
+        else if (rk_step != 1 && de_minb == 3) WLAUNCH((dt_edge_kernel<5, false, false, 3>), p.nEdgesSolveLoop, shm, p);
+        else if (rk_step != 1) WLAUNCH((dt_edge_kernel<5, false, false>), p.nEdgesSolveLoop, shm, p);
         else if (p.v_mom_eddy_visc2 > (real)0.0) WLAUNCH((dt_edge_kernel<5, true, true>), p.nEdgesSolveLoop, shm, p);
         else WLAUNCH((dt_edge_kernel<5, true, false>), p.nEdgesSolveLoop, shm, p);
         KCHECK("dt_edge_kernel");
