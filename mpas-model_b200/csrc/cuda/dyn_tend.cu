@@ -1267,7 +1267,8 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
         KCHECK("dt_edge_kernel");
     }
     {
-        static const int minb = tune("dt_cell_minb", 4);
+        static const int minb1 = tune("dt_cell_minb_rk1", 4), minb23 = tune("dt_cell_minb", 5);  // measured: 438 / 464 us (rk 1), 258 / 246 us (rk 2, 3) at 4 / 5
+        const int minb = rk_step == 1 ? minb1 : minb23;
         const size_t shm = (size_t)WPB * (rk_step == 1 ? CC_NCOL_RK1 : CC_NCOL_RK23) * tma_slot(L + 1) * sizeof(real);
         if (rk_step == 1) {
             if (minb == 3) WLAUNCH((dt_cell_kernel<true, 3>), p.nCellsSolveLoop, shm, p, ft, fw, ft2);

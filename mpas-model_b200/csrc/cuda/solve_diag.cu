@@ -180,6 +180,59 @@ __global__ void __launch_bounds__(256) sd_edge_kernel(SdP p) {
 // reference's order.  Lists are padded with zero-factor self references (x + 0*y == x exactly: the sums start at +0 and
 // are never -0).
 
+// sd_vertex: the three edges' metadata are warp-uniform loads, once per vertex
+template <int MINB>
+__global__ void __launch_bounds__(WPB * 32, MINB) sd_vertex_warp_kernel(SdP p) {
+    const int L = p.L;
+    WARP_ENTITY(p.vertexStart, p.nVerticesLoop);
+    const int iVertex = ent;
+    const int* eov = p.edgesOnVertex + (size_t)(iVertex - 1) * 3;
+    const real* sg = p.edgesOnVertex_sign + (size_t)(iVertex - 1) * 3;
+    unsigned eo[3];
+    real sdc[3], efac[3];
+#pragma unroll
+    for (int i = 0; i < 3; ++i) {
+        const int e = eov[i];
+        const real dc = p.dcEdge[e - 1], dv = p.dvEdge[e - 1];
+        eo[i] = (unsigned)(e - 1) * (unsigned)L;
+        sdc[i] = sg[i] * dc;
+        efac[i] = dc * dv;
+    }
+    const real iat = p.invAreaTriangle[iVertex - 1];
+    const real fv = p.fVertex[iVertex - 1];
+    const real r = (real)0.25 * iat;
+    const size_t voff = (size_t)(iVertex - 1) * L;
+    for (int ka = lane; ka < L; ka += 64) {
+        const bool vb = ka + 32 < L;
+        const int bo = vb ? 32 : 0;
+        real ua[3], ub[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            const real* __restrict__ q = elem_ptr(p.u + ka, eo[i]);
+            ua[i] = q[0];
+            ub[i] = q[bo];
+        }
+        real va = 0.0, vbb = 0.0, ka_[3], kb_[3];
+#pragma unroll
+        for (int i = 0; i < 3; ++i) {
+            va = va + sdc[i] * ua[i];
+            vbb = vbb + sdc[i] * ub[i];
+            ka_[i] = efac[i] * (ua[i] * ua[i]);
+            kb_[i] = efac[i] * (ub[i] * ub[i]);
+        }
+        va = va * iat;
+        vbb = vbb * iat;
+        p.vorticity[voff + ka] = va;
+        p.ke_vertex[voff + ka] = (ka_[0] + ka_[1] + ka_[2]) * r;
+        p.pv_vertex[voff + ka] = (fv + va);
+        if (vb) {
+            p.vorticity[voff + ka + 32] = vbb;
+            p.ke_vertex[voff + ka + 32] = (kb_[0] + kb_[1] + kb_[2]) * r;
+            p.pv_vertex[voff + ka + 32] = (fv + vbb);
+        }
+    }
+}
+
 // sd_cell: divergence, ke (with the ke_vertex blend), pv_cell.  NE = padded edge count (6 or 8).
 template <int NE>
 __device__ __forceinline__ void sd_cell_levels(const SdP& p, int L, int lane, const unsigned* eo, const real* sdv, const real* efac, const unsigned* vo,
@@ -405,17 +458,23 @@ extern "C" int mpas_b200_compute_solve_diagnostics_work(MPAS_SOLVEDIAG_ARGS) {
     p.nEdgesOnEdge = X(nEdgesOnEdge);
     p.h_edge = X(h_edge); p.v = X(v); p.vorticity = X(vorticity); p.ke = X(ke); p.pv_edge = X(pv_edge); p.pv_vertex = X(pv_vertex); p.pv_cell = X(pv_cell);
     p.gradPVn = X(gradPVn); p.gradPVt = X(gradPVt); p.divergence = X(divergence); p.ke_vertex = X(ke_vertex); p.ke_edge = X(ke_edge);
-    KLAUNCH(sd_vertex_kernel, (long long)p.nVerticesLoop * p.L, 256, p);
+    static const int vw = tune("sd_vertex_warp", 8);  // blocks per SM of the warp form, 0 = flat kernel
+    if (vw == 4) WLAUNCH(sd_vertex_warp_kernel<4>, p.nVerticesLoop, 0, p);
+    else if (vw == 8) WLAUNCH(sd_vertex_warp_kernel<8>, p.nVerticesLoop, 0, p);
+    else if (vw) WLAUNCH(sd_vertex_warp_kernel<6>, p.nVerticesLoop, 0, p);
+    else KLAUNCH(sd_vertex_kernel, (long long)p.nVerticesLoop * p.L, 256, p);
     KCHECK("sd_vertex_kernel");
     static const int warp_form = tune("sd_warp", 7);  // bit 0: sd_cell, bit 1: sd_edge with reconstruct_v, bit 2: sd_edge without (0 = the flat kernels)
     static const int cell_minb = tune("sd_cell_minb", 6), edge_minb = tune("sd_edge_minb", 6);
     const bool cw = (warp_form & 1) && maxEdges <= 8;
     if (cw && cell_minb == 4) WLAUNCH(sd_cell_warp_kernel<4>, p.nCellsLoop, 0, p);
+    else if (cw && cell_minb == 8) WLAUNCH(sd_cell_warp_kernel<8>, p.nCellsLoop, 0, p);
     else if (cw) WLAUNCH(sd_cell_warp_kernel<6>, p.nCellsLoop, 0, p);
     else KLAUNCH(sd_cell_kernel, (long long)p.nCellsLoop * p.L, 256, p);
     KCHECK("sd_cell_kernel");
     if (p.reconstruct_v && (warp_form & 2) && maxEdges2 <= 20) WLAUNCH((sd_edge_warp_kernel<5, 4, true>), p.nEdgesLoop, 0, p);
     else if (!p.reconstruct_v && (warp_form & 4) && edge_minb == 6) WLAUNCH((sd_edge_warp_kernel<5, 6, false>), p.nEdgesLoop, 0, p);
+    else if (!p.reconstruct_v && (warp_form & 4) && edge_minb == 8) WLAUNCH((sd_edge_warp_kernel<5, 8, false>), p.nEdgesLoop, 0, p);
     else if (!p.reconstruct_v && (warp_form & 4)) WLAUNCH((sd_edge_warp_kernel<5, 4, false>), p.nEdgesLoop, 0, p);
     else if (p.reconstruct_v) KLAUNCH(sd_edge_kernel<true>, (long long)p.nEdgesLoop * p.L, 256, p);
     else KLAUNCH(sd_edge_kernel<false>, (long long)p.nEdgesLoop * p.L, 256, p);
