@@ -11,6 +11,9 @@
 //                          (TI:2687-2708).  Also performs the rtheta_pp_old <- rtheta_pp copy of
 //                          TI:2603-2611 for its own column (halo columns only do that copy).
 //   divdamp_kernel         one thread per (k, edge) (TI:2768-2793).
+#include <map>
+#include <mutex>
+
 #include "common.cuh"
 
 using namespace mpasb200;
@@ -56,6 +59,7 @@ struct AcCellP {
     const real *rho_zz, *theta_m, *zz, *cofwt, *coftz, *a_tri, *alpha_tri, *gamma_tri, *dss;
     const real *tend_rho, *tend_rt, *tend_rw, *cofwr, *cofwz, *w, *rw, *rw_save;
     const real *fzm, *fzp, *rdzw, *cofrz, *ru_p;
+    const real* tend_ru_fold;  // FOLD: tend_ru in place of ru_p
     real *rw_p, *rtheta_pp, *rtheta_pp_old, *wwAvg, *rho_pp;
 };
 
@@ -64,17 +68,19 @@ struct AcCellP {
 enum { AC_ZZ, AC_COFTZ, AC_COFWT, AC_RHOZZ, AC_ATRI, AC_ALTRI, AC_GATRI, AC_NTMA_FIRST, AC_RTPP = AC_NTMA_FIRST, AC_RHOPP, AC_RWPOLD, AC_NTMA, AC_TS = AC_NTMA, AC_RS, AC_RWP, AC_NCOL };
 
 // rs/ts -= flux over NE edges for the two levels of a lane; all 6*NE loads are issued before the first dependent subtract
-template <int NE>
+// SCALE: the gathered column holds tend_ru and ru_p = scale * tend_ru is formed on the fly (first substep, folded edge pass)
+template <int NE, bool SCALE>
 __device__ __forceinline__ void ac_flux_sub(const real* __restrict__ rup_ka, const real* __restrict__ thp_ka, const unsigned* eo, const unsigned* c1o,
-                                            const unsigned* c2o, const real* coef, real invArea, int bo, real& rs_a, real& rs_b, real& ts_a, real& ts_b) {
+                                            const unsigned* c2o, const real* coef, real invArea, int bo, real scale, real& rs_a, real& rs_b, real& ts_a,
+                                            real& ts_b) {
     real ua[NE], ub[NE], t1a[NE], t1b[NE], t2a[NE], t2b[NE];
 #pragma unroll
     for (int t = 0; t < NE; ++t) {
         const real* __restrict__ q = elem_ptr(rup_ka, eo[t]);
         const real* __restrict__ q1 = elem_ptr(thp_ka, c1o[t]);
         const real* __restrict__ q2 = elem_ptr(thp_ka, c2o[t]);
-        ua[t] = q[0];
-        ub[t] = q[bo];
+        ua[t] = SCALE ? scale * q[0] : q[0];
+        ub[t] = SCALE ? scale * q[bo] : q[bo];
         t1a[t] = q1[0];
         t1b[t] = q1[bo];
         t2a[t] = q2[0];
@@ -97,7 +103,9 @@ __device__ __forceinline__ void ac_flux_sub(const real* __restrict__ rup_ka, con
 // per lane, the edge list staged as element offsets + the coefficient (sign*dts)*dvEdge (zero beyond nEdgesOnCell).
 // FIRST = small_step 1: rtheta_pp, rho_pp, rw_p, wwAvg start from zero and are not read (TI:2603-2622).
 // dynamic shared memory: WPB * AC_NCOL * tma_slot(L + 1) reals.
-template <bool FIRST>
+// FOLD (first substep of the device-resident driver only): the edge pass ru_p = dts * tend_ru is not run; the fluxes read
+// tend_ru and scale it, the divergence damping that follows writes ru_p and ruAvg (divdamp_kernel<true>)
+template <bool FIRST, bool FOLD = false>
 __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
     extern __shared__ __align__(16) real s_dyn[];
     __shared__ __align__(8) unsigned long long s_bar[WPB];
@@ -198,11 +206,11 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
         const int bo = vb ? 32 : 0;
         real rs_a = 0.0, rs_b = 0.0, ts_a = 0.0, ts_b = 0.0;
         {
-            const real* __restrict__ rup = p.ru_p + kl;
+            const real* __restrict__ rup = (FOLD ? p.tend_ru_fold : p.ru_p) + kl;
             const real* __restrict__ thp = p.theta_m + kl;
-            ac_flux_sub<3>(rup, thp, s_eo[warp], s_c1[warp], s_c2[warp], s_coef[warp], invArea, bo, rs_a, rs_b, ts_a, ts_b);
-            ac_flux_sub<3>(rup, thp, s_eo[warp] + 3, s_c1[warp] + 3, s_c2[warp] + 3, s_coef[warp] + 3, invArea, bo, rs_a, rs_b, ts_a, ts_b);
-            if (npad > 6) ac_flux_sub<2>(rup, thp, s_eo[warp] + 6, s_c1[warp] + 6, s_c2[warp] + 6, s_coef[warp] + 6, invArea, bo, rs_a, rs_b, ts_a, ts_b);
+            ac_flux_sub<3, FOLD>(rup, thp, s_eo[warp], s_c1[warp], s_c2[warp], s_coef[warp], invArea, bo, dts, rs_a, rs_b, ts_a, ts_b);
+            ac_flux_sub<3, FOLD>(rup, thp, s_eo[warp] + 3, s_c1[warp] + 3, s_c2[warp] + 3, s_coef[warp] + 3, invArea, bo, dts, rs_a, rs_b, ts_a, ts_b);
+            if (npad > 6) ac_flux_sub<2, FOLD>(rup, thp, s_eo[warp] + 6, s_c1[warp] + 6, s_c2[warp] + 6, s_coef[warp] + 6, invArea, bo, dts, rs_a, rs_b, ts_a, ts_b);
         }
         // single-use operands of this chunk, loaded now so that they share the round trip of the gather
         const real trho_a = p.tend_rho[coff + kl], trho_b = p.tend_rho[coff + kl + bo];
@@ -359,8 +367,14 @@ struct DivDampP {
     const int* cellsOnEdge;
     const real *theta_m, *rtheta_pp, *rtheta_pp_old, *specZoneMaskEdge;
     real* ru_p;
+    const real* tend_ru;  // FOLD: ru_p = dts * tend_ru has not been stored yet
+    real* ruAvg;
+    real dts;
 };
 
+// FOLD: this call also does the first substep's edge pass (TI:2592-2597: ru_p = dts * tend_ru, ruAvg = ru_p) that the acoustic
+// step left out -- the same products, one read of tend_ru instead of a write and a read of ru_p
+template <bool FOLD>
 __global__ void __launch_bounds__(256) divdamp_kernel(DivDampP p) {
     FLAT_KC(p.nEdgesLoop, p.L);
     const int L = p.L;
@@ -370,10 +384,35 @@ __global__ void __launch_bounds__(256) divdamp_kernel(DivDampP p) {
     const size_t i1 = IX2(k, cell1, L), i2 = IX2(k, cell2, L), ie = IX2(k, iEdge, L);
     const real divCell1 = -(p.rtheta_pp[i1] - p.rtheta_pp_old[i1]);
     const real divCell2 = -(p.rtheta_pp[i2] - p.rtheta_pp_old[i2]);
-    p.ru_p[ie] = p.ru_p[ie] + p.coef_divdamp * (divCell2 - divCell1) * ((real)1.0 - p.specZoneMaskEdge[iEdge - 1]) / (p.theta_m[i1] + p.theta_m[i2]);
+    real r;
+    if (FOLD) {
+        r = p.dts * p.tend_ru[ie];
+        p.ruAvg[ie] = r;
+    } else {
+        r = p.ru_p[ie];
+    }
+    p.ru_p[ie] = r + p.coef_divdamp * (divCell2 - divCell1) * ((real)1.0 - p.specZoneMaskEdge[iEdge - 1]) / (p.theta_m[i1] + p.theta_m[i2]);
 }
 
+// Folded first substep: which ru_p arrays wait for their edge pass (one entry per block between the acoustic step and the
+// divergence damping of the same substep)
+struct FoldEntry {
+    const real* tend_ru;
+    real* ruAvg;
+    real dts;
+    int edgeStart, nEdgesLoop;
+};
+std::mutex g_fold_mu;
+std::map<const void*, FoldEntry> g_fold;
+thread_local bool tl_fold_next = false;
+
 }  // namespace
+
+namespace mpasb200 {
+// device-resident driver (srk3.cu): the next acoustic step on this thread may leave its first-substep edge pass to the
+// divergence damping that follows it
+void acoustic_fold_next_call() { tl_fold_next = true; }
+}  // namespace mpasb200
 
 extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
     (void)nCells; (void)nEdges; (void)vertexStart; (void)vertexEnd; (void)vertexSolveStart; (void)vertexSolveEnd;
@@ -382,6 +421,7 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
     const real c2 = MPAS_CP * rcv;
     const real resm = ((real)1.0 - epssm) / ((real)1.0 + epssm);
     const int L = nVertLevels;
+    bool fold = false;
     {
         AcEdgeP p;
         p.L = L; p.km.set(L, L + 1); p.nCellsSolve = nCellsSolve; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1; p.small_step = small_step;
@@ -390,8 +430,16 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
         p.rtheta_pp = X(rtheta_pp); p.rho_pp = X(rho_pp); p.zz = X(zz); p.exner = X(exner); p.cqu = X(cqu); p.zxu = X(zxu);
         p.tend_ru = X(tend_ru); p.invDcEdge = X(invDcEdge); p.specZoneMaskEdge = X(specZoneMaskEdge);
         p.ru_p = X(ru_p); p.ruAvg = X(ruAvg);
-        KLAUNCH(acoustic_edge_kernel, (long long)p.nEdgesLoop * L, 256, p);
-        KCHECK("acoustic_edge_kernel");
+        fold = tl_fold_next && small_step == 1;
+        tl_fold_next = false;
+        if (fold) {
+            std::lock_guard<std::mutex> lk(g_fold_mu);
+            if (g_fold.count(p.ru_p)) return fail_msg("mpas_b200_advance_acoustic_step_work: folded edge pass of the previous call was never consumed");
+            g_fold[p.ru_p] = FoldEntry{p.tend_ru, p.ruAvg, dts, p.edgeStart, p.nEdgesLoop};
+        } else {
+            KLAUNCH(acoustic_edge_kernel, (long long)p.nEdgesLoop * L, 256, p);
+            KCHECK("acoustic_edge_kernel");
+        }
     }
     {
         AcCellP p;
@@ -407,7 +455,9 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
         p.rw_p = X(rw_p); p.rtheta_pp = X(rtheta_pp); p.rtheta_pp_old = X(rtheta_pp_old); p.wwAvg = X(wwAvg); p.rho_pp = X(rho_pp);
         const int ncols = cellEnd - cellStart + 1;
         const size_t shm = (size_t)WPB * AC_NCOL * tma_slot(L + 1) * sizeof(real);
-        if (small_step == 1) WLAUNCH(acoustic_cell_kernel<true>, ncols, shm, p);
+        p.tend_ru_fold = X(tend_ru);
+        if (fold) WLAUNCH((acoustic_cell_kernel<true, true>), ncols, shm, p);
+        else if (small_step == 1) WLAUNCH(acoustic_cell_kernel<true>, ncols, shm, p);
         else WLAUNCH(acoustic_cell_kernel<false>, ncols, shm, p);
         KCHECK("acoustic_cell_kernel");
     }
@@ -423,7 +473,21 @@ extern "C" int mpas_b200_divergence_damping_3d(MPAS_DIVDAMP_ARGS) {
     p.L = nVertLevels; p.nCellsSolve = nCellsSolve; p.edgeStart = edgeStart; p.nEdgesLoop = edgeEnd - edgeStart + 1;
     p.cellsOnEdge = X(cellsOnEdge); p.theta_m = X(theta_m); p.rtheta_pp = X(rtheta_pp); p.rtheta_pp_old = X(rtheta_pp_old);
     p.specZoneMaskEdge = X(specZoneMaskEdge); p.ru_p = X(ru_p);
-    KLAUNCH(divdamp_kernel, (long long)p.nEdgesLoop * p.L, 256, p);
+    p.tend_ru = nullptr; p.ruAvg = nullptr; p.dts = 0;
+    bool fold = false;
+    {
+        std::lock_guard<std::mutex> lk(g_fold_mu);
+        auto it = g_fold.find(p.ru_p);
+        if (it != g_fold.end()) {
+            const FoldEntry& f = it->second;
+            if (f.edgeStart != p.edgeStart || f.nEdgesLoop != p.nEdgesLoop) return fail_msg("mpas_b200_divergence_damping_3d: edge range differs from the folded acoustic step's");
+            p.tend_ru = f.tend_ru; p.ruAvg = f.ruAvg; p.dts = f.dts;
+            fold = true;
+            g_fold.erase(it);
+        }
+    }
+    if (fold) KLAUNCH(divdamp_kernel<true>, (long long)p.nEdgesLoop * p.L, 256, p);
+    else KLAUNCH(divdamp_kernel<false>, (long long)p.nEdgesLoop * p.L, 256, p);
     KCHECK("divdamp_kernel");
     return 0;
 }

@@ -247,6 +247,10 @@ inline T* X(T* p) { return (T*)xlate((const void*)p); }
 template <class T>
 inline const T* X(const T* p) { return (const T*)xlate((const void*)p); }
 
+// acoustic.cu: the next mpas_b200_advance_acoustic_step_work call of this thread (small_step 1 only) skips its edge pass
+// ru_p = dts * tend_ru; the mpas_b200_divergence_damping_3d call on the same ru_p that follows does it
+void acoustic_fold_next_call();
+
 // opt a kernel in to more than 48 KB of dynamic shared memory (cached per kernel); false if it cannot be granted
 bool ensure_dyn_smem(const void* kernel, size_t bytes);
 

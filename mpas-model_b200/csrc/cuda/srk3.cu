@@ -405,7 +405,11 @@ static int srk3_body(Dycore& m) {
                 CK(xchg(m, {{"rho_pp", 1}}));  // TI:792
                 {
                     Phase ph(m, "atm_advance_acoustic_step");
-                    for (auto& b : m.blocks) CK(call_acoustic(b, rk_sub_timestep[rk_step], small_step));  // TI:824
+                    static const int fold_first = tune("ac_fold_first", 1);
+                    for (auto& b : m.blocks) {
+                        if (fold_first && small_step == 1) acoustic_fold_next_call();  // its edge pass runs inside the divergence damping below
+                        CK(call_acoustic(b, rk_sub_timestep[rk_step], small_step));  // TI:824
+                    }
                 }
                 CK(xchg(m, {{"rtheta_pp", 1}}));  // TI:845
                 {
