@@ -105,8 +105,8 @@ __device__ __forceinline__ void ac_flux_sub(const real* __restrict__ rup_ka, con
 // dynamic shared memory: WPB * AC_NCOL * tma_slot(L + 1) reals.
 // FOLD (first substep of the device-resident driver only): the edge pass ru_p = dts * tend_ru is not run; the fluxes read
 // tend_ru and scale it, the divergence damping that follows writes ru_p and ruAvg (divdamp_kernel<true>)
-template <bool FIRST, bool FOLD = false>
-__global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
+template <bool FIRST, bool FOLD = false, int MINB = 4>
+__global__ void __launch_bounds__(WPB * 32, MINB) acoustic_cell_kernel(AcCellP p) {
     extern __shared__ __align__(16) real s_dyn[];
     __shared__ __align__(8) unsigned long long s_bar[WPB];
     __shared__ unsigned s_eo[WPB][8], s_c1[WPB][8], s_c2[WPB][8];
@@ -146,7 +146,9 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
         __syncthreads();
         return;
     }
-    real* sc = s_dyn + (size_t)warp * AC_NCOL * LS;
+    // the first substep stages no rtheta_pp / rho_pp / rw_p columns: its scratch columns move down, 10 slots per warp
+    constexpr int C_TS = FIRST ? (int)AC_NTMA_FIRST : (int)AC_TS, C_RS = C_TS + 1, C_RWP = C_TS + 2, NCOL = C_TS + 3;
+    real* sc = s_dyn + (size_t)warp * NCOL * LS;
     const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
     const real *g_zz = p.zz + coff, *g_coftz = p.coftz + woff, *g_cofwt = p.cofwt + coff, *g_rhozz = p.rho_zz + coff;
     const real *g_a = p.a_tri + coff, *g_al = p.alpha_tri + coff, *g_ga = p.gamma_tri + coff;
@@ -180,9 +182,9 @@ __global__ void __launch_bounds__(WPB * 32, 4) acoustic_cell_kernel(AcCellP p) {
     const real* s_rtpp = sc + AC_RTPP * LS + tma_shift(g_rtpp) - 1;
     const real* s_rhopp = sc + AC_RHOPP * LS + tma_shift(g_rhopp) - 1;
     const real* s_rwold = sc + AC_RWPOLD * LS + tma_shift(g_rwp) - 1;
-    real* ts = sc + AC_TS * LS - 1;
-    real* rs = sc + AC_RS * LS - 1;
-    real* rwp = sc + AC_RWP * LS - 1;
+    real* ts = sc + C_TS * LS - 1;
+    real* rs = sc + C_RS * LS - 1;
+    real* rwp = sc + C_RWP * LS - 1;
 
     const int ne = p.nEdgesOnCell[iCell - 1];
     const int npad = ne <= 6 ? 6 : 8;
@@ -454,9 +456,12 @@ extern "C" int mpas_b200_advance_acoustic_step_work(MPAS_ACOUSTIC_ARGS) {
         p.ru_p = X(ru_p);
         p.rw_p = X(rw_p); p.rtheta_pp = X(rtheta_pp); p.rtheta_pp_old = X(rtheta_pp_old); p.wwAvg = X(wwAvg); p.rho_pp = X(rho_pp);
         const int ncols = cellEnd - cellStart + 1;
-        const size_t shm = (size_t)WPB * AC_NCOL * tma_slot(L + 1) * sizeof(real);
+        const size_t shm = (size_t)WPB * (small_step == 1 ? AC_NCOL - 3 : AC_NCOL) * tma_slot(L + 1) * sizeof(real);
         p.tend_ru_fold = X(tend_ru);
-        if (fold) WLAUNCH((acoustic_cell_kernel<true, true>), ncols, shm, p);
+        static const int first_minb = tune("ac_first_minb", 5);
+        if (fold && first_minb == 5) WLAUNCH((acoustic_cell_kernel<true, true, 5>), ncols, shm, p);
+        else if (fold) WLAUNCH((acoustic_cell_kernel<true, true>), ncols, shm, p);
+        else if (small_step == 1 && first_minb == 5) WLAUNCH((acoustic_cell_kernel<true, false, 5>), ncols, shm, p);
         else if (small_step == 1) WLAUNCH(acoustic_cell_kernel<true>, ncols, shm, p);
         else WLAUNCH(acoustic_cell_kernel<false>, ncols, shm, p);
         KCHECK("acoustic_cell_kernel");
