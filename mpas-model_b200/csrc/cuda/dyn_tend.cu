@@ -726,7 +726,9 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : MINB) dt_edge_kernel(DtP 
     const int L = p.L, L1 = L + 1, mE2 = p.mE2, LS = tma_slot(L1);
     WARP_ENTITY(p.edgeSolveStart, p.nEdgesSolveLoop);
     const int iEdge = ent;
-    real* sc = s_dyn + (size_t)warp * (RK1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * LS;
+    // rk 2, 3: the vertical flux of a level overwrites the rw column of cell 1 it was computed from (same lane, same level),
+    // 10 slots per warp; rk 1 keeps its own slot (the rw slots are reused by the delsq_vorticity copies)
+    real* sc = s_dyn + (size_t)warp * (RK1 ? EC_NCOL_RK1 : EC_NCOL_RK23 - 1) * LS;
     const unsigned mbar = (unsigned)__cvta_generic_to_shared(&s_bar[warp]);
     const int cell1 = p.cellsOnEdge[IX2(1, iEdge, 2)], cell2 = p.cellsOnEdge[IX2(2, iEdge, 2)];
     const bool del4 = (RK1 && p.h_mom_eddy_visc4 > (real)0.0);
@@ -801,7 +803,7 @@ __global__ void __launch_bounds__(WPB * 32, VMIX ? 1 : MINB) dt_edge_kernel(DtP 
     const real* su = sc + x_u - 1;  // 1-based views: su[k] = u(k, iEdge)
     const real* srw1 = sc + x_rw1 - 1;
     const real* srw2 = sc + x_rw2 - 1;
-    real* wz = sc + EC_WZ * LS - 1;
+    real* wz = RK1 ? sc + EC_WZ * LS - 1 : sc + x_rw1 - 1;
     for (int kk = lane + 1; kk <= L1; kk += 32) {  // vertical flux of u at the interfaces, TI:4792-4804
         // branch-free: every lane evaluates both the 3rd-order flux (stencil indices clamped into the column) and the
         // 2nd-order boundary form, then selects; a divergent if/else would make the warp execute both anyway
@@ -1257,7 +1259,7 @@ extern "C" int mpas_b200_compute_dyn_tend_work(MPAS_DYNTEND_ARGS) {
     else WLAUNCH((dt_edge_flux_kernel<false, 0>), p.nEdgesLoop, 0, p, ft, fw, ft2);
     KCHECK("dt_edge_flux_kernel");
     {
-        const size_t shm = (size_t)WPB * (rk_step == 1 ? EC_NCOL_RK1 : EC_NCOL_RK23) * tma_slot(L + 1) * sizeof(real);
+        const size_t shm = (size_t)WPB * (rk_step == 1 ? EC_NCOL_RK1 : EC_NCOL_RK23 - 1) * tma_slot(L + 1) * sizeof(real);
         static const int de_minb = tune("dt_edge_minb", 5);
         if (rk_step != 1 && de_minb == 5) WLAUNCH((dt_edge_kernel<5, false, false, 5>), p.nEdgesSolveLoop, shm, p);
         else if (rk_step != 1 && de_minb == 3) WLAUNCH((dt_edge_kernel<5, false, false, 3>), p.nEdgesSolveLoop, shm, p);
