@@ -117,7 +117,7 @@ long mpas_b200_dycore_exchange_count(void* h);
  * (CUDA IPC over NVLink, switched on after the second step when every rank can map every other); -2 a peer-to-peer wait
  * timed out since the last call.  MPAS_B200_TUNE_p2p=0 keeps NCCL. */
 int mpas_b200_dycore_halo_transport(void* h);
-int mpas_b200_dycore_set_option(void* h, const char* name, int value); /* "timing", "graph", "aggregate"; "diet" (before attach_block) */
+int mpas_b200_dycore_set_option(void* h, const char* name, int value); /* "timing", "graph", "aggregate"; "diet" (before attach_block); "fold_first" (before the first step) */
 /* memory diet (default on; option "diet" = 0 before attach_block gives every pool array its own mirror): arrays only physics or
  * output use (gradPVn/t, ke_edge, tend_*_physics, rthdynten, tend_rtheta_adv, rt_diabatic_tend: optional arguments of the work
  * routines) get no mirror, and phase-local scratch (the delsq_* / dpdz arrays of TI:592-605, the mono scratch of TI:1029-1050,

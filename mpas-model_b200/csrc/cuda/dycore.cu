@@ -596,6 +596,7 @@ int mpas_b200_dycore_set_option(void* h, const char* name, int value) {
     else if (n == "graph") m->use_graph = value != 0;
     else if (n == "aggregate") m->aggregate = value != 0;
     else if (n == "diet") m->diet = value != 0;  // before attach_block
+    else if (n == "fold_first") m->fold_first = value != 0;  // before the first step (a captured graph keeps what it was captured with)
     else return fail_msg("unknown option " + n);
     return 0;
 }

@@ -85,6 +85,7 @@ struct Dycore {
     long nExchanges = 0;
     bool timing = false;
     bool aggregate = true;
+    bool fold_first = true;  // first acoustic substep's edge pass folded into the divergence damping (srk3.cu, acoustic.cu); option "fold_first"
     bool use_graph = false;
     bool diet = true;  // phase-local scratch shares one arena; optional (physics / output-only) arrays get no mirror
     std::map<std::string, PhaseTimer> timers;

@@ -407,7 +407,7 @@ static int srk3_body(Dycore& m) {
                     Phase ph(m, "atm_advance_acoustic_step");
                     static const int fold_first = tune("ac_fold_first", 1);
                     for (auto& b : m.blocks) {
-                        if (fold_first && small_step == 1) acoustic_fold_next_call();  // its edge pass runs inside the divergence damping below
+                        if (fold_first && m.fold_first && small_step == 1) acoustic_fold_next_call();  // its edge pass runs inside the divergence damping below
                         CK(call_acoustic(b, rk_sub_timestep[rk_step], small_step));  // TI:824
                     }
                 }

@@ -1,5 +1,7 @@
 """GPU parity proper: the device-resident dycore (every kernel, through the C ABI work routines) against
 the CPU oracle on identical inputs.  Tolerance: 1e-12 relative L2 after 1 and 10 steps (north_star)."""
+import ctypes as C
+
 import numpy as np
 import pytest
 
@@ -226,6 +228,31 @@ def test_memory_diet_is_bitwise_neutral_and_smaller(nblocks):
     a.step(4); b.step(4)
     for ib in range(nblocks):
         for n in STATE + DIAG:
+            assert np.array_equal(a.field(ib, n), b.field(ib, n)), (ib, n)
+
+
+@pytest.mark.parametrize("nblocks", [1, 3])
+def test_folded_first_substep_edge_pass_is_bitwise_neutral(nblocks):
+    """The device-resident driver leaves the first acoustic substep's edge pass (TI:2592-2597: ru_p = dts * tend_ru, ruAvg = ru_p) to
+    the divergence damping that follows (DESIGN.md section 3 rule 12; option "fold_first", default on).  Every STATE / DIAG field,
+    ru_p and ruAvg included, stays bitwise equal to the run that launches the edge pass; eager and graph replay; the launch count
+    drops by one per first substep (3 RK stages x config_dynamics_split_steps)."""
+    case, blocks = common.make_case(4, nblocks, nVertLevels=26, num_scalars=2)
+    _tracers(blocks, 2)
+    cfg = common.level_config(4)
+    a = common.GpuModel(blocks, cfg)
+    b = common.GpuModel(blocks, cfg)
+    b.set_option("fold_first", 0)
+    a.set_option("graph", 1)
+    a.init(); b.init()
+    L = common.host.lib()
+    L.mpas_b200_launch_count.restype = C.c_longlong
+    n0 = L.mpas_b200_launch_count(); b.step(1); n_plain = L.mpas_b200_launch_count() - n0
+    n0 = L.mpas_b200_launch_count(); a.step(1); n_fold = L.mpas_b200_launch_count() - n0
+    assert n_plain - n_fold == 3 * int(cfg.get("config_dynamics_split_steps", 3)) * nblocks, (n_plain, n_fold)
+    a.step(3); b.step(3)
+    for ib in range(nblocks):
+        for n in STATE + DIAG + ["ru_p", "ruAvg"]:
             assert np.array_equal(a.field(ib, n), b.field(ib, n)), (ib, n)
 
 
