@@ -247,9 +247,13 @@ inline T* X(T* p) { return (T*)xlate((const void*)p); }
 template <class T>
 inline const T* X(const T* p) { return (const T*)xlate((const void*)p); }
 
-// acoustic.cu: the next mpas_b200_advance_acoustic_step_work call of this thread (small_step 1 only) skips its edge pass
-// ru_p = dts * tend_ru; the mpas_b200_divergence_damping_3d call on the same ru_p that follows does it
-void acoustic_fold_next_call();
+// acoustic.cu: what the device-resident driver tells the next mpas_b200_advance_acoustic_step_work call of this thread.
+//   FIRST (small_step 1): skip the edge pass ru_p = dts * tend_ru; the mpas_b200_divergence_damping_3d call on the same ru_p
+//          that follows does it;
+//   NEXT:  a substep follows: that damping call also runs the NEXT substep's edge pass (the driver exchanges rho_pp first);
+//   DONE:  this call's edge pass has been run that way: skip it.
+enum { ACOUSTIC_FOLD_FIRST = 1, ACOUSTIC_FOLD_NEXT = 2, ACOUSTIC_FOLD_DONE = 4 };
+void acoustic_fold_next_call(int flags);
 
 // opt a kernel in to more than 48 KB of dynamic shared memory (cached per kernel); false if it cannot be granted
 bool ensure_dyn_smem(const void* kernel, size_t bytes);

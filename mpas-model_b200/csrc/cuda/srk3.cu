@@ -401,17 +401,23 @@ static int srk3_body(Dycore& m) {
                 Phase ph(m, "small_step_prep");
                 for (auto& b : m.blocks) CK(call_smlstep(b));  // TI:669
             }
+            // The edge pass of an acoustic substep (TI:2552-2599) is folded into the divergence damping of the substep before it (the
+            // first one: into its own), DESIGN.md section 3 rule 12: the damping kernel then needs the rho_pp halo of the NEXT
+            // substep, so that exchange (TI:792) moves up from the top of the next substep to just before the damping.
+            static const int fold_tune = tune("ac_fold_first", 1);
+            const bool fold = fold_tune && m.fold_first;
             for (int small_step = 1; small_step <= number_sub_steps[rk_step]; ++small_step) {
-                CK(xchg(m, {{"rho_pp", 1}}));  // TI:792
+                const bool next = fold && small_step < number_sub_steps[rk_step], done = fold && small_step > 1;
+                if (!done) CK(xchg(m, {{"rho_pp", 1}}));  // TI:792
                 {
                     Phase ph(m, "atm_advance_acoustic_step");
-                    static const int fold_first = tune("ac_fold_first", 1);
                     for (auto& b : m.blocks) {
-                        if (fold_first && m.fold_first && small_step == 1) acoustic_fold_next_call();  // its edge pass runs inside the divergence damping below
+                        if (fold) acoustic_fold_next_call((small_step == 1 ? ACOUSTIC_FOLD_FIRST : 0) | (next ? ACOUSTIC_FOLD_NEXT : 0) | (done ? ACOUSTIC_FOLD_DONE : 0));
                         CK(call_acoustic(b, rk_sub_timestep[rk_step], small_step));  // TI:824
                     }
                 }
                 CK(xchg(m, {{"rtheta_pp", 1}}));  // TI:845
+                if (next) CK(xchg(m, {{"rho_pp", 1}}));  // TI:792 of the next substep
                 {
                     Phase ph(m, "atm_divergence_damping_3d");
                     for (auto& b : m.blocks) CK(call_divdamp(b, rk_sub_timestep[rk_step]));  // TI:862

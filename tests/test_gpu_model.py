@@ -235,8 +235,9 @@ def test_memory_diet_is_bitwise_neutral_and_smaller(nblocks):
 def test_folded_first_substep_edge_pass_is_bitwise_neutral(nblocks):
     """The device-resident driver leaves the first acoustic substep's edge pass (TI:2592-2597: ru_p = dts * tend_ru, ruAvg = ru_p) to
     the divergence damping that follows (DESIGN.md section 3 rule 12; option "fold_first", default on).  Every STATE / DIAG field,
-    ru_p and ruAvg included, stays bitwise equal to the run that launches the edge pass; eager and graph replay; the launch count
-    drops by one per first substep (3 RK stages x config_dynamics_split_steps)."""
+    ru_p and ruAvg included, stays bitwise equal to the run that launches the edge pass; eager and graph replay.  Later substeps'
+    edge passes run inside the damping of the substep before them, so the launch count drops by one per acoustic substep
+    (number_sub_steps = 1, 1, 2 over the three RK stages, times config_dynamics_split_steps)."""
     case, blocks = common.make_case(4, nblocks, nVertLevels=26, num_scalars=2)
     _tracers(blocks, 2)
     cfg = common.level_config(4)
@@ -249,7 +250,7 @@ def test_folded_first_substep_edge_pass_is_bitwise_neutral(nblocks):
     L.mpas_b200_launch_count.restype = C.c_longlong
     n0 = L.mpas_b200_launch_count(); b.step(1); n_plain = L.mpas_b200_launch_count() - n0
     n0 = L.mpas_b200_launch_count(); a.step(1); n_fold = L.mpas_b200_launch_count() - n0
-    assert n_plain - n_fold == 3 * int(cfg.get("config_dynamics_split_steps", 3)) * nblocks, (n_plain, n_fold)
+    assert n_plain - n_fold == (1 + 1 + 2) * int(cfg.get("config_dynamics_split_steps", 3)) * nblocks, (n_plain, n_fold)
     a.step(3); b.step(3)
     for ib in range(nblocks):
         for n in STATE + DIAG + ["ru_p", "ruAvg"]:
