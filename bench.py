@@ -425,14 +425,13 @@ def run_b200(a):
         phases[name] = e
     # The device-resident driver runs every acoustic edge pass inside a divergence-damping launch (DESIGN.md section 3 rule 12), so the two
     # routines' timers are only meaningful together: their combined algorithmic bytes over their combined time.
-    a, d = phases.get("atm_advance_acoustic_step"), phases.get("atm_divergence_damping_3d")
-    if a and d and "algorithmic_GB_per_call" in a and "algorithmic_GB_per_call" in d:
-        gb = a["algorithmic_GB_per_call"] * a["calls_per_step"] + d["algorithmic_GB_per_call"] * d["calls_per_step"]
-        ms = a["ms_per_step"] + d["ms_per_step"]
-        note = "edge pass folded into the damping launch: read with the other routine, see acoustic_plus_divergence_damping"
-        a["note"] = d["note"] = note
-        phases["acoustic_plus_divergence_damping"] = {"ms_per_step": ms, "algorithmic_GB_per_step": gb, "achieved_GBs": gb / (ms / 1000.0),
-                                                      "frac": gb / (ms / 1000.0) / peak_gbs}
+    ph_ac, ph_dd = phases.get("atm_advance_acoustic_step"), phases.get("atm_divergence_damping_3d")
+    if ph_ac and ph_dd and "algorithmic_GB_per_call" in ph_ac and "algorithmic_GB_per_call" in ph_dd:
+        gb_pair = ph_ac["algorithmic_GB_per_call"] * ph_ac["calls_per_step"] + ph_dd["algorithmic_GB_per_call"] * ph_dd["calls_per_step"]
+        ms_pair = ph_ac["ms_per_step"] + ph_dd["ms_per_step"]
+        ph_ac["note"] = ph_dd["note"] = "edge pass folded into the damping launch: read with the other routine, see acoustic_plus_divergence_damping"
+        phases["acoustic_plus_divergence_damping"] = {"ms_per_step": ms_pair, "algorithmic_GB_per_step": gb_pair, "achieved_GBs": gb_pair / (ms_pair / 1000.0),
+                                                      "frac": gb_pair / (ms_pair / 1000.0) / peak_gbs}
     dom = max((n for n in phases if n in words), key=lambda n: phases[n]["ms_per_step"])
     roofline = {"bound": "hbm", "kernel": dom, "achieved": phases[dom]["achieved_GBs"], "peak": peak_gbs, "unit": "GB/s", "frac": phases[dom]["frac"],
                 "traffic": None, "peak_source": peak_src,
